@@ -1,0 +1,133 @@
+"""Training-step engine (the hot loops of ``resnet50_test.py:521-567`` and
+``transformer_test.py:241-283``).
+
+One :class:`Trainer` step is::
+
+    zero flat grads → forward + loss (bf16 on CUDA) → backward → engine.reduce_gradients()
+    → global-norm clip (device scalar, non-finite guard) → optimizer.step() → engine.post_step()
+
+with **no host synchronisation anywhere** (the reference syncs for ``loss.item()``, the
+GradScaler's found-inf check, every NGD factor and four times for its progress line).  Because
+of that the whole step can be captured in a CUDA graph: ``use_cuda_graph=True`` captures one
+graph per optimizer step kind ("update" = Fisher refresh, "plain") after an eager warm-up and
+replays them, so a ResNet-50 step at 32×32 — hundreds of small kernels — costs one launch.
+
+bf16 replaces the reference's fp16 autocast + GradScaler (``resnet50_test.py:533-548``): no loss
+scaling is needed; ``fdt.engine.amp.DynamicLossScaler`` provides the GradScaler-equivalent
+(device-side, sync-free) for ``--dtype fp16`` runs.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..parallel.ddp import DataParallelEngine
+from ..parallel.comm import Communicator
+
+
+def as_engine(model: nn.Module) -> nn.Module:
+    """Wrap a bare module so that it has the flat-buffer engine interface."""
+    if hasattr(model, "reduce_gradients"):
+        return model
+    return DataParallelEngine(model, Communicator())
+
+
+class Trainer:
+    def __init__(self, engine: nn.Module, optimizer, forward_loss: Callable, clip_norm: Optional[float] = 10.0,
+                 use_cuda_graph: bool = False, scaler=None, graph_warmup: int = 11):
+        self.engine = as_engine(engine)
+        self.optimizer = optimizer
+        self.forward_loss = forward_loss
+        self.clip_norm = clip_norm
+        self.scaler = scaler
+        self.device = self.engine.flat.device
+        self.use_graph = bool(use_cuda_graph) and self.device.type == "cuda"
+        self.graph_warmup = graph_warmup
+        self._graphs: Dict[str, Any] = {}
+        self._static_in = None
+        self._static_out = None
+        self._steps = 0
+        self.skipped = torch.zeros((), device=self.device)   # steps whose gradients were non-finite
+        if self.use_graph and hasattr(optimizer, "set_capturable"):
+            optimizer.set_capturable(True)
+
+    # ------------------------------------------------------------------ one eager step
+    def _local_grad(self) -> torch.Tensor:
+        eng = self.engine
+        if hasattr(eng, "region") and eng.comm.world > 1:
+            lo, hi = eng.region
+            return eng.flat.grad_flat[lo:hi]
+        return eng.flat.grad_flat
+
+    def _clip(self):
+        g = self._local_grad()
+        sq = self.engine.grad_sq_norm()
+        finite = torch.isfinite(sq)
+        if self.clip_norm is not None:
+            coef = (self.clip_norm / (sq.sqrt() + 1e-6)).clamp(max=1.0)
+        else:
+            coef = torch.ones_like(sq)
+        coef = torch.where(finite, coef, torch.zeros_like(coef))
+        g.mul_(coef)
+        torch.nan_to_num_(g, nan=0.0, posinf=0.0, neginf=0.0)
+        self.skipped += (~finite).float()
+
+    def _eager_step(self, batch) -> Tuple[torch.Tensor, Any]:
+        eng = self.engine
+        eng.zero_grad()
+        eng.pre_forward()
+        loss, aux = self.forward_loss(eng, batch)
+        if self.scaler is not None:
+            self.scaler.scale(loss).backward()
+        else:
+            loss.backward()
+        eng.reduce_gradients()
+        if self.scaler is not None:
+            self.scaler.unscale_(self._local_grad())
+        self._clip()
+        self.optimizer.step()
+        if hasattr(eng, "post_step"):
+            eng.post_step()
+        return loss.detach(), aux
+
+    # ------------------------------------------------------------------ graph capture
+    def _kind(self) -> str:
+        fn = getattr(self.optimizer, "next_step_kind", None)
+        return fn() if fn is not None else "plain"
+
+    def _copy_in(self, batch):
+        if self._static_in is None:
+            self._static_in = tuple(b.clone() if torch.is_tensor(b) else b for b in batch)
+        else:
+            for s, b in zip(self._static_in, batch):
+                if torch.is_tensor(s):
+                    s.copy_(b, non_blocking=True)
+        return self._static_in
+
+    def step(self, batch) -> Tuple[torch.Tensor, Any]:
+        """``batch`` is a tuple of device tensors.  Returns ``(loss, aux)`` (device tensors; with
+        graphs they are static buffers overwritten by the next step)."""
+        self._steps += 1
+        if hasattr(self.optimizer, "sync_lr"):
+            self.optimizer.sync_lr()
+        if not self.use_graph:
+            return self._eager_step(batch)
+        kind = self._kind()
+        if kind == "warm" or self._steps <= self.graph_warmup:
+            return self._eager_step(batch)
+        static = self._copy_in(batch)
+        if kind not in self._graphs:
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out = self._eager_step(static)
+            self._graphs[kind] = (g, out)
+            return out
+        g, out = self._graphs[kind]
+        g.replay()
+        adv = getattr(self.optimizer, "advance_without_python", None)
+        if adv is not None:
+            adv()
+        return out

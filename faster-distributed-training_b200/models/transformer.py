@@ -1,0 +1,212 @@
+"""Encoder-only Transformer classifier with reference-compatible state-dict keys.
+
+Capability parity with ``transformer.py:12-371`` of the reference: token + learned-position +
+segment embeddings scaled by sqrt(d_model), sinusoidal encoding, ``n_layers`` × [pre-LN
+multi-head attention sub-layer, pre-LN GELU FFN sub-layer], tanh pooler over token 0,
+manifold mixup of the pooled vector, two-layer ReLU classifier head.  Key names follow
+SURVEY.md §5.4 (``sublayer_attention.L.multiheads.heads.{0,1,2}.weight``,
+``classifier.classifier.W1`` ...), so checkpoints interchange with the reference.
+
+Execution goes through :mod:`fdt.ops`: on a B200 the projections are tcgen05 GEMMs with fused
+bias/GELU epilogues, LayerNorm / attention / embedding / head are single fused kernels; on CPU
+the PyTorch oracle runs.
+
+Reference semantics kept: Q12 ``x = emb + dropout(emb + pe)``; Q15 LayerNorm
+with unbiased std and eps outside the sqrt.  Deliberate fixes, each with a compat switch:
+Q11 padding is really masked (``mask_compat=True`` restores the ``-1e-9`` fill);
+Q13 mixup only in training, eval returns logits; Q14 head bias gradients are sums
+(``bias_grad_mean_compat=True`` restores the batch-mean).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..data import mixup as mx
+
+
+class LayerNorm(nn.Module):
+    def __init__(self, features, eps=1e-6):
+        super().__init__()
+        self.a_2 = nn.Parameter(torch.ones(features))
+        self.b_2 = nn.Parameter(torch.zeros(features))
+        self.eps = eps
+
+    def forward(self, x):
+        return ops.layernorm_ref(x, self.a_2, self.b_2, self.eps)
+
+
+class Embeddings(nn.Module):
+    def __init__(self, d_model, vocab, maxlen):
+        super().__init__()
+        self.token_embedding = nn.Embedding(vocab, d_model)
+        self.pos_embedding = nn.Embedding(maxlen, d_model)
+        self.segment_embedding = nn.Embedding(3, d_model)
+        self.d_model, self.maxlen = d_model, maxlen
+
+    def forward(self, tokens, token_types):
+        return ops.embed(tokens, token_types, self.token_embedding.weight, self.pos_embedding.weight,
+                         self.segment_embedding.weight, math.sqrt(self.d_model))
+
+
+class PositionalEncoding(nn.Module):
+    """Sinusoidal table; kept as a plain attribute (not in the state dict), as in the reference
+    (transformer.py:118)."""
+
+    def __init__(self, d_model, dropout, max_len):
+        super().__init__()
+        self.p = dropout
+        pe = torch.zeros(max_len, d_model)
+        position = torch.arange(0, max_len).unsqueeze(1).float()
+        scale = torch.exp(torch.arange(0, d_model, 2).float() * -(math.log(10000.0) / d_model))
+        pe[:, 0::2] = torch.sin(position * scale)
+        pe[:, 1::2] = torch.cos(position * scale)
+        self.pe = pe.unsqueeze(0)
+
+    def table(self, like: torch.Tensor, L: int):
+        if self.pe.device != like.device or self.pe.dtype != like.dtype:
+            self.pe = self.pe.to(device=like.device, dtype=like.dtype)
+        return self.pe[:, :L]
+
+
+class MultiheadAttention(nn.Module):
+    def __init__(self, h, d_model, dropout=0.1, mask_compat=False):
+        super().__init__()
+        assert d_model % h == 0
+        self.d_k, self.h, self.p, self.mask_compat = d_model // h, h, dropout, mask_compat
+        self.heads = nn.ModuleList([nn.Linear(d_model, d_model) for _ in range(3)])
+        self.output = nn.Linear(d_model, d_model)
+
+    def forward(self, x, key_mask=None):
+        B, L, _ = x.shape
+        q, k, v = [ops.linear(x, l.weight, l.bias).view(B, L, self.h, self.d_k).transpose(1, 2)
+                   for l in self.heads]
+        o = ops.attention(q, k, v, key_mask, self.p, self.training, self.mask_compat)
+        o = o.transpose(1, 2).reshape(B, L, self.h * self.d_k)
+        return ops.linear(o, self.output.weight, self.output.bias)
+
+
+class PositionalWiseFFN(nn.Module):
+    def __init__(self, d_model, d_ff, dropout=0.1):
+        super().__init__()
+        self.w_1 = nn.Linear(d_model, d_ff)
+        self.w_2 = nn.Linear(d_ff, d_model)
+        self.p = dropout
+
+    def forward(self, x):
+        h = ops.linear(x, self.w_1.weight, self.w_1.bias, act="gelu")
+        if self.p > 0 and self.training:
+            h = torch.nn.functional.dropout(h, self.p, True)
+        return ops.linear(h, self.w_2.weight, self.w_2.bias)
+
+
+class sublayerConnectionAttention(nn.Module):
+    def __init__(self, h, d_model, dropout_head=0.1, dropout_connection=0.1, mask_compat=False):
+        super().__init__()
+        self.multiheads = MultiheadAttention(h, d_model, dropout_head, mask_compat)
+        self.layernorm = LayerNorm(d_model)
+        self.p = dropout_connection
+
+    def forward(self, x, key_mask=None):
+        return ops.dropout_add(self.multiheads(self.layernorm(x), key_mask), x, self.p, self.training)
+
+
+class sublayerConnectionFFN(nn.Module):
+    def __init__(self, d_model, d_ff, dropout_ffn=0.1, dropout_connection=0.1):
+        super().__init__()
+        self.ffn = PositionalWiseFFN(d_model, d_ff, dropout_ffn)
+        self.layernorm = LayerNorm(d_model)
+        self.p = dropout_connection
+
+    def forward(self, x):
+        return ops.dropout_add(self.ffn(self.layernorm(x)), x, self.p, self.training)
+
+
+class Pooler(nn.Module):
+    def __init__(self, hidden_size):
+        super().__init__()
+        self.dense = nn.Linear(hidden_size, hidden_size)
+
+    def forward(self, x):
+        return ops.linear(x[:, 0, :].contiguous(), self.dense.weight, self.dense.bias, act="tanh")
+
+
+class FusedMLP(nn.Module):
+    """Linear → ReLU → Linear head with (1, H) biases (transformer.py:341-371)."""
+
+    def __init__(self, input_channel, hidden_channel, output_channel, bias_grad_mean_compat=False):
+        super().__init__()
+        self.W1 = nn.Parameter(torch.empty(hidden_channel, input_channel))
+        self.b1 = nn.Parameter(torch.zeros(1, hidden_channel))
+        self.W2 = nn.Parameter(torch.empty(output_channel, hidden_channel))
+        self.b2 = nn.Parameter(torch.zeros(1, output_channel))
+        self.compat = bias_grad_mean_compat
+        nn.init.xavier_uniform_(self.W1)
+        nn.init.xavier_uniform_(self.W2)
+
+    def forward(self, x):
+        return ops.mlp_head(x, self.W1, self.b1, self.W2, self.b2, self.compat)
+
+
+class Classifier(nn.Module):
+    def __init__(self, d_model, d_hidden, n_class, bias_grad_mean_compat=False):
+        super().__init__()
+        self.classifier = FusedMLP(d_model, d_hidden, n_class, bias_grad_mean_compat)
+
+    def forward(self, x):
+        return self.classifier(x)
+
+
+class Transformer(nn.Module):
+    def __init__(self, n_class, vocab, n_layers=6, h=8, d_model=512, d_ff=1024, d_hidden=1024,
+                 maxlen=512, dropout_encodings=0.1, dropout_connection_attention=0.1,
+                 dropout_connection_ffn=0.1, dropout_attention=0.1, dropout_ffn=0.1, alpha=0.99,
+                 mask_compat=False, bias_grad_mean_compat=False):
+        super().__init__()
+        self.input_embeddings = Embeddings(d_model, vocab, maxlen)
+        self.input_encodings = PositionalEncoding(d_model, dropout_encodings, maxlen)
+        self.sublayer_attention = nn.ModuleList()
+        self.sublayer_ffn = nn.ModuleList()
+        for _ in range(n_layers):
+            self.sublayer_attention.append(sublayerConnectionAttention(
+                h, d_model, dropout_attention, dropout_connection_attention, mask_compat))
+            self.sublayer_ffn.append(sublayerConnectionFFN(d_model, d_ff, dropout_ffn, dropout_connection_ffn))
+        self.pooler = Pooler(d_model)
+        self.p_post = 0.1
+        self.classifier = Classifier(d_model, d_hidden, n_class, bias_grad_mean_compat)
+        self.n_layers, self.alpha = n_layers, alpha
+        self.init_params()
+
+    def init_params(self):
+        for _, p in self.named_parameters():
+            if p.dim() > 1:
+                nn.init.xavier_uniform_(p)
+
+    def encode(self, tokens, token_types, key_mask=None):
+        emb = self.input_embeddings(tokens, token_types)
+        pe = self.input_encodings.table(emb, emb.size(1))
+        # Q12: embeddings are counted twice, x = emb + dropout(emb + pe)
+        x = ops.dropout_add(emb + pe, emb, self.input_encodings.p, self.training)
+        for att, ffn in zip(self.sublayer_attention, self.sublayer_ffn):
+            x = ffn(att(x, key_mask))
+        x = self.pooler(x)
+        if self.training:
+            x = torch.nn.functional.dropout(x, self.p_post, True)
+        return x
+
+    def forward(self, tokens, token_types, index=None, mask=None, generator=None):
+        """``mask`` may be [B, L] or the reference's [B, 1, 1, L] (transformer_test.py:260).
+        ``index`` (the reference's position-index argument) is accepted and ignored: positions
+        are always ``arange(L)``.  Training returns ``(logits, perm, lam)``, eval ``logits``."""
+        key_mask = None if mask is None else mask.reshape(mask.shape[0], -1)
+        x = self.encode(tokens, token_types, key_mask)
+        if not self.training:
+            return self.classifier(x)
+        lam = mx.sample_beta(self.alpha, x.device, generator=generator)
+        perm = mx.randperm(x.size(0), x.device, generator)
+        l = lam.to(x.dtype)
+        mixed = l * x + (1.0 - l) * x[perm]
+        return self.classifier(mixed), perm, lam

@@ -1,0 +1,103 @@
+"""Fused-op front end.
+
+Every model and optimizer in the framework calls the functions below.  On CPU tensors they
+run the pure-PyTorch oracle in :mod:`fdt.ops.reference`; on CUDA tensors they run the
+hand-written sm_100a kernels from ``csrc/`` (loaded by :mod:`fdt.ops._lib`) through the
+autograd wrappers in :mod:`fdt.ops.cuda_ops`.  There is no silent fallback on a GPU: if the
+native library is missing the call raises, unless ``FDT_FORCE_TORCH=1`` explicitly selects
+the oracle (used by the numerics tests to produce reference values on the same device).
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from . import reference as ref
+
+_FORCE_TORCH = os.environ.get("FDT_FORCE_TORCH", "0") == "1"
+
+
+def force_torch(flag: bool) -> None:
+    """Route CUDA tensors through the PyTorch oracle (tests / debugging only)."""
+    global _FORCE_TORCH
+    _FORCE_TORCH = bool(flag)
+
+
+def use_native(t: torch.Tensor) -> bool:
+    return t.is_cuda and not _FORCE_TORCH
+
+
+def _cu():
+    from . import cuda_ops
+    return cuda_ops
+
+
+def conv_bnstat_act(x, weight, stride=1, padding=0, eps=1e-3, act="none", residual=None):
+    if use_native(x):
+        return _cu().conv_bnstat_act(x, weight, stride, padding, eps, act, residual)
+    return ref.conv_bnstat_act(x, weight, stride, padding, eps, act, residual)
+
+
+def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_batches_tracked,
+                      stride=1, padding=0, eps=1e-5, momentum=0.1, training=True,
+                      act="none", residual=None):
+    if use_native(x):
+        return _cu().conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
+                                       num_batches_tracked, stride, padding, eps, momentum,
+                                       training, act, residual)
+    return ref.conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
+                                 num_batches_tracked, stride, padding, eps, momentum,
+                                 training, act, residual)
+
+
+def pool_fc(x, weight, bias):
+    if use_native(x):
+        return _cu().pool_fc(x, weight, bias)
+    return ref.pool_fc(x, weight, bias)
+
+
+def mixup_cross_entropy(logits, y_a, y_b, lam):
+    if use_native(logits):
+        return _cu().mixup_cross_entropy(logits, y_a, y_b, lam)
+    return ref.mixup_cross_entropy(logits, y_a, y_b, lam)
+
+
+def mixup_correct(logits, y_a, y_b, lam):
+    return ref.mixup_correct(logits, y_a, y_b, lam)
+
+
+def layernorm_ref(x, a_2, b_2, eps=1e-6):
+    if use_native(x):
+        return _cu().layernorm_ref(x, a_2, b_2, eps)
+    return ref.layernorm_ref(x, a_2, b_2, eps)
+
+
+def linear(x, weight, bias=None, act="none"):
+    if use_native(x):
+        return _cu().linear(x, weight, bias, act)
+    return ref.linear(x, weight, bias, act)
+
+
+def attention(q, k, v, key_mask=None, dropout_p=0.0, training=True, mask_compat=False):
+    if use_native(q):
+        return _cu().attention(q, k, v, key_mask, dropout_p, training, mask_compat)
+    return ref.attention(q, k, v, key_mask, dropout_p, training, mask_compat)
+
+
+def embed(tokens, token_types, tok_w, pos_w, seg_w, scale):
+    if use_native(tok_w):
+        return _cu().embed(tokens, token_types, tok_w, pos_w, seg_w, scale)
+    return ref.embed(tokens, token_types, tok_w, pos_w, seg_w, scale)
+
+
+def mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat=False):
+    if use_native(x):
+        return _cu().mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat)
+    return ref.mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat)
+
+
+def dropout_add(x, residual, p, training):
+    if use_native(x):
+        return _cu().dropout_add(x, residual, p, training)
+    return ref.dropout_add(x, residual, p, training)

@@ -1,0 +1,412 @@
+"""NGD — SGD whose gradient is preconditioned per tensor axis by an online natural-gradient
+(low-rank-plus-identity inverse-Fisher) factor.
+
+Capability parity with ``ngd_optimizer.py:8-508`` of the reference (``OnlineNaturalGradient`` +
+``NGD``; maths in SURVEY.md §3.4), re-designed for a B200:
+
+* **Batched by shape.**  Parameters with identical shapes are processed together: their
+  gradients form one ``[n, *shape]`` tensor (a zero-copy view when the parameters live in a
+  :class:`fdt.parallel.flat.FlatParameters` buffer) and every factor quantity is a batched
+  tensor (``W [n,R,D]``, ``d [n,R]``, ``rho [n]``).  ResNet-50's 157 active factors become
+  ~35 batched problems instead of 157 serial Python objects (``ngd_optimizer.py:474-491``).
+* **No host synchronisation.**  The reference reads 7 scalars back per factor per update
+  (``.item()`` at ``ngd_optimizer.py:225,240,285,287,289,300`` + ``math.isnan`` :158); here β, e,
+  z-scale, floors, ρ and the NaN guard are device tensors, and on CUDA the R×R symmetric
+  eigenproblem plus all the scalar algebra is ONE kernel launch for every factor of every
+  group (``csrc/ngd_eig.cu``: in-shared-memory parallel Jacobi), so a step is capturable in a
+  CUDA graph.
+* **Tensor-only state** (``state_dict`` holds W/d/rho/momentum tensors and integer counters),
+  unlike the reference whose state holds live Python objects.
+
+Semantics kept exactly: weight decay is added to the gradient in place
+*before* preconditioning; axes are preconditioned sequentially; the Frobenius norm of the
+gradient is restored after each axis; at the first call the factor is default-initialised and
+warm-started with 3 extra updates on the same gradient (``ngd_optimizer.py:356-376``); the Fisher
+estimate is refreshed on every call for the first 10 calls, then every ``update_period``.
+Fixed (Q18): Nesterov uses ``d_p + momentum * buf``.
+"""
+from __future__ import annotations
+
+import math
+from collections import OrderedDict
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch.optim import Optimizer
+
+EPSILON = 1.0e-10   # ngd_optimizer.py:37
+DELTA = 5.0e-4      # ngd_optimizer.py:38
+NUM_INITIAL_ITERS = 10
+
+
+def default_rank(dim: int) -> int:
+    return min((dim + 1) // 2, 80)
+
+
+def orthonormal_special(rank: int, dim: int, dtype, device) -> torch.Tensor:
+    """The deterministic near-orthonormal R×D start matrix (ngd_optimizer.py:397-420)."""
+    first_elem = 1.1
+    num_cols = dim // rank
+    remainder = dim % rank
+    k = torch.full((rank,), 1.0 / math.sqrt(first_elem * first_elem + num_cols - 1), dtype=dtype, device=device)
+    k[:remainder] = 1.0 / math.sqrt(first_elem * first_elem + num_cols)
+    diag = torch.diag(k)
+    first = torch.diag(k * first_elem)
+    return torch.cat((first, diag.repeat(1, num_cols + 1)), 1)[:, :dim].contiguous()
+
+
+class FactorBatch:
+    """State of ``n`` same-shaped Fisher factors acting on one axis of ``n`` same-shaped tensors."""
+
+    def __init__(self, n: int, N: int, D: int, alpha: float, rank: int, update_period: int, eta: float,
+                 dtype, device):
+        assert D > 1
+        if rank >= 0:
+            assert 0 < rank < D
+        else:
+            rank = default_rank(D)
+        self.n, self.N, self.D, self.R = n, N, D, rank
+        self.alpha, self.update_period, self.eta = float(alpha), int(update_period), float(eta)
+        self.t = 0
+        E_tii = 1.0 / (2.0 + (D + rank) * self.alpha / D)
+        W0 = math.sqrt(E_tii) * orthonormal_special(rank, D, dtype, device)
+        self.W = W0.unsqueeze(0).repeat(n, 1, 1).contiguous()
+        self.d = torch.full((n, rank), EPSILON, dtype=dtype, device=device)
+        self.rho = torch.full((n,), EPSILON, dtype=dtype, device=device)
+
+    # -- tensors that make up the checkpointable state
+    def tensors(self) -> Dict[str, torch.Tensor]:
+        return {"W": self.W, "d": self.d, "rho": self.rho}
+
+    def updating(self) -> bool:
+        return self.t < NUM_INITIAL_ITERS or self.t % self.update_period == 0
+
+
+def fisher_update_torch(fb: FactorBatch, J, K, L, trXXt):
+    """One refresh of (W, d, rho) from the statistics J=HᵀX, K=JJᵀ, L — pure torch, batched,
+    sync-free.  Mirrors ngd_optimizer.py:225-324; also the oracle for ``csrc/ngd_eig.cu``."""
+    n, N, D, R = fb.n, fb.N, fb.D, fb.R
+    alpha, eta = fb.alpha, fb.eta
+    W, d, rho = fb.W, fb.d, fb.rho
+    d_sum = d.sum(1)
+    beta = rho * (1.0 + alpha) + alpha * d_sum / D
+    e = 1.0 / (beta[:, None] / d + 1.0)
+    inv_sqrt_e = 1.0 / torch.sqrt(e)
+    z_scale = torch.diagonal(K, dim1=1, dim2=2).sum(1).clamp_min(1.0)
+    dpr = d + rho[:, None]
+    eN = eta / N
+    c1 = (eN * eN) / z_scale
+    c2 = (eN * (1.0 - eta)) / z_scale
+    c3 = ((1.0 - eta) ** 2) / z_scale
+    outer0 = inv_sqrt_e[:, :, None] * inv_sqrt_e[:, None, :]
+    op1 = inv_sqrt_e[:, :, None] * (inv_sqrt_e * dpr)[:, None, :]
+    Z = K * outer0 * c1[:, None, None] + L * (op1 + op1.transpose(1, 2)) * c2[:, None, None]
+    Z = Z + torch.diag_embed(c3[:, None] * dpr * dpr)
+    Z = 0.5 * (Z + Z.transpose(1, 2))
+    c, U = torch.linalg.eigh(Z)
+    c = c.flip(1)
+    U = U.flip(2)
+    # the reference builds this floor as a default-dtype (fp32) tensor (ngd_optimizer.py:278);
+    # rounding it the same way keeps fp64 trajectories bit-comparable and is a no-op in fp32
+    c_floor = ((rho * (1.0 - eta)) ** 2 / z_scale).float().to(c.dtype)
+    c = torch.maximum(c, c_floor[:, None])
+    sqrt_c = c.sqrt() * z_scale.sqrt()[:, None]
+    inv_sqrt_c = 1.0 / sqrt_c
+    rho1 = (1.0 / (D - R)) * (eN * trXXt + (1.0 - eta) * (D * rho + d_sum) - sqrt_c.sum(1))
+    floor_val = torch.clamp_min(DELTA * sqrt_c.max(1).values, EPSILON)
+    d1 = torch.maximum(sqrt_c - rho1[:, None], floor_val[:, None])
+    rho1 = torch.maximum(rho1, floor_val)
+    beta1 = rho1 * (1.0 + alpha) + alpha * d1.sum(1) / D
+    e1 = 1.0 / (beta1[:, None] / d1 + 1.0)
+    sqrt_e1 = torch.sqrt(e1)
+    w_coeff = ((1.0 - eta) / eN) * dpr
+    left = eN * sqrt_e1 * inv_sqrt_c
+    A = U.transpose(1, 2) * (left[:, :, None] * inv_sqrt_e[:, None, :])
+    return A, w_coeff, d1, rho1
+
+
+def _fisher_update(fb: FactorBatch, J, K, L, trXXt):
+    if K.is_cuda:
+        from .. import ops
+        if ops.use_native(K):
+            return ops._cu().ngd_eig_update(fb, K, L, trXXt)
+    return fisher_update_torch(fb, J, K, L, trXXt)
+
+
+def _refresh(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor, trXXt: torch.Tensor):
+    """Update (W, d, rho) in place from the current gradient matrix and H (= X Wᵀ or its
+    transpose)."""
+    W = fb.W
+    if left:   # Xm: [n, D, N], H: [n, R, N]
+        J = torch.bmm(H, Xm.transpose(1, 2))
+        L = torch.bmm(J, W.transpose(1, 2)) if fb.N > fb.D else torch.bmm(H, H.transpose(1, 2))
+    else:      # Xm: [n, N, D], H: [n, N, R]
+        J = torch.bmm(H.transpose(1, 2), Xm)
+        L = torch.bmm(J, W.transpose(1, 2)) if fb.N > fb.D else torch.bmm(H.transpose(1, 2), H)
+    K = torch.bmm(J, J.transpose(1, 2))
+    A, w_coeff, d1, rho1 = _fisher_update(fb, J, K, L, trXXt)
+    B = torch.addcmul(J, w_coeff.unsqueeze(2), W)
+    W1 = torch.bmm(A, B)
+    # device-side guard: a factor whose refresh produced non-finite numbers keeps its old state
+    ok = torch.isfinite(W1).flatten(1).all(1) & torch.isfinite(d1).all(1) & torch.isfinite(rho1)
+    # in-place so that a captured CUDA graph keeps reading / writing the same state buffers
+    fb.W.copy_(torch.where(ok[:, None, None], W1, W))
+    fb.d.copy_(torch.where(ok[:, None], d1, fb.d))
+    fb.rho.copy_(torch.where(ok, rho1, fb.rho))
+
+
+def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool) -> torch.Tensor:
+    """Apply (and, on refresh steps, update) the inverse-Fisher factor.
+
+    ``Xm`` is ``[n, N, D]`` (``left=False``) or its transpose ``[n, D, N]`` (``left=True``, used
+    when the preconditioned axis is the tensor's first axis so no transpose copy is needed).
+    Returns the preconditioned matrix in the same layout with its Frobenius norm restored
+    (ngd_optimizer.py:138-168)."""
+    p0 = (Xm * Xm).sum((1, 2))
+
+    def project():
+        W = fb.W
+        if left:
+            H = torch.bmm(W, Xm)
+            return H, torch.baddbmm(Xm, W.transpose(1, 2), H, alpha=-1.0)
+        H = torch.bmm(Xm, W.transpose(1, 2))
+        return H, torch.baddbmm(Xm, H, W, alpha=-1.0)
+
+    if fb.t == 0:
+        # warm start: 3 refreshes on the same gradient (ngd_optimizer.py:356-376)
+        for _ in range(3):
+            H, _ = project()
+            _refresh(fb, Xm, left, H, p0)
+    updating = fb.updating()
+    fb.t += 1
+    H, Xhat = project()
+    if updating:
+        _refresh(fb, Xm, left, H, p0)
+    p1 = (Xhat * Xhat).sum((1, 2))
+    scale = torch.sqrt(p0 / (p1 + 1.0e-30))
+    out = Xhat * scale[:, None, None]
+    return torch.where(torch.isnan(p1)[:, None, None], Xm, out)
+
+
+class _ShapeGroup:
+    """Same-shaped parameters of one param group, processed as one batched tensor."""
+
+    def __init__(self, params: List[torch.Tensor]):
+        self.params = params
+        self.shape = tuple(params[0].shape)
+        self.factors: Dict[int, FactorBatch] = {}
+        self.momentum: Optional[torch.Tensor] = None
+        self._flat = None  # (grad_view, param_view) when backed by FlatParameters
+
+    def bind_flat(self):
+        """Use zero-copy ``[n, *shape]`` views when the params sit contiguously in a flat buffer."""
+        g0 = getattr(self.params[0], "_fdt_flat", None)
+        if g0 is None:
+            return
+        flat, first = g0
+        idxs = []
+        for p in self.params:
+            f = getattr(p, "_fdt_flat", None)
+            if f is None or f[0] is not flat:
+                return
+            idxs.append(f[1])
+        views = flat.stacked_views(idxs, self.shape)
+        if views is not None:
+            self._flat = views
+
+    def grads(self) -> torch.Tensor:
+        if self._flat is not None:
+            return self._flat[0]
+        return torch.stack([p.grad for p in self.params])
+
+    def values(self) -> torch.Tensor:
+        if self._flat is not None:
+            return self._flat[1]
+        return torch.stack([p.data for p in self.params])
+
+    def write_back(self, new_values: torch.Tensor):
+        if self._flat is not None:
+            return  # updated in place through the view
+        for p, v in zip(self.params, new_values.unbind(0)):
+            p.data.copy_(v)
+
+
+class NGD(Optimizer):
+    """Drop-in for the reference's ``NGD(params, lr, momentum, dampening, weight_decay, nesterov,
+    ngd, alpha, rank, update_period, eta)`` (ngd_optimizer.py:423-450)."""
+
+    def __init__(self, params, lr=1e-4, momentum=0, dampening=0, weight_decay=0, nesterov=False,
+                 ngd=True, alpha=4, rank=-1, update_period=4, eta=0.1):
+        if lr < 0.0:
+            raise ValueError(f"Invalid learning rate: {lr}")
+        if momentum < 0.0:
+            raise ValueError(f"Invalid momentum value: {momentum}")
+        if weight_decay < 0.0:
+            raise ValueError(f"Invalid weight_decay value: {weight_decay}")
+        if nesterov and (momentum <= 0 or dampening != 0):
+            raise ValueError("Nesterov momentum requires a momentum and zero dampening")
+        defaults = dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
+                        nesterov=nesterov, ngd=ngd, alpha=alpha, rank=rank,
+                        update_period=update_period, eta=eta)
+        super().__init__(params, defaults)
+        self._groups: Dict[int, List[_ShapeGroup]] = {}
+        self._lr_tensors: Dict[int, torch.Tensor] = {}
+        self.capturable = False
+
+    # ------------------------------------------------------------------ grouping
+    def _shape_groups(self, gi: int, group) -> List[_ShapeGroup]:
+        if gi in self._groups:
+            return self._groups[gi]
+        buckets: "OrderedDict[Tuple, List[torch.Tensor]]" = OrderedDict()
+        for p in group["params"]:
+            if p.grad is None:
+                continue
+            key = (tuple(p.shape), p.dtype, p.device)
+            buckets.setdefault(key, []).append(p)
+        sgs = [_ShapeGroup(ps) for ps in buckets.values()]
+        for sg in sgs:
+            sg.bind_flat()
+        self._groups[gi] = sgs
+        return sgs
+
+    # ------------------------------------------------------------------ CUDA-graph support
+    def _factor_batches(self):
+        for sgs in self._groups.values():
+            for sg in sgs:
+                yield from sg.factors.values()
+
+    def next_step_kind(self) -> str:
+        """'warm' (first call: factors are created and warm-started), 'update' (Fisher refresh)
+        or 'plain'.  The kind decides which kernels a step launches, i.e. which captured graph
+        can replay it."""
+        fbs = list(self._factor_batches())
+        if not fbs or any(fb.t == 0 for fb in fbs):
+            return "warm"
+        kinds = {fb.updating() for fb in fbs}
+        if any(not g["ngd"] for g in self.param_groups) and not kinds:
+            return "plain"
+        return "update" if True in kinds else "plain"
+
+    def advance_without_python(self):
+        """Account for a step that ran as a CUDA-graph replay (no Python executed)."""
+        for fb in self._factor_batches():
+            fb.t += 1
+
+    def set_capturable(self, flag: bool = True):
+        """Keep the learning rate in a device scalar so a captured CUDA graph sees LR changes."""
+        self.capturable = flag
+
+    def _lr(self, gi: int, group, device):
+        if not self.capturable:
+            return group["lr"]
+        t = self._lr_tensors.get(gi)
+        if t is None or t.device != device:
+            t = torch.zeros((), dtype=torch.float32, device=device)
+            self._lr_tensors[gi] = t
+        return t
+
+    def sync_lr(self):
+        """Copy each group's python ``lr`` into its device scalar (call outside graph replay)."""
+        for gi, group in enumerate(self.param_groups):
+            t = self._lr_tensors.get(gi)
+            if t is not None:
+                t.fill_(float(group["lr"]))
+
+    # ------------------------------------------------------------------ step
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for gi, group in enumerate(self.param_groups):
+            wd, mom, damp = group["weight_decay"], group["momentum"], group["dampening"]
+            for sg in self._shape_groups(gi, group):
+                G = sg.grads()
+                P = sg.values()
+                n = G.shape[0]
+                if wd != 0:
+                    G.add_(P, alpha=wd)
+                d_p = G
+                if group["ngd"]:
+                    nd = len(sg.shape)
+                    for axis in range(nd):
+                        D = sg.shape[axis]
+                        if D == 1:
+                            continue
+                        numel = d_p[0].numel()
+                        N = numel // D
+                        fb = sg.factors.get(axis)
+                        if fb is None:
+                            fb = sg.factors[axis] = FactorBatch(
+                                n, N, D, group["alpha"], group["rank"], group["update_period"],
+                                group["eta"], d_p.dtype, d_p.device)
+                        if axis == nd - 1:
+                            out = precondition(fb, d_p.reshape(n, N, D), left=False)
+                            d_p = out.reshape(n, *sg.shape)
+                        elif axis == 0:
+                            out = precondition(fb, d_p.reshape(n, D, N), left=True)
+                            d_p = out.reshape(n, *sg.shape)
+                        else:
+                            Xm = d_p.movedim(axis + 1, -1)
+                            mid_shape = Xm.shape
+                            out = precondition(fb, Xm.reshape(n, N, D), left=False)
+                            d_p = out.reshape(mid_shape).movedim(-1, axis + 1)
+                if mom != 0:
+                    if sg.momentum is None:
+                        sg.momentum = d_p.clone(memory_format=torch.contiguous_format)
+                    else:
+                        sg.momentum.mul_(mom).add_(d_p, alpha=1.0 - damp)
+                    d_p = d_p.add(sg.momentum, alpha=mom) if group["nesterov"] else sg.momentum
+                lr = self._lr(gi, group, P.device)
+                if torch.is_tensor(lr):
+                    P.sub_(d_p * lr)
+                else:
+                    P.add_(d_p, alpha=-lr)
+                sg.write_back(P)
+        return loss
+
+    # ------------------------------------------------------------------ (de)serialisation
+    def state_dict(self):
+        """Tensor-only state: per param group, per shape group: momentum + per-axis W/d/rho/t."""
+        groups = []
+        for gi, group in enumerate(self.param_groups):
+            entry = {k: v for k, v in group.items() if k != "params"}
+            sgs = []
+            for sg in self._groups.get(gi, []):
+                sgs.append({
+                    "shape": sg.shape, "n": len(sg.params),
+                    "momentum": None if sg.momentum is None else sg.momentum.detach().clone(),
+                    "factors": {axis: {"t": fb.t, **{k: v.detach().clone() for k, v in fb.tensors().items()}}
+                                for axis, fb in sg.factors.items()},
+                })
+            entry["shape_groups"] = sgs
+            groups.append(entry)
+        return {"format": "fdt-ngd-v1", "groups": groups}
+
+    def load_state_dict(self, state):
+        if state.get("format") != "fdt-ngd-v1":
+            raise ValueError("not an fdt NGD state dict")
+        for gi, (group, entry) in enumerate(zip(self.param_groups, state["groups"])):
+            for k, v in entry.items():
+                if k != "shape_groups":
+                    group[k] = v
+            # shape groups need gradients to exist to be discovered; build them from params
+            for p in group["params"]:
+                if p.grad is None:
+                    p.grad = torch.zeros_like(p)
+            sgs = self._shape_groups(gi, group)
+            assert len(sgs) == len(entry["shape_groups"]), "parameter set changed"
+            for sg, s in zip(sgs, entry["shape_groups"]):
+                assert tuple(s["shape"]) == sg.shape and s["n"] == len(sg.params)
+                dev, dt = sg.params[0].device, sg.params[0].dtype
+                sg.momentum = None if s["momentum"] is None else s["momentum"].to(dev, dt)
+                sg.factors = {}
+                for axis, f in s["factors"].items():
+                    D = sg.shape[axis]
+                    N = sg.params[0].numel() // D
+                    fb = FactorBatch(len(sg.params), N, D, group["alpha"], group["rank"],
+                                     group["update_period"], group["eta"], dt, dev)
+                    fb.t = int(f["t"])
+                    fb.W, fb.d, fb.rho = f["W"].to(dev, dt), f["d"].to(dev, dt), f["rho"].to(dev, dt)
+                    sg.factors[int(axis)] = fb

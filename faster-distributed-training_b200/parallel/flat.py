@@ -1,0 +1,151 @@
+"""Flat parameter / gradient storage.
+
+All trainable tensors of a model are re-homed into ONE fp32 parameter buffer and ONE fp32
+gradient buffer (``p.data`` / ``p.grad`` become views).  This is the B200-first replacement for
+the reference's per-tensor world (69 / 105 separate tensors, each with its own all-reduce bucket
+slot, ``clip_grad_norm_`` and optimizer launches — ``resnet50_test.py:499-502,546``,
+``ngd_optimizer.py:462-506``):
+
+* the DDP all-reduce, the FSDP reduce-scatter / all-gather, gradient clipping, zeroing and the
+  bf16 weight-shadow cast each run over one contiguous range (one kernel, one collective);
+* tensors with the **same shape are laid out adjacently**, so the NGD optimizer sees each shape
+  group as a zero-copy ``[n, *shape]`` batch (see ``fdt/optim/ngd.py``);
+* the gradient buffer can be placed in NVLink symmetric memory (``allocator``) so the fused
+  all-reduce kernels in ``csrc/comm.cu`` can read peers' gradients directly;
+* shape groups can be assigned to owner ranks (``owners``) and padded so every rank's region has
+  the same length — the layout the FSDP engine shards on.
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+ALIGN = 128  # elements; every shape group (and rank region) starts on a 512-byte boundary
+
+
+def _round_up(x: int, a: int) -> int:
+    return (x + a - 1) // a * a
+
+
+class ShapeGroupLayout:
+    def __init__(self, shape, params, offset, owner=0):
+        self.shape = tuple(shape)
+        self.params = params
+        self.numel = params[0].numel()
+        self.offset = offset          # element offset of the first member in the flat buffers
+        self.owner = owner            # FSDP owner rank (0 when unsharded)
+
+    @property
+    def n(self):
+        return len(self.params)
+
+    @property
+    def size(self):
+        return self.n * self.numel
+
+
+class FlatParameters:
+    def __init__(self, params: Sequence[torch.nn.Parameter], device=None,
+                 allocator: Optional[Callable[[int], torch.Tensor]] = None,
+                 world_size: int = 1, shard: bool = False):
+        params = [p for p in params if p.requires_grad]
+        assert params, "no trainable parameters"
+        device = device or params[0].device
+        self.device = torch.device(device)
+        self.world_size = world_size
+        self.sharded = shard and world_size > 1
+
+        buckets: "OrderedDict[Tuple, List[torch.nn.Parameter]]" = OrderedDict()
+        for p in params:
+            buckets.setdefault(tuple(p.shape), []).append(p)
+
+        # owner assignment: greedy balance of element counts (largest groups first)
+        owners: Dict[Tuple, int] = {s: 0 for s in buckets}
+        if self.sharded:
+            load = [0] * world_size
+            for s, ps in sorted(buckets.items(), key=lambda kv: -len(kv[1]) * kv[1][0].numel()):
+                r = min(range(world_size), key=lambda i: load[i])
+                owners[s] = r
+                load[r] += _round_up(len(ps) * ps[0].numel(), ALIGN)
+
+        self.groups: List[ShapeGroupLayout] = []
+        self.region: List[Tuple[int, int]] = []   # per rank (start, end) element range
+        off = 0
+        if self.sharded:
+            sizes = []
+            for r in range(world_size):
+                sz = sum(_round_up(len(ps) * ps[0].numel(), ALIGN) for s, ps in buckets.items() if owners[s] == r)
+                sizes.append(sz)
+            region_size = _round_up(max(sizes), ALIGN)
+            for r in range(world_size):
+                off = r * region_size
+                self.region.append((off, off + region_size))
+                for s, ps in buckets.items():
+                    if owners[s] != r:
+                        continue
+                    g = ShapeGroupLayout(s, ps, off, r)
+                    self.groups.append(g)
+                    off += _round_up(g.size, ALIGN)
+            total = world_size * region_size
+        else:
+            for s, ps in buckets.items():
+                g = ShapeGroupLayout(s, ps, off, 0)
+                self.groups.append(g)
+                off += _round_up(g.size, ALIGN)
+            total = _round_up(off, ALIGN * max(world_size, 1))
+            per = total // max(world_size, 1)
+            self.region = [(r * per, (r + 1) * per) for r in range(max(world_size, 1))]
+        self.total = total
+
+        self.param_flat = torch.zeros(total, dtype=torch.float32, device=self.device)
+        if allocator is not None:
+            self.grad_flat = allocator(total)
+            assert self.grad_flat.numel() == total and self.grad_flat.dtype == torch.float32
+            self.grad_flat.zero_()
+        else:
+            self.grad_flat = torch.zeros(total, dtype=torch.float32, device=self.device)
+
+        self._index: Dict[int, Tuple[ShapeGroupLayout, int]] = {}
+        self.params: List[torch.nn.Parameter] = []
+        with torch.no_grad():
+            for g in self.groups:
+                for i, p in enumerate(g.params):
+                    lo = g.offset + i * g.numel
+                    pv = self.param_flat[lo:lo + g.numel].view(g.shape)
+                    pv.copy_(p.data.to(self.device, torch.float32))
+                    p.data = pv
+                    p.grad = self.grad_flat[lo:lo + g.numel].view(g.shape)
+                    idx = len(self.params)
+                    p._fdt_flat = (self, idx)
+                    self._index[idx] = (g, i)
+                    self.params.append(p)
+
+    # -- zero-copy batched views for the optimizer
+    def stacked_views(self, idxs: List[int], shape) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
+        g0, i0 = self._index[idxs[0]]
+        for k, idx in enumerate(idxs):
+            g, i = self._index[idx]
+            if g is not g0 or i != i0 + k:
+                return None
+        lo = g0.offset + i0 * g0.numel
+        hi = lo + len(idxs) * g0.numel
+        n = len(idxs)
+        return (self.grad_flat[lo:hi].view(n, *shape), self.param_flat[lo:hi].view(n, *shape))
+
+    def rebind_grads(self):
+        """Re-point ``p.grad`` at the flat buffer (after someone set grads to ``None``)."""
+        for idx, p in enumerate(self.params):
+            g, i = self._index[idx]
+            lo = g.offset + i * g.numel
+            p.grad = self.grad_flat[lo:lo + g.numel].view(g.shape)
+
+    def zero_grad(self):
+        self.grad_flat.zero_()
+
+    def owned_params(self, rank: int) -> List[torch.nn.Parameter]:
+        return [p for g in self.groups if g.owner == rank for p in g.params]
+
+    def local_region(self, rank: int) -> Tuple[int, int]:
+        return self.region[rank]

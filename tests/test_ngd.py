@@ -1,0 +1,163 @@
+"""NGD optimizer: trajectory parity with the reference's ``ngd_optimizer.py`` on CPU, plus
+state-dict round trip and invariants."""
+import copy
+
+import pytest
+import torch
+
+from fdt.optim.ngd import NGD, FactorBatch, fisher_update_torch, orthonormal_special, precondition
+
+from _refmods import load
+
+
+def _make_params(seed, shapes, dtype=torch.float64):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.nn.Parameter(torch.randn(*s, generator=g, dtype=dtype) * 0.1) for s in shapes]
+
+
+# Shapes whose every factor sees N >= R rows.  Rank-deficient factors (1-D tensors, N = 1) are
+# excluded from the strict comparison: there the reference's own update amplifies eigensolver
+# rounding noise into O(1e-3) differences of W's null-space rows, so no two implementations
+# (or BLAS builds) agree; they are covered by test_rank_deficient_factors_are_sane instead.
+SHAPES = [(16, 8, 3, 3), (16, 8, 3, 3), (12, 16, 1, 1), (10, 12), (7, 5)]
+
+
+@pytest.mark.parametrize("momentum,wd", [(0.9, 1e-4), (0.0, 0.0)])
+def test_trajectory_matches_reference(momentum, wd):
+    ref = load("ngd_optimizer")
+    p_ref = _make_params(0, SHAPES)
+    p_new = [torch.nn.Parameter(p.detach().clone()) for p in p_ref]
+    o_ref = ref.NGD(p_ref, lr=0.05, momentum=momentum, weight_decay=wd)
+    o_new = NGD(p_new, lr=0.05, momentum=momentum, weight_decay=wd)
+    g = torch.Generator().manual_seed(1)
+    for step in range(14):  # crosses the t<10 / t%4 boundary
+        for a, b in zip(p_ref, p_new):
+            grad = torch.randn(a.shape, generator=g, dtype=a.dtype) * (1.0 + 0.1 * step)
+            a.grad = grad.clone()
+            b.grad = grad.clone()
+        o_ref.step()
+        o_new.step()
+        for i, (a, b) in enumerate(zip(p_ref, p_new)):
+            assert torch.allclose(a, b, rtol=1e-6, atol=1e-9), f"step {step} param {i} diverged: {(a-b).abs().max()}"
+    # factor state: compare the sign-invariant WᵀW, and d, rho
+    sg = {s.shape: s for s in o_new._groups[0]}
+    for i, p in enumerate(p_ref):
+        st = o_ref.state[p]
+        for axis, obj in st["ngd_dict"].items():
+            if obj.dim == 1:
+                continue
+            group = sg[tuple(p.shape)]
+            idx = [id(q) for q in group.params].index(id(p_new[i]))
+            fb = group.factors[axis]
+            assert fb.t == obj.t
+            Wn, Wr = fb.W[idx], obj.W_t
+            assert torch.allclose(Wn.T @ Wn, Wr.T @ Wr, rtol=1e-5, atol=1e-8)
+            assert torch.allclose(fb.d[idx], obj.d_t_cpu, rtol=1e-6, atol=1e-12)
+            assert abs(float(fb.rho[idx]) - float(obj.rho_t)) <= 1e-6 * abs(float(obj.rho_t)) + 1e-14
+
+
+def test_rank_deficient_factors_are_sane():
+    params = _make_params(7, [(12,), (1, 12), (12,)], torch.float32)
+    opt = NGD(params, lr=0.05, momentum=0.9)
+    g = torch.Generator().manual_seed(8)
+    for _ in range(12):
+        for p in params:
+            p.grad = torch.randn(p.shape, generator=g)
+        before = [p.detach().clone() for p in params]
+        opt.step()
+        for p, b in zip(params, before):
+            assert torch.isfinite(p).all() and not torch.equal(p, b)
+
+
+def test_fp32_trajectory_close():
+    ref = load("ngd_optimizer")
+    shapes = [(32, 16, 3, 3), (24, 32)]
+    p_ref = _make_params(3, shapes, torch.float32)
+    p_new = [torch.nn.Parameter(p.detach().clone()) for p in p_ref]
+    o_ref = ref.NGD(p_ref, lr=0.01, momentum=0.9, weight_decay=1e-4)
+    o_new = NGD(p_new, lr=0.01, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(4)
+    for _ in range(6):
+        for a, b in zip(p_ref, p_new):
+            grad = torch.randn(a.shape, generator=g)
+            a.grad, b.grad = grad.clone(), grad.clone()
+        o_ref.step()
+        o_new.step()
+    for a, b in zip(p_ref, p_new):
+        assert torch.allclose(a, b, rtol=2e-3, atol=2e-4)
+
+
+def test_orthonormal_special_matches_reference():
+    ref = load("ngd_optimizer")
+    p = torch.zeros(30, 7)
+    obj = ref.OnlineNaturalGradient(p, 0)
+    ours = orthonormal_special(obj.rank, obj.dim, torch.float32, "cpu")
+    assert torch.equal(ours, obj._create_orthonormal_special())
+
+
+def test_norm_preserved_and_invariant():
+    torch.manual_seed(0)
+    fb = FactorBatch(3, 40, 24, 4.0, -1, 4, 0.1, torch.float64, "cpu")
+    X = torch.randn(3, 40, 24, dtype=torch.float64)
+    for _ in range(12):
+        out = precondition(fb, X, left=False)
+        assert torch.allclose(out.flatten(1).norm(dim=1), X.flatten(1).norm(dim=1), rtol=1e-9)
+    # W E^-1 Wᵀ ≈ I  (reference _self_test, ngd_optimizer.py:330-345)
+    beta = fb.rho * (1 + fb.alpha) + fb.alpha * fb.d.sum(1) / fb.D
+    e = 1.0 / (beta[:, None] / fb.d + 1.0)
+    inv_sqrt_e = e.rsqrt()
+    M = torch.bmm(fb.W, fb.W.transpose(1, 2)) * (inv_sqrt_e[:, :, None] * inv_sqrt_e[:, None, :])
+    assert (M - torch.eye(fb.R, dtype=M.dtype)).abs().max() < 0.1
+    assert (fb.rho >= 1e-10).all() and (fb.d.min(1).values >= 1e-10).all()
+
+
+def test_left_form_equals_right_form():
+    torch.manual_seed(1)
+    a = FactorBatch(2, 30, 10, 4.0, -1, 4, 0.1, torch.float64, "cpu")
+    b = FactorBatch(2, 30, 10, 4.0, -1, 4, 0.1, torch.float64, "cpu")
+    for _ in range(5):
+        X = torch.randn(2, 30, 10, dtype=torch.float64)
+        o1 = precondition(a, X, left=False)
+        o2 = precondition(b, X.transpose(1, 2).contiguous(), left=True).transpose(1, 2)
+        assert torch.allclose(o1, o2, rtol=1e-8, atol=1e-10)
+
+
+def test_state_dict_roundtrip():
+    params = _make_params(5, [(8, 6), (8, 6), (4, 3, 3, 3)], torch.float32)
+    opt = NGD(params, lr=0.1, momentum=0.9)
+    g = torch.Generator().manual_seed(2)
+
+    def step(o, ps):
+        for p in ps:
+            p.grad = torch.randn(p.shape, generator=g)
+        o.step()
+
+    for _ in range(3):
+        step(opt, params)
+    sd = copy.deepcopy(opt.state_dict())
+    assert sd["format"] == "fdt-ngd-v1"
+    params2 = [torch.nn.Parameter(p.detach().clone()) for p in params]
+    opt2 = NGD(params2, lr=0.1, momentum=0.9)
+    opt2.load_state_dict(sd)
+    g2 = torch.Generator().manual_seed(9)
+    g3 = torch.Generator().manual_seed(9)
+    for p, q in zip(params, params2):
+        p.grad = torch.randn(p.shape, generator=g2)
+        q.grad = torch.randn(q.shape, generator=g3)
+    opt.step()
+    opt2.step()
+    for p, q in zip(params, params2):
+        assert torch.allclose(p, q, rtol=1e-5, atol=1e-7)
+
+
+def test_plain_sgd_mode_and_nesterov():
+    p = torch.nn.Parameter(torch.ones(4, 3))
+    q = torch.nn.Parameter(torch.ones(4, 3))
+    o1 = NGD([p], lr=0.1, momentum=0.9, nesterov=True, ngd=False)
+    o2 = torch.optim.SGD([q], lr=0.1, momentum=0.9, nesterov=True)
+    for i in range(4):
+        p.grad = torch.full_like(p, 0.5 + i)
+        q.grad = torch.full_like(q, 0.5 + i)
+        o1.step()
+        o2.step()
+    assert torch.allclose(p, q)
