@@ -1,0 +1,230 @@
+// Channel-wise (batch-norm family) kernels on NHWC bf16 activations viewed as [P, C].
+//
+// Parity: the normalisation maths of the reference's FusedConvBN2DFunction (resnet.py:75-100,
+// batch_norm_backward :37-69) and of nn.BatchNorm2d for its 7 "real" BN layers — there ~5 (fwd)
+// and ~15 (bwd) ATen launches per layer over NCHW tensors.  Here each
+// direction is two bandwidth-bound passes plus a C-sized finalise:
+//   fwd : chan_reduce2 (Σy, Σy²)  → bn_finalize_fwd → chan_affine_act  (normalise [+res] + act)
+//   bwd : chan_reduce2 (g = gout·act'(out), Σg, Σg·y) → bn_finalize_bwd → chan_affine_act (A·g + B·y + C)
+// (the forward reduction disappears once the conv epilogue emits the sums).
+#include "common.cuh"
+using namespace fdt;
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// Σ_p a[p,c]  and  Σ_p a[p,c]·b[p,c]   where a = g (optionally g = gout·act'(out), optionally stored)
+// grid.x blocks each own a slab of rows; thread → fixed 8-channel vector, loops over rows.
+template <bool kMask>
+__global__ void __launch_bounds__(kThreads)
+chan_reduce2_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                    const __nv_bfloat16* __restrict__ out_act, __nv_bfloat16* __restrict__ g_store,
+                    float* __restrict__ sums /*[2,C]*/, int64_t P, int C, int act, int rows_per_block) {
+    const int vecC = C >> 3;
+    const int tpr = vecC < kThreads ? vecC : kThreads;      // threads per row
+    const int lanes = kThreads / tpr;                       // rows processed concurrently
+    const int cv = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = min(P, r0 + rows_per_block);
+    __shared__ float red[2][kThreads][8 + 1];
+    for (int cbase = cv; cbase < vecC; cbase += tpr) {
+        float s1[8], s2[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s1[i] = s2[i] = 0.f;
+        if (rl < lanes) {
+            for (int64_t r = r0 + rl; r < r1; r += lanes) {
+                const int64_t off = r * C + (int64_t)cbase * 8;
+                float fa[8], fb[8];
+                unpack8(ld8(a + off), fa);
+                unpack8(ld8(b + off), fb);
+                if (kMask) {
+                    float fo[8];
+                    unpack8(ld8(out_act + off), fo);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) fa[i] *= act_bwd_from_out(fo[i], act);
+                    if (g_store) {
+                        bf16x8 pk = pack8(fa);
+                        st8(g_store + off, pk);
+                        unpack8(pk, fa);          // reduce exactly what later passes will read
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s1[i] += fa[i]; s2[i] += fa[i] * fb[i]; }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { red[0][threadIdx.x][i] = s1[i]; red[1][threadIdx.x][i] = s2[i]; }
+        __syncthreads();
+        if (rl == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float t1 = 0.f, t2 = 0.f;
+                for (int l = 0; l < lanes; ++l) { t1 += red[0][l * tpr + cv][i]; t2 += red[1][l * tpr + cv][i]; }
+                atomicAdd(&sums[cbase * 8 + i], t1);
+                atomicAdd(&sums[C + cbase * 8 + i], t2);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// out = act(A[c]·x1 + B[c]·x2 + Cc[c] + res);  x2 / res optional.
+__global__ void __launch_bounds__(kThreads)
+chan_affine_act_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
+                       const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
+                       const float* __restrict__ coef /*[3,C]: A,B,Cc*/, int64_t P, int C, int act, int rows_per_block) {
+    const int vecC = C >> 3;
+    const int tpr = vecC < kThreads ? vecC : kThreads;
+    const int lanes = kThreads / tpr;
+    const int cv = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    if (rl >= lanes) return;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = min(P, r0 + rows_per_block);
+    for (int cbase = cv; cbase < vecC; cbase += tpr) {
+        float A[8], B[8], Cc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            A[i] = coef[cbase * 8 + i];
+            B[i] = x2 ? coef[C + cbase * 8 + i] : 0.f;
+            Cc[i] = coef[2 * C + cbase * 8 + i];
+        }
+        for (int64_t r = r0 + rl; r < r1; r += lanes) {
+            const int64_t off = r * C + (int64_t)cbase * 8;
+            float f1[8], o[8];
+            unpack8(ld8(x1 + off), f1);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = fmaf(A[i], f1[i], Cc[i]);
+            if (x2) {
+                float f2[8];
+                unpack8(ld8(x2 + off), f2);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaf(B[i], f2[i], o[i]);
+            }
+            if (res) {
+                float fr[8];
+                unpack8(ld8(res + off), fr);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] += fr[i];
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = act_fwd(o[i], act);
+            st8(out + off, pack8(o));
+        }
+    }
+}
+
+// form 0: reference FusedConvBN  (unbiased var, eps added to the std, no affine)      resnet.py:85-100
+// form 1: nn.BatchNorm2d training (biased var, eps inside sqrt, affine, running-stat update)
+// form 2: nn.BatchNorm2d eval     (running stats)
+// ctx[5,C] = mean, inv (1/denominator, no gamma), scale (A of the fwd affine), k (bwd coefficient), gamma
+__global__ void bn_finalize_fwd_kernel(const float* __restrict__ sums, float* __restrict__ coef, float* __restrict__ ctx,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       float* __restrict__ running_mean, float* __restrict__ running_var,
+                                       int C, float N, float eps, float momentum, int form) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float mean, inv, k, g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+    if (form == 2) {
+        mean = running_mean[c];
+        inv = rsqrtf(running_var[c] + eps);
+        k = 0.f;
+    } else {
+        float s = sums[c], ss = sums[C + c];
+        mean = s / N;
+        float m2 = fmaxf(ss - s * mean, 0.f);
+        if (form == 0) {
+            float sd = sqrtf(m2 / (N - 1.f));
+            inv = 1.f / (sd + eps);
+            k = (sd + eps) / ((N - 1.f) * fmaxf(sd, 1e-20f));
+        } else {
+            float var_b = m2 / N;
+            inv = rsqrtf(var_b + eps);
+            k = 1.f / N;
+            if (running_mean) {
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / fmaxf(N - 1.f, 1.f));
+            }
+        }
+    }
+    float scale = g * inv;
+    coef[c] = scale; coef[C + c] = 0.f; coef[2 * C + c] = b - mean * scale;
+    ctx[c] = mean; ctx[C + c] = inv; ctx[2 * C + c] = scale; ctx[3 * C + c] = k; ctx[4 * C + c] = g;
+}
+
+// sums = (Σg, Σg·y) → dy = A·g + B·y + Cc ;  dgamma = Σg·ŷ, dbeta = Σg
+__global__ void bn_finalize_bwd_kernel(const float* __restrict__ sums, const float* __restrict__ ctx,
+                                       float* __restrict__ coef, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       int C, float N, int form) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float mean = ctx[c], inv = ctx[C + c], scale = ctx[2 * C + c], k = ctx[3 * C + c];
+    float sg = sums[c], sgy = sums[C + c];
+    float sgyh = inv * (sgy - mean * sg);          // Σ g·ŷ
+    if (dgamma) { dgamma[c] = sgyh; dbeta[c] = sg; }
+    if (form == 2) {                                 // eval: statistics are constants
+        coef[c] = scale; coef[C + c] = 0.f; coef[2 * C + c] = 0.f;
+        return;
+    }
+    float a = scale, b = sg / N, cc = k * sgyh;
+    coef[c] = a;
+    coef[C + c] = -a * cc * inv;
+    coef[2 * C + c] = -a * b + a * cc * inv * mean;
+}
+
+int pick_rows_per_block(int64_t P, int C, int* grid) {
+    const int vecC = C >> 3;
+    const int tpr = vecC < kThreads ? vecC : kThreads;
+    const int lanes = kThreads / tpr;
+    int64_t target_blocks = 148 * 8;
+    int64_t rpb = (P + target_blocks - 1) / target_blocks;
+    int64_t min_rows = (int64_t)lanes * 4;
+    if (rpb < min_rows) rpb = min_rows;
+    rpb = (rpb + lanes - 1) / lanes * lanes;
+    *grid = (int)((P + rpb - 1) / rpb);
+    return (int)rpb;
+}
+
+}  // namespace
+
+// sums[2,C] must be zero on entry (the wrapper memsets it on the same stream).
+FDT_API int fdt_chan_reduce2(const void* a, const void* b, const void* out_act, void* g_store, float* sums,
+                             int64_t P, int C, int act, cudaStream_t st) {
+    if (C % 8) return -1;
+    int grid; int rpb = pick_rows_per_block(P, C, &grid);
+    cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
+    if (out_act && act != ACT_NONE)
+        chan_reduce2_kernel<true><<<grid, kThreads, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
+            (const __nv_bfloat16*)out_act, (__nv_bfloat16*)g_store, sums, P, C, act, rpb);
+    else
+        chan_reduce2_kernel<false><<<grid, kThreads, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
+            nullptr, nullptr, sums, P, C, act, rpb);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res, void* out, const float* coef,
+                                int64_t P, int C, int act, cudaStream_t st) {
+    if (C % 8) return -1;
+    int grid; int rpb = pick_rows_per_block(P, C, &grid);
+    chan_affine_act_kernel<<<grid, kThreads, 0, st>>>((const __nv_bfloat16*)x1, (const __nv_bfloat16*)x2,
+        (const __nv_bfloat16*)res, (__nv_bfloat16*)out, coef, P, C, act, rpb);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_bn_finalize_fwd(const float* sums, float* coef, float* ctx, const float* gamma, const float* beta,
+                                float* running_mean, float* running_var, int C, float N, float eps, float momentum,
+                                int form, cudaStream_t st) {
+    bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(sums, coef, ctx, gamma, beta, running_mean, running_var,
+                                                          C, N, eps, momentum, form);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_bn_finalize_bwd(const float* sums, const float* ctx, float* coef, float* dgamma, float* dbeta,
+                                int C, float N, int form, cudaStream_t st) {
+    bn_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(sums, ctx, coef, dgamma, dbeta, C, N, form);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

@@ -1,0 +1,86 @@
+// Shared device helpers for the sm_100a kernels of faster-distributed-training_b200.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#define FDT_API extern "C" __attribute__((visibility("default")))
+
+#define FDT_CHECK_LAUNCH() do { cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) return (int)e__; } while (0)
+
+namespace fdt {
+
+enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_CELU = 2, ACT_GELU = 3, ACT_TANH = 4 };
+constexpr float kCeluAlpha = 0.075f;   // resnet.py:240
+
+__device__ __forceinline__ float act_fwd(float x, int act) {
+    switch (act) {
+        case ACT_RELU: return fmaxf(x, 0.f);
+        case ACT_CELU: return x > 0.f ? x : kCeluAlpha * (__expf(x * (1.f / kCeluAlpha)) - 1.f);
+        case ACT_GELU: return 0.5f * x * (1.f + erff(x * 0.70710678118654752f));
+        case ACT_TANH: return tanhf(x);
+        default: return x;
+    }
+}
+// derivative expressed through the OUTPUT o = act(x) (relu / celu / tanh) — lets the backward
+// pass read the saved activation instead of the pre-activation
+__device__ __forceinline__ float act_bwd_from_out(float o, int act) {
+    switch (act) {
+        case ACT_RELU: return o > 0.f ? 1.f : 0.f;
+        case ACT_CELU: return o > 0.f ? 1.f : (o * (1.f / kCeluAlpha) + 1.f);
+        case ACT_TANH: return 1.f - o * o;
+        default: return 1.f;
+    }
+}
+__device__ __forceinline__ float gelu_bwd_from_in(float x) {
+    const float k = 0.70710678118654752f, c = 0.3989422804014327f;   // 1/sqrt(2), 1/sqrt(2*pi)
+    return 0.5f * (1.f + erff(x * k)) + x * c * __expf(-0.5f * x * x);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+struct alignas(16) bf16x8 { __nv_bfloat162 v[4]; };
+
+__device__ __forceinline__ void unpack8(const bf16x8& p, float* f) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 t = __bfloat1622float2(p.v[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ bf16x8 pack8(const float* f) {
+    bf16x8 p;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) p.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return p;
+}
+__device__ __forceinline__ bf16x8 ld8(const __nv_bfloat16* p) { return *reinterpret_cast<const bf16x8*>(p); }
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const bf16x8& v) { *reinterpret_cast<bf16x8*>(p) = v; }
+
+// Philox4x32-10 counter-based RNG (dropout masks, device-side Beta / permutation sampling)
+struct Philox {
+    uint32_t key[2];
+    __device__ Philox(uint64_t seed) { key[0] = (uint32_t)seed; key[1] = (uint32_t)(seed >> 32); }
+    __device__ __forceinline__ uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
+        uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+        uint32_t k0 = key[0], k1 = key[1];
+#pragma unroll
+        for (int r = 0; r < 10; ++r) {
+            uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+            uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+            uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+            k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        }
+        return make_uint4(c0, c1, c2, c3);
+    }
+};
+__device__ __forceinline__ float u32_to_unit(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f); }   // [0,1)
+
+}  // namespace fdt

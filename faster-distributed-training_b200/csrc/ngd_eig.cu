@@ -1,0 +1,218 @@
+// NGD Fisher-factor refresh: Z assembly + batched symmetric eigensolver + all scalar algebra,
+// one CTA per factor, everything in shared memory, no host round trips.
+//
+// Parity: ngd_optimizer.py:225-317 of the reference, where each factor costs a
+// cuSOLVER syevd call, ~25 tiny ATen kernels and 7 `.item()` host syncs.  Inputs per factor are the
+// statistics K = J Jᵀ and L (R×R), the current d (R), rho and tr(X Xᵀ); outputs are
+//     A (R×R)  with  W_{t+1} = A · (J + w_coeff ∘ W_t),   w_coeff (R),   d_{t+1} (R),   rho_{t+1}.
+// The eigensolver is a two-sided cyclic Jacobi with round-robin (tournament) pair ordering: all
+// R/2 rotations of a step are independent, so the CTA applies them in parallel (columns of Z and V,
+// then rows of Z).  R <= 80 so Z and V (2 x 80 x 81 floats) fit in 52 KB of shared memory.
+#include "common.cuh"
+using namespace fdt;
+
+namespace {
+
+constexpr int kMaxR = 80;
+constexpr int kThreads = 256;
+constexpr float kEpsilon = 1.0e-10f;   // ngd_optimizer.py:37
+constexpr float kDelta = 5.0e-4f;      // ngd_optimizer.py:38
+
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) scratch[w] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < kThreads / 32; ++i) t += scratch[i];
+    return t;
+}
+__device__ __forceinline__ float block_max(float v, float* scratch) {
+    v = warp_max(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) scratch[w] = v;
+    __syncthreads();
+    float t = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < kThreads / 32; ++i) t = fmaxf(t, scratch[i]);
+    return t;
+}
+
+__global__ void __launch_bounds__(kThreads)
+ngd_eig_kernel(const float* __restrict__ Kg, const float* __restrict__ Lg, const float* __restrict__ dg,
+               const float* __restrict__ rhog, const float* __restrict__ trg,
+               float* __restrict__ Ag, float* __restrict__ wcg, float* __restrict__ d1g, float* __restrict__ rho1g,
+               int R, int D, float N, float alpha, float eta, int max_sweeps) {
+    extern __shared__ float sm[];
+    const int ld = R + 1 + ((R & 1) ? 1 : 0);        // padded leading dim, odd => conflict-free column walks
+    const int n2 = (R + 1) & ~1;                     // even problem size (dummy index R when R is odd)
+    float* Z = sm;                                   // [n2][ld]
+    float* V = Z + n2 * ld;                          // [n2][ld]
+    float* ise = V + n2 * ld;                        // inv_sqrt_e [R]
+    float* dpr = ise + kMaxR;                        // d + rho     [R]
+    float* cs = dpr + kMaxR;                         // rotation (c, s) per pair [n2]
+    float* lam = cs + 2 * kMaxR;                     // eigenvalues, then sqrt_c
+    float* leftv = lam + kMaxR;
+    float* scratch = leftv + kMaxR;                  // [8]
+    __shared__ int order[kMaxR];
+    __shared__ int pp[kMaxR / 2 + 1], qq[kMaxR / 2 + 1];
+
+    const int f = blockIdx.x, tid = threadIdx.x;
+    const float* K = Kg + (int64_t)f * R * R;
+    const float* L = Lg + (int64_t)f * R * R;
+    const float* d = dg + (int64_t)f * R;
+    const float rho = rhog[f];
+    const float trXXt = trg[f];
+
+    // ---- scalars that precede the eigenproblem (ngd_optimizer.py:225-260)
+    float v = 0.f, tk = 0.f;
+    for (int i = tid; i < R; i += kThreads) { v += d[i]; tk += K[i * R + i]; }
+    const float d_sum = block_sum(v, scratch);
+    const float z_scale = fmaxf(1.f, block_sum(tk, scratch));
+    const float beta = rho * (1.f + alpha) + alpha * d_sum / D;
+    for (int i = tid; i < R; i += kThreads) {
+        const float e = 1.f / (beta / d[i] + 1.f);
+        ise[i] = rsqrtf(e);
+        dpr[i] = d[i] + rho;
+    }
+    __syncthreads();
+    const float eN = eta / N;
+    const float c1 = eN * eN / z_scale, c2 = eN * (1.f - eta) / z_scale, c3 = (1.f - eta) * (1.f - eta) / z_scale;
+    for (int idx = tid; idx < n2 * n2; idx += kThreads) {
+        const int i = idx / n2, j = idx % n2;
+        float z = 0.f;
+        if (i < R && j < R) {
+            const float kij = 0.5f * (K[i * R + j] + K[j * R + i]);
+            const float lij = 0.5f * (L[i * R + j] + L[j * R + i]);
+            const float w = ise[i] * ise[j];
+            z = kij * w * c1 + lij * w * (dpr[i] + dpr[j]) * c2;
+            if (i == j) z += c3 * dpr[i] * dpr[i];
+        }
+        Z[i * ld + j] = z;
+        V[i * ld + j] = (i == j) ? 1.f : 0.f;
+    }
+    __syncthreads();
+
+    // ---- parallel cyclic Jacobi
+    const int half = n2 / 2;
+    for (int sweep = 0; sweep < max_sweeps; ++sweep) {
+        float off = 0.f, dia = 0.f;
+        for (int idx = tid; idx < R * R; idx += kThreads) {
+            const int i = idx / R, j = idx % R;
+            const float z = Z[i * ld + j];
+            if (i == j) dia += z * z; else off += z * z;
+        }
+        off = block_sum(off, scratch);
+        dia = block_sum(dia, scratch);
+        if (off <= 1e-13f * dia || off == 0.f) break;
+        for (int step = 0; step < n2 - 1; ++step) {
+            if (tid < half) {
+                int p, q;
+                if (tid == 0) { p = n2 - 1; q = step; }
+                else { p = (step + tid) % (n2 - 1); q = (step - tid + (n2 - 1)) % (n2 - 1); }
+                if (p > q) { int t = p; p = q; q = t; }
+                float c = 1.f, s = 0.f;
+                if (q < R) {
+                    const float zpq = Z[p * ld + q];
+                    if (fabsf(zpq) > 1e-37f) {
+                        const float tau = (Z[q * ld + q] - Z[p * ld + p]) / (2.f * zpq);
+                        const float t = (tau >= 0.f ? 1.f : -1.f) / (fabsf(tau) + sqrtf(1.f + tau * tau));
+                        c = rsqrtf(1.f + t * t);
+                        s = t * c;
+                    }
+                }
+                pp[tid] = p; qq[tid] = q; cs[2 * tid] = c; cs[2 * tid + 1] = s;
+            }
+            __syncthreads();
+            // columns of Z and V:  [col_p, col_q] <- [c·col_p − s·col_q,  s·col_p + c·col_q]
+            for (int idx = tid; idx < half * n2; idx += kThreads) {
+                const int k = idx / n2, i = idx % n2;
+                const int p = pp[k], q = qq[k];
+                const float c = cs[2 * k], s = cs[2 * k + 1];
+                const float zp = Z[i * ld + p], zq = Z[i * ld + q];
+                Z[i * ld + p] = c * zp - s * zq;
+                Z[i * ld + q] = s * zp + c * zq;
+                const float vp = V[i * ld + p], vq = V[i * ld + q];
+                V[i * ld + p] = c * vp - s * vq;
+                V[i * ld + q] = s * vp + c * vq;
+            }
+            __syncthreads();
+            // rows of Z
+            for (int idx = tid; idx < half * n2; idx += kThreads) {
+                const int k = idx / n2, j = idx % n2;
+                const int p = pp[k], q = qq[k];
+                const float c = cs[2 * k], s = cs[2 * k + 1];
+                const float zp = Z[p * ld + j], zq = Z[q * ld + j];
+                Z[p * ld + j] = c * zp - s * zq;
+                Z[q * ld + j] = s * zp + c * zq;
+            }
+            __syncthreads();
+        }
+    }
+
+    // ---- sort eigenvalues descending (rank by counting), floors, rho/d update (ngd_optimizer.py:265-295)
+    for (int i = tid; i < R; i += kThreads) lam[i] = Z[i * ld + i];
+    __syncthreads();
+    for (int i = tid; i < R; i += kThreads) {
+        const float li = lam[i];
+        int r = 0;
+        for (int j = 0; j < R; ++j) { const float lj = lam[j]; r += (lj > li) || (lj == li && j < i); }
+        order[r] = i;
+    }
+    __syncthreads();
+    const float c_floor = (rho * (1.f - eta)) * (rho * (1.f - eta)) / z_scale;
+    float sc = 0.f;
+    if (tid < R) {
+        sc = sqrtf(fmaxf(lam[order[tid]], c_floor)) * sqrtf(z_scale);   // sqrt_c, sorted position = tid
+    }
+    __syncthreads();
+    if (tid < R) leftv[tid] = sc;          // stash sqrt_c by sorted position
+    const float sum_sqrt_c = block_sum(tid < R ? sc : 0.f, scratch);
+    const float max_sqrt_c = block_max(tid < R ? sc : -INFINITY, scratch);
+    float rho1 = (1.f / (D - R)) * (eN * trXXt + (1.f - eta) * (D * rho + d_sum) - sum_sqrt_c);
+    const float floor_val = fmaxf(kEpsilon, kDelta * max_sqrt_c);
+    float d1 = 0.f;
+    if (tid < R) d1 = fmaxf(sc - rho1, floor_val);
+    if (rho1 < floor_val) rho1 = floor_val;
+    const float d1_sum = block_sum(tid < R ? d1 : 0.f, scratch);
+    const float beta1 = rho1 * (1.f + alpha) + alpha * d1_sum / D;
+    if (tid < R) {
+        const float e1 = 1.f / (beta1 / d1 + 1.f);
+        d1g[(int64_t)f * R + tid] = d1;
+        wcg[(int64_t)f * R + tid] = ((1.f - eta) / eN) * dpr[tid];
+        lam[tid] = eN * sqrtf(e1) / sc;     // left_i  (lam reused; order[] already consumed for values)
+    }
+    if (tid == 0) rho1g[f] = rho1;
+    __syncthreads();
+    // A[i][j] = U[j][i] · left_i · inv_sqrt_e_j ,  U[:, i] = V[:, order[i]]
+    float* A = Ag + (int64_t)f * R * R;
+    for (int idx = tid; idx < R * R; idx += kThreads) {
+        const int i = idx / R, j = idx % R;
+        A[idx] = V[j * ld + order[i]] * lam[i] * ise[j];
+    }
+}
+
+}  // namespace
+
+// One launch refreshes `n` same-shaped factors.  K, L: [n,R,R]; d: [n,R]; rho, trXXt: [n];
+// outputs A: [n,R,R]; w_coeff, d1: [n,R]; rho1: [n].
+FDT_API int fdt_ngd_eig_update(const float* K, const float* L, const float* d, const float* rho, const float* trXXt,
+                               float* A, float* w_coeff, float* d1, float* rho1, int n, int R, int D, float N,
+                               float alpha, float eta, int max_sweeps, cudaStream_t st) {
+    if (R < 1 || R > kMaxR || R >= D) return -1;
+    const int n2 = (R + 1) & ~1;
+    const int ld = R + 1 + ((R & 1) ? 1 : 0);
+    const size_t smem = sizeof(float) * (2 * (size_t)n2 * ld + 6 * kMaxR + 8);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(ngd_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    ngd_eig_kernel<<<n, kThreads, smem, st>>>(K, L, d, rho, trXXt, A, w_coeff, d1, rho1, R, D, N, alpha, eta, max_sweeps);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

@@ -55,15 +55,16 @@ class Trainer:
 
     # ------------------------------------------------------------------ one eager step
     def _local_grad(self) -> torch.Tensor:
-        eng = self.engine
-        if hasattr(eng, "region") and eng.comm.world > 1:
-            lo, hi = eng.region
-            return eng.flat.grad_flat[lo:hi]
-        return eng.flat.grad_flat
+        return self.engine.local_grad()
 
     def _clip(self):
         g = self._local_grad()
         sq = self.engine.grad_sq_norm()
+        if g.is_cuda:
+            from .. import ops
+            if ops.use_native(g):       # one fused kernel: clip coefficient, non-finite guard, scaling
+                ops._cu().clip_scale_(g, sq, self.clip_norm, self.skipped)
+                return
         finite = torch.isfinite(sq)
         if self.clip_norm is not None:
             coef = (self.clip_norm / (sq.sqrt() + 1e-6)).clamp(max=1.0)

@@ -33,6 +33,12 @@ def _cu():
     return cuda_ops
 
 
+def launch_counter():
+    """Counter of native kernel launches issued by this process (see ``fdt.ops._lib``)."""
+    from . import _lib
+    return _lib.LAUNCHES
+
+
 def conv_bnstat_act(x, weight, stride=1, padding=0, eps=1e-3, act="none", residual=None):
     if use_native(x):
         return _cu().conv_bnstat_act(x, weight, stride, padding, eps, act, residual)

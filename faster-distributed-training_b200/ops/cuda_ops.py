@@ -1,0 +1,413 @@
+"""CUDA execution path of :mod:`fdt.ops`: autograd wrappers around the sm_100a kernels in
+``csrc/`` (loaded through :mod:`fdt.ops._lib`).
+
+Tensor conventions on the GPU:
+* CNN activations are bf16, logical ``[N, C, H, W]`` with channels_last strides, i.e. physically
+  NHWC — what the implicit-GEMM conv kernels and the channel-wise kernels index as ``[P, C]``;
+* conv / linear weights are fp32 master copies inside :class:`fdt.parallel.flat.FlatParameters`
+  with a bf16 shadow refreshed once per step; conv weights are physically ``[O, kh, kw, I]``;
+* the transformer's residual stream is fp32 ``[B, L, D]``; LayerNorm emits bf16 for the GEMMs.
+
+Each fused unit saves exactly what its backward needs; the conv output ``y`` is kept (bf16)
+rather than recomputed as the reference does (``resnet.py:108``) — with 180 GB of HBM the extra
+conv per layer is the more expensive choice.
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from ._lib import call, i64
+from . import reference as ref
+
+ACT = {"none": 0, "relu": 1, "celu": 2, "gelu": 3, "tanh": 4}
+BF16 = torch.bfloat16
+
+# Which implementation runs the GEMM-shaped work.  "tcgen05" = csrc/gemm_sm100.cu (hand-written
+# tcgen05/TMEM/TMA kernels); "library" = cuDNN / cuBLAS through torch (kept as the oracle and for
+# shapes the native kernels do not cover yet).
+GEMM_BACKEND = os.environ.get("FDT_GEMM", "auto")
+
+
+def _native_gemm() -> bool:
+    if GEMM_BACKEND == "library":
+        return False
+    try:
+        from . import gemm_sm100
+        return gemm_sm100.available()
+    except Exception:
+        if GEMM_BACKEND == "tcgen05":
+            raise
+        return False
+
+
+# ----------------------------------------------------------------------------- small helpers
+def to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    return x.to(dtype=BF16, memory_format=torch.channels_last)
+
+
+def _nhwc(x: torch.Tensor) -> torch.Tensor:
+    if x.dtype != BF16 or not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.to(dtype=BF16, memory_format=torch.channels_last)
+    return x
+
+
+def _w16(p: torch.Tensor) -> torch.Tensor:
+    """bf16 operand copy of a parameter: a view of the flat shadow when available."""
+    f = getattr(p, "_fdt_flat", None)
+    if f is not None:
+        s = f[0].shadow_of(p)
+        if s is not None:
+            return s
+    if p.dim() == 4:
+        return p.detach().to(dtype=BF16, memory_format=torch.channels_last)
+    return p.detach().to(BF16)
+
+
+def cast_bf16_(src: torch.Tensor, dst: torch.Tensor):
+    call("fdt_cast_bf16", src, dst, i64(src.numel()))
+
+
+def sqnorm(g: torch.Tensor) -> torch.Tensor:
+    out = torch.zeros((), dtype=torch.float32, device=g.device)
+    call("fdt_sqnorm", g, i64(g.numel()), out)
+    return out
+
+
+def clip_scale_(g: torch.Tensor, sq: torch.Tensor, max_norm: float, skipped: Optional[torch.Tensor]):
+    call("fdt_clip_scale", g, i64(g.numel()), sq, float(max_norm if max_norm is not None else 0.0), skipped)
+
+
+def sgd_momentum_(p, d, buf, lr, momentum, dampening, nesterov, first):
+    lr_ptr = lr if torch.is_tensor(lr) else None
+    lr_val = 0.0 if torch.is_tensor(lr) else float(lr)
+    call("fdt_sgd_momentum", p, d, buf, i64(p.numel()), lr_ptr, lr_val, float(momentum), float(dampening),
+         int(bool(nesterov)), int(bool(first)))
+
+
+def madgrad_(p, g, v, s, x0, lamb, ck, decay, eps, mirror):
+    call("fdt_madgrad", p, g, v, s, x0, i64(p.numel()), float(lamb), float(ck), float(decay), float(eps), int(mirror))
+
+
+_seed_state = {}
+
+
+def _next_seed_off(device) -> torch.Tensor:
+    """Device-resident (seed, counter) pair for Philox dropout masks; advances without a host sync
+    (and inside CUDA-graph replays)."""
+    st = _seed_state.get(device)
+    if st is None:
+        st = torch.tensor([torch.initial_seed() & 0x7FFFFFFFFFFF, 0], dtype=torch.int64, device=device)
+        _seed_state[device] = st
+    cur = st.clone()
+    st[1] += 1
+    return cur
+
+
+# ----------------------------------------------------------------------------- conv back ends
+def _conv_fwd(x, w16, stride, padding):
+    if _native_gemm():
+        from . import gemm_sm100
+        y = gemm_sm100.conv_fwd(x, w16, stride, padding)
+        if y is not None:
+            return y
+    return F.conv2d(x, w16, stride=stride, padding=padding)
+
+
+def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape):
+    dx = dw = None
+    if _native_gemm():
+        from . import gemm_sm100
+        if need_dx:
+            dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding)
+        if need_dw:
+            dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding)
+    if (need_dx and dx is None) or (need_dw and dw is None):
+        mask = [need_dx and dx is None, need_dw and dw is None, False]
+        rdx, rdw, _ = torch.ops.aten.convolution_backward(dy, x, w16, None, [stride, stride], [padding, padding],
+                                                          [1, 1], False, [0, 0], 1, mask)
+        dx = rdx if dx is None else dx
+        dw = rdw if dw is None else dw
+    return dx, dw
+
+
+# ----------------------------------------------------------------------------- conv + BN + act unit
+class _ConvBNAct(torch.autograd.Function):
+    """y = conv(x, w);  out = act(bn(y) [+ residual]).  ``form`` 0: reference batch-stat form,
+    1: BatchNorm2d training, 2: BatchNorm2d eval."""
+
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, residual, cfg):
+        stride, padding, eps, act, form = cfg["stride"], cfg["padding"], cfg["eps"], ACT[cfg["act"]], cfg["form"]
+        x = _nhwc(x)
+        w16 = _w16(weight)
+        y = _conv_fwd(x, w16, stride, padding)
+        Nb, C, Ho, Wo = y.shape
+        P = Nb * Ho * Wo
+        dev = y.device
+        sums = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        if form != 2:
+            call("fdt_chan_reduce2", y, y, None, None, sums, i64(P), C, 0, launches=2)
+        coef = torch.empty(3 * C, dtype=torch.float32, device=dev)
+        bnctx = torch.empty(5 * C, dtype=torch.float32, device=dev)
+        call("fdt_bn_finalize_fwd", sums, coef, bnctx, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
+             C, float(P), float(eps), float(cfg.get("momentum") or 0.0), form)
+        out = torch.empty_like(y)
+        res = _nhwc(residual) if residual is not None else None
+        call("fdt_chan_affine_act", y, None, res, out, coef, i64(P), C, act)
+        ctx.save_for_backward(x, weight, w16, y, out, bnctx)
+        ctx.cfg = (stride, padding, act, form, residual is not None, gamma is not None)
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, weight, w16, y, out, bnctx = ctx.saved_tensors
+        stride, padding, act, form, has_res, affine = ctx.cfg
+        Nb, C, Ho, Wo = y.shape
+        P = Nb * Ho * Wo
+        dev = y.device
+        gout = _nhwc(gout)
+        sums = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        if act != 0:
+            g = torch.empty_like(gout)
+            call("fdt_chan_reduce2", gout, y, out, g, sums, i64(P), C, act, launches=2)
+        else:
+            g = gout
+            call("fdt_chan_reduce2", gout, y, None, None, sums, i64(P), C, 0, launches=2)
+        coef = torch.empty(3 * C, dtype=torch.float32, device=dev)
+        dgamma = dbeta = None
+        if affine:
+            dgamma = torch.empty(C, dtype=torch.float32, device=dev)
+            dbeta = torch.empty(C, dtype=torch.float32, device=dev)
+        call("fdt_bn_finalize_bwd", sums, bnctx, coef, dgamma, dbeta, C, float(P), form)
+        dy = torch.empty_like(y)
+        call("fdt_chan_affine_act", g, y, None, dy, coef, i64(P), C, 0)
+        dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape)
+        return dx, dw, dgamma, dbeta, (g if has_res else None), None
+
+
+def conv_bnstat_act(x, weight, stride, padding, eps, act, residual):
+    cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=0)
+    return _ConvBNAct.apply(x, weight, None, None, residual, cfg)
+
+
+def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_batches_tracked, stride, padding,
+                      eps, momentum, training, act, residual):
+    if training and num_batches_tracked is not None:
+        num_batches_tracked.add_(1)
+    cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=1 if training else 2,
+               running_mean=running_mean, running_var=running_var, momentum=momentum)
+    return _ConvBNAct.apply(x, weight, gamma, beta, residual, cfg)
+
+
+def pool_fc(x, weight, bias):
+    # [N, C, H, W] bf16 NHWC → fp32 logits; tiny (B x 2048 x 10)
+    pooled = x.float().mean(dim=(2, 3))
+    return F.linear(pooled, weight, bias)
+
+
+# ----------------------------------------------------------------------------- mixup
+def mixup_blend(x, index, lam):
+    lam = lam.to(x.dtype)
+    if lam.dim() == 1:
+        lam = lam.view(-1, *([1] * (x.dim() - 1)))
+    return torch.lerp(x[index], x, lam)
+
+
+class _MixupCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, y_a, y_b, lam):
+        logits = logits.float().contiguous()
+        B, C = logits.shape
+        out = torch.zeros(2, dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        lam = lam.reshape(-1).float().contiguous()
+        call("fdt_mixup_ce", logits, y_a.contiguous(), y_b.contiguous(), lam, lam.numel(), out, dlogits, B, C)
+        ctx.save_for_backward(dlogits)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits * g, None, None, None
+
+
+def mixup_cross_entropy(logits, y_a, y_b, lam):
+    if not torch.is_tensor(lam):
+        lam = torch.tensor([float(lam)], device=logits.device)
+    if lam.requires_grad or logits.shape[1] > 32:
+        return ref.mixup_cross_entropy(logits, y_a, y_b, lam)       # learnable λ: differentiable path
+    return _MixupCE.apply(logits, y_a, y_b, lam)
+
+
+# ----------------------------------------------------------------------------- transformer ops
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, a, b, eps):
+        shp = x.shape
+        D = shp[-1]
+        x2 = x.float().contiguous().view(-1, D)
+        M = x2.shape[0]
+        y = torch.empty(M, D, dtype=BF16, device=x.device)
+        stats = torch.empty(M, 2, dtype=torch.float32, device=x.device)
+        call("fdt_ln_fwd", x2, a, b, y, stats, M, D, float(eps))
+        ctx.save_for_backward(x2, a, stats)
+        ctx.eps, ctx.shp = eps, shp
+        return y.view(shp)
+
+    @staticmethod
+    def backward(ctx, g):
+        x2, a, stats = ctx.saved_tensors
+        M, D = x2.shape
+        g = g.to(BF16).contiguous().view(M, D)
+        dx = torch.zeros_like(x2)
+        da = torch.zeros(D, dtype=torch.float32, device=x2.device)
+        db = torch.zeros(D, dtype=torch.float32, device=x2.device)
+        call("fdt_ln_bwd", x2, a, stats, g, dx, da, db, M, D, float(ctx.eps))
+        return dx.view(ctx.shp), da, db, None
+
+
+def layernorm_ref(x, a_2, b_2, eps):
+    if x.shape[-1] not in (128, 256, 512, 1024):
+        return ref.layernorm_ref(x, a_2, b_2, eps)
+    return _LayerNorm.apply(x, a_2, b_2, eps)
+
+
+class _LinearLib(torch.autograd.Function):
+    """bf16 GEMM with fp32 master weights: library back end (cuBLAS) with the same contract as the
+    tcgen05 path (x any float dtype → bf16 out; fused bias + activation)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act):
+        x16 = x.to(BF16)
+        w16 = _w16(weight)
+        z = F.linear(x16, w16, None if bias is None else bias.to(BF16).reshape(-1))
+        out = ref.activation(z, act) if act != "none" else z
+        ctx.save_for_backward(x16, w16, z if act in ("gelu",) else out)
+        ctx.act, ctx.has_bias, ctx.xdtype, ctx.bshape = act, bias is not None, x.dtype, None if bias is None else bias.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x16, w16, saved = ctx.saved_tensors
+        g = g.to(BF16)
+        if ctx.act == "gelu":
+            zf = saved.float()
+            g = (g.float() * (0.5 * (1 + torch.erf(zf * 0.7071067811865476)) +
+                              zf * 0.3989422804014327 * torch.exp(-0.5 * zf * zf))).to(BF16)
+        elif ctx.act == "relu":
+            g = g * (saved > 0)
+        elif ctx.act == "tanh":
+            g = (g.float() * (1 - saved.float() ** 2)).to(BF16)
+        g2 = g.reshape(-1, g.shape[-1])
+        dx = (g2 @ w16).view(x16.shape).to(ctx.xdtype) if ctx.needs_input_grad[0] else None
+        dw = (g2.t() @ x16.reshape(-1, x16.shape[-1])).float() if ctx.needs_input_grad[1] else None
+        db = g2.float().sum(0).view(ctx.bshape) if ctx.has_bias and ctx.needs_input_grad[2] else None
+        return dx, dw, db, None
+
+
+def linear(x, weight, bias, act):
+    if _native_gemm():
+        from . import gemm_sm100
+        out = gemm_sm100.linear(x, weight, bias, act)
+        if out is not None:
+            return out
+    return _LinearLib.apply(x, weight, bias, act)
+
+
+def attention(q, k, v, key_mask, dropout_p, training, mask_compat):
+    if _native_gemm():
+        from . import gemm_sm100
+        out = gemm_sm100.attention(q, k, v, key_mask, dropout_p if training else 0.0, mask_compat)
+        if out is not None:
+            return out
+    if mask_compat:
+        return ref.attention(q, k, v, key_mask, dropout_p, training, True)
+    m = None if key_mask is None else (key_mask != 0)[:, None, None, :]
+    return F.scaled_dot_product_attention(q, k, v, attn_mask=m, dropout_p=dropout_p if training else 0.0)
+
+
+class _Embed(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens, types, tok_w, pos_w, seg_w, scale):
+        B, L = tokens.shape
+        D = tok_w.shape[1]
+        tokens = tokens.long().contiguous()
+        types = types.long().contiguous()
+        out = torch.empty(B, L, D, dtype=torch.float32, device=tok_w.device)
+        call("fdt_embed_fwd", tokens, types, tok_w, pos_w, seg_w, out, B * L, L, D, float(scale))
+        ctx.save_for_backward(tokens, types)
+        ctx.shapes = (tok_w.shape, pos_w.shape, seg_w.shape, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        tokens, types = ctx.saved_tensors
+        ts, ps, ss, scale = ctx.shapes
+        B, L = tokens.shape
+        D = ts[1]
+        g = g.float().contiguous()
+        dtok = torch.zeros(ts, dtype=torch.float32, device=g.device)
+        dpos = torch.zeros(ps, dtype=torch.float32, device=g.device)
+        dseg = torch.zeros(ss, dtype=torch.float32, device=g.device)
+        call("fdt_embed_bwd", tokens, types, g, dtok, dpos, dseg, B * L, L, D, float(scale))
+        return None, None, dtok, dpos, dseg, None
+
+
+def embed(tokens, token_types, tok_w, pos_w, seg_w, scale):
+    return _Embed.apply(tokens, token_types, tok_w, pos_w, seg_w, scale)
+
+
+def mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat):
+    # B x 512 → 1024 → n_class: negligible work; differentiable torch ops in fp32
+    return ref.mlp_head(x.float(), W1, b1, W2, b2, bias_grad_mean_compat)
+
+
+class _DropoutAdd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, p):
+        x = x.contiguous()
+        res = residual.float().contiguous()
+        out = torch.empty_like(res)
+        so = _next_seed_off(x.device)
+        assert x.dtype in (BF16, torch.float32)
+        call("fdt_dropout_add", x, int(x.dtype == BF16), res, out, i64(x.numel()), float(p), so)
+        ctx.save_for_backward(so)
+        ctx.p, ctx.xdtype = p, x.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (so,) = ctx.saved_tensors
+        g = g.float().contiguous()
+        dx = torch.empty(g.shape, dtype=ctx.xdtype, device=g.device)
+        call("fdt_dropout_bwd", g, dx, int(ctx.xdtype == BF16), i64(g.numel()), float(ctx.p), so)
+        return dx, g, None
+
+
+def dropout_add(x, residual, p, training):
+    if x.dtype not in (BF16, torch.float32):
+        x = x.float()
+    return _DropoutAdd.apply(x, residual, p if training else 0.0)
+
+
+# ----------------------------------------------------------------------------- NGD
+def ngd_eig_update(fb, K, L, trXXt, max_sweeps: int = 12):
+    """(A, w_coeff, d1, rho1) for a FactorBatch — csrc/ngd_eig.cu."""
+    if K.dtype != torch.float32:
+        from ..optim.ngd import fisher_update_torch
+        return fisher_update_torch(fb, None, K, L, trXXt)
+    n, R = fb.n, fb.R
+    dev = K.device
+    A = torch.empty(n, R, R, dtype=torch.float32, device=dev)
+    wc = torch.empty(n, R, dtype=torch.float32, device=dev)
+    d1 = torch.empty(n, R, dtype=torch.float32, device=dev)
+    rho1 = torch.empty(n, dtype=torch.float32, device=dev)
+    call("fdt_ngd_eig_update", K.contiguous(), L.contiguous(), fb.d, fb.rho, trXXt.contiguous(), A, wc, d1, rho1,
+         n, R, fb.D, float(fb.N), float(fb.alpha), float(fb.eta), int(max_sweeps))
+    return A, wc, d1, rho1

@@ -189,21 +189,31 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool) -> torch.Tensor:
 
 
 class _ShapeGroup:
-    """Same-shaped parameters of one param group, processed as one batched tensor."""
+    """Same-shaped parameters of one param group, processed as one batched tensor.
+
+    Work happens on the *physical* (contiguous) arrangement of the stacked tensor: conv weights
+    kept channels_last by :class:`FlatParameters` are ``[n, O, kh, kw, I]`` in memory, and
+    ``axis_map[logical_axis]`` gives the physical position of each logical axis so the axes are
+    still preconditioned in the reference's logical order (0: O, 1: I, 2: kh, 3: kw)."""
 
     def __init__(self, params: List[torch.Tensor]):
         self.params = params
         self.shape = tuple(params[0].shape)
         self.factors: Dict[int, FactorBatch] = {}
         self.momentum: Optional[torch.Tensor] = None
-        self._flat = None  # (grad_view, param_view) when backed by FlatParameters
+        self._flat = None                       # (grad_view, param_view): logical [n, *shape] views
+        self.flat_owner = None                  # FlatParameters backing this group (fused update path)
+        self.flat_idxs: List[int] = []
+        nd = len(self.shape)
+        self.axis_map = list(range(nd))         # logical axis -> physical axis (without the batch dim)
+        self._to_phys = None                    # permutation logical[n,*shape] -> physical contiguous
 
     def bind_flat(self):
         """Use zero-copy ``[n, *shape]`` views when the params sit contiguously in a flat buffer."""
         g0 = getattr(self.params[0], "_fdt_flat", None)
         if g0 is None:
             return
-        flat, first = g0
+        flat = g0[0]
         idxs = []
         for p in self.params:
             f = getattr(p, "_fdt_flat", None)
@@ -211,17 +221,26 @@ class _ShapeGroup:
                 return
             idxs.append(f[1])
         views = flat.stacked_views(idxs, self.shape)
-        if views is not None:
-            self._flat = views
+        if views is None:
+            return
+        self._flat = views
+        self.flat_owner, self.flat_idxs = flat, idxs
+        if len(self.shape) == 4 and not views[0].is_contiguous():
+            # physical [n, O, kh, kw, I]
+            self._to_phys = (0, 1, 3, 4, 2)
+            self.axis_map = [0, 3, 1, 2]
+
+    def _phys(self, t: torch.Tensor) -> torch.Tensor:
+        return t if self._to_phys is None else t.permute(*self._to_phys)
 
     def grads(self) -> torch.Tensor:
         if self._flat is not None:
-            return self._flat[0]
+            return self._phys(self._flat[0])
         return torch.stack([p.grad for p in self.params])
 
     def values(self) -> torch.Tensor:
         if self._flat is not None:
-            return self._flat[1]
+            return self._phys(self._flat[1])
         return torch.stack([p.data for p in self.params])
 
     def write_back(self, new_values: torch.Tensor):
@@ -309,10 +328,54 @@ class NGD(Optimizer):
         """Copy each group's python ``lr`` into its device scalar (call outside graph replay)."""
         for gi, group in enumerate(self.param_groups):
             t = self._lr_tensors.get(gi)
-            if t is not None:
+            if torch.is_tensor(t):
                 t.fill_(float(group["lr"]))
 
     # ------------------------------------------------------------------ step
+    def _precondition_group(self, sg: _ShapeGroup, group, d_p: torch.Tensor) -> torch.Tensor:
+        """Sequentially precondition every (logical) axis of the stacked physical tensor."""
+        n = d_p.shape[0]
+        nd = len(sg.shape)
+        phys_shape = tuple(d_p.shape[1:])
+        for axis in range(nd):
+            D = sg.shape[axis]
+            if D == 1:
+                continue
+            pa = sg.axis_map[axis]
+            N = d_p[0].numel() // D
+            fb = sg.factors.get(axis)
+            if fb is None:
+                fb = sg.factors[axis] = FactorBatch(n, N, D, group["alpha"], group["rank"], group["update_period"],
+                                                    group["eta"], d_p.dtype, d_p.device)
+            if pa == nd - 1:
+                d_p = precondition(fb, d_p.reshape(n, N, D), left=False).reshape(n, *phys_shape)
+            elif pa == 0:
+                d_p = precondition(fb, d_p.reshape(n, D, N), left=True).reshape(n, *phys_shape)
+            else:
+                Xm = d_p.movedim(pa + 1, -1)
+                mid = Xm.shape
+                d_p = precondition(fb, Xm.reshape(n, N, D), left=False).reshape(mid).movedim(-1, pa + 1)
+        return d_p
+
+    def _flat_span(self, gi: int, sgs: List[_ShapeGroup]):
+        """(flat, lo, hi) when this param group's flat-backed shape groups share one buffer."""
+        key = ("span", gi)
+        if key in self._lr_tensors:
+            return self._lr_tensors[key]
+        owners = {id(sg.flat_owner): sg.flat_owner for sg in sgs if sg.flat_owner is not None}
+        span = None
+        if len(owners) == 1:
+            flat = next(iter(owners.values()))
+            idxs = [i for sg in sgs if sg.flat_owner is not None for i in sg.flat_idxs]
+            lo, hi = flat.span_of(idxs)
+            # only safe when no foreign parameter lives inside [lo, hi)
+            mine = set(idxs)
+            inside = [i for i in range(len(flat.params)) if lo <= flat.span_of([i])[0] < hi]
+            if all(i in mine for i in inside):
+                span = (flat, lo, hi)
+        self._lr_tensors[key] = span
+        return span
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
@@ -321,37 +384,25 @@ class NGD(Optimizer):
                 loss = closure()
         for gi, group in enumerate(self.param_groups):
             wd, mom, damp = group["weight_decay"], group["momentum"], group["dampening"]
-            for sg in self._shape_groups(gi, group):
+            sgs = self._shape_groups(gi, group)
+            span = self._flat_span(gi, sgs)
+            lr = None
+            if span is not None:
+                flat, lo, hi = span
+                gflat, pflat = flat.grad_flat[lo:hi], flat.param_flat[lo:hi]
+                if wd != 0:
+                    gflat.add_(pflat, alpha=wd)
+            for sg in sgs:
+                fused = span is not None and sg.flat_owner is not None
                 G = sg.grads()
                 P = sg.values()
-                n = G.shape[0]
-                if wd != 0:
+                if wd != 0 and not fused:
                     G.add_(P, alpha=wd)
-                d_p = G
-                if group["ngd"]:
-                    nd = len(sg.shape)
-                    for axis in range(nd):
-                        D = sg.shape[axis]
-                        if D == 1:
-                            continue
-                        numel = d_p[0].numel()
-                        N = numel // D
-                        fb = sg.factors.get(axis)
-                        if fb is None:
-                            fb = sg.factors[axis] = FactorBatch(
-                                n, N, D, group["alpha"], group["rank"], group["update_period"],
-                                group["eta"], d_p.dtype, d_p.device)
-                        if axis == nd - 1:
-                            out = precondition(fb, d_p.reshape(n, N, D), left=False)
-                            d_p = out.reshape(n, *sg.shape)
-                        elif axis == 0:
-                            out = precondition(fb, d_p.reshape(n, D, N), left=True)
-                            d_p = out.reshape(n, *sg.shape)
-                        else:
-                            Xm = d_p.movedim(axis + 1, -1)
-                            mid_shape = Xm.shape
-                            out = precondition(fb, Xm.reshape(n, N, D), left=False)
-                            d_p = out.reshape(mid_shape).movedim(-1, axis + 1)
+                d_p = self._precondition_group(sg, group, G) if group["ngd"] else G
+                if fused:
+                    if d_p is not G:
+                        G.copy_(d_p)                      # result lands in the flat gradient buffer
+                    continue
                 if mom != 0:
                     if sg.momentum is None:
                         sg.momentum = d_p.clone(memory_format=torch.contiguous_format)
@@ -364,7 +415,35 @@ class NGD(Optimizer):
                 else:
                     P.add_(d_p, alpha=-lr)
                 sg.write_back(P)
+            if span is not None:
+                self._fused_update(gi, group, gflat, pflat)
         return loss
+
+    def _fused_update(self, gi: int, group, gflat: torch.Tensor, pflat: torch.Tensor):
+        """Momentum + parameter update over the whole flat range: one kernel on CUDA."""
+        mom, damp, nesterov = group["momentum"], group["dampening"], group["nesterov"]
+        key = ("mom", gi)
+        buf = self._lr_tensors.get(key)
+        first = buf is None
+        if first and mom != 0:
+            buf = self._lr_tensors[key] = torch.zeros_like(gflat)
+        lr = self._lr(gi, group, pflat.device)
+        if pflat.is_cuda:
+            from .. import ops
+            if ops.use_native(pflat):
+                ops._cu().sgd_momentum_(pflat, gflat, buf, lr, mom, damp, nesterov, first)
+                return
+        d_p = gflat
+        if mom != 0:
+            if first:
+                buf.copy_(d_p)
+            else:
+                buf.mul_(mom).add_(d_p, alpha=1.0 - damp)
+            d_p = d_p.add(buf, alpha=mom) if nesterov else buf
+        if torch.is_tensor(lr):
+            pflat.sub_(d_p * lr)
+        else:
+            pflat.add_(d_p, alpha=-lr)
 
     # ------------------------------------------------------------------ (de)serialisation
     def state_dict(self):
@@ -381,6 +460,8 @@ class NGD(Optimizer):
                                 for axis, fb in sg.factors.items()},
                 })
             entry["shape_groups"] = sgs
+            fm = self._lr_tensors.get(("mom", gi))
+            entry["flat_momentum"] = None if fm is None else fm.detach().clone()
             groups.append(entry)
         return {"format": "fdt-ngd-v1", "groups": groups}
 
@@ -389,8 +470,11 @@ class NGD(Optimizer):
             raise ValueError("not an fdt NGD state dict")
         for gi, (group, entry) in enumerate(zip(self.param_groups, state["groups"])):
             for k, v in entry.items():
-                if k != "shape_groups":
+                if k not in ("shape_groups", "flat_momentum"):
                     group[k] = v
+            if entry.get("flat_momentum") is not None:
+                dev = group["params"][0].device
+                self._lr_tensors[("mom", gi)] = entry["flat_momentum"].to(dev)
             # shape groups need gradients to exist to be discovered; build them from params
             for p in group["params"]:
                 if p.grad is None:

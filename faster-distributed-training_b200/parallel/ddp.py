@@ -36,22 +36,41 @@ class DataParallelEngine(nn.Module):
         self.comm.broadcast_(self.flat.param_flat, src=0)
         for b in module.buffers():
             self.comm.broadcast_(b, src=0)
+        self._stale = True
 
     def forward(self, *a, **kw):
+        self.pre_forward()
         return self.module(*a, **kw)
 
     def optimizer_params(self):
         return self.flat.params
 
     def pre_forward(self):
-        pass
+        """Refresh the bf16 operand shadow of every parameter (one cast kernel) if stale."""
+        if self._stale:
+            self.flat.refresh_shadow()
+            self._stale = False
+
+    def post_step(self):
+        self._stale = True
 
     def reduce_gradients(self):
         self.comm.all_reduce_mean_(self.flat.grad_flat)
 
+    def local_grad(self) -> torch.Tensor:
+        return self.flat.grad_flat
+
     def grad_sq_norm(self) -> torch.Tensor:
         g = self.flat.grad_flat
+        if g.is_cuda:
+            from .. import ops
+            if ops.use_native(g):
+                return ops._cu().sqnorm(g)
         return torch.dot(g, g)
+
+    def load_state_dict(self, *a, **kw):
+        self._stale = True
+        return super().load_state_dict(*a, **kw)
 
     def zero_grad(self):
         self.flat.zero_grad()

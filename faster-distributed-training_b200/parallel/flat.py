@@ -109,18 +109,51 @@ class FlatParameters:
 
         self._index: Dict[int, Tuple[ShapeGroupLayout, int]] = {}
         self.params: List[torch.nn.Parameter] = []
+        self.shadow_flat: Optional[torch.Tensor] = None      # bf16 copy of param_flat, same layout
         with torch.no_grad():
             for g in self.groups:
                 for i, p in enumerate(g.params):
                     lo = g.offset + i * g.numel
-                    pv = self.param_flat[lo:lo + g.numel].view(g.shape)
+                    pv = self._view(self.param_flat, lo, g.shape)
                     pv.copy_(p.data.to(self.device, torch.float32))
                     p.data = pv
-                    p.grad = self.grad_flat[lo:lo + g.numel].view(g.shape)
+                    p.grad = self._view(self.grad_flat, lo, g.shape)
                     idx = len(self.params)
                     p._fdt_flat = (self, idx)
                     self._index[idx] = (g, i)
                     self.params.append(p)
+
+    # 4-D (conv) weights are stored physically as [O, kh, kw, I] — the K-major operand layout of
+    # the implicit-GEMM kernels and torch's channels_last — while their logical shape stays the
+    # reference's [O, I, kh, kw], so state dicts are unchanged.
+    @staticmethod
+    def _view(flat: torch.Tensor, lo: int, shape, n: Optional[int] = None) -> torch.Tensor:
+        numel = 1
+        for s in shape:
+            numel *= s
+        lead = () if n is None else (n,)
+        cnt = numel * (1 if n is None else n)
+        if len(shape) == 4:
+            O, I, H, W = shape
+            v = flat[lo:lo + cnt].view(*lead, O, H, W, I)
+            k = len(lead)
+            return v.permute(*range(k), k, k + 3, k + 1, k + 2)
+        return flat[lo:lo + cnt].view(*lead, *shape)
+
+    def refresh_shadow(self):
+        """bf16 shadow of every parameter in one pass (the GEMM / conv kernels' B operands)."""
+        if self.device.type != "cuda":
+            return
+        if self.shadow_flat is None:
+            self.shadow_flat = torch.empty(self.total, dtype=torch.bfloat16, device=self.device)
+        from ..ops import cuda_ops
+        cuda_ops.cast_bf16_(self.param_flat, self.shadow_flat)
+
+    def shadow_of(self, p: torch.nn.Parameter) -> Optional[torch.Tensor]:
+        if self.shadow_flat is None:
+            return None
+        g, i = self._index[p._fdt_flat[1]]
+        return self._view(self.shadow_flat, g.offset + i * g.numel, g.shape)
 
     # -- zero-copy batched views for the optimizer
     def stacked_views(self, idxs: List[int], shape) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
@@ -130,16 +163,20 @@ class FlatParameters:
             if g is not g0 or i != i0 + k:
                 return None
         lo = g0.offset + i0 * g0.numel
-        hi = lo + len(idxs) * g0.numel
         n = len(idxs)
-        return (self.grad_flat[lo:hi].view(n, *shape), self.param_flat[lo:hi].view(n, *shape))
+        return (self._view(self.grad_flat, lo, shape, n), self._view(self.param_flat, lo, shape, n))
+
+    def span_of(self, idxs: List[int]) -> Tuple[int, int]:
+        """Element range [lo, hi) of the flat buffers covered by parameters ``idxs``."""
+        lo = min(self._index[i][0].offset + self._index[i][1] * self._index[i][0].numel for i in idxs)
+        hi = max(self._index[i][0].offset + (self._index[i][1] + 1) * self._index[i][0].numel for i in idxs)
+        return lo, hi
 
     def rebind_grads(self):
         """Re-point ``p.grad`` at the flat buffer (after someone set grads to ``None``)."""
         for idx, p in enumerate(self.params):
             g, i = self._index[idx]
-            lo = g.offset + i * g.numel
-            p.grad = self.grad_flat[lo:lo + g.numel].view(g.shape)
+            p.grad = self._view(self.grad_flat, g.offset + i * g.numel, g.shape)
 
     def zero_grad(self):
         self.grad_flat.zero_()

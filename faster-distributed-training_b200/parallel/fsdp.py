@@ -45,6 +45,7 @@ class FullyShardedEngine(nn.Module):
         for b in module.buffers():
             self.comm.broadcast_(b, src=0)
         self._gathered = True
+        self._stale = True
 
     def forward(self, *a, **kw):
         self.pre_forward()
@@ -57,6 +58,10 @@ class FullyShardedEngine(nn.Module):
         if not self._gathered:
             self.comm.all_gather_(self.flat.param_flat, self.region)
             self._gathered = True
+            self._stale = True
+        if self._stale:
+            self.flat.refresh_shadow()
+            self._stale = False
 
     def reduce_gradients(self):
         self.comm.reduce_scatter_mean_(self.flat.grad_flat, self.region)
@@ -64,11 +69,17 @@ class FullyShardedEngine(nn.Module):
     def post_step(self):
         """Call after the optimizer updated the owned region: remote regions are now stale."""
         self._gathered = self.comm.world == 1
+        self._stale = True
+
+    def local_grad(self) -> torch.Tensor:
+        lo, hi = self.region
+        return self.flat.grad_flat[lo:hi]
 
     def grad_sq_norm(self) -> torch.Tensor:
         lo, hi = self.region
         g = self.flat.grad_flat[lo:hi]
-        sq = torch.dot(g, g).reshape(1)
+        from .. import ops
+        sq = (ops._cu().sqnorm(g) if ops.use_native(g) else torch.dot(g, g)).reshape(1)
         return self.comm.all_reduce_sum_(sq)[0]
 
     def zero_grad(self):

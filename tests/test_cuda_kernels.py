@@ -1,0 +1,205 @@
+"""Numerics of the sm_100a kernels against the plain-PyTorch fp32 oracle of the same op
+(``fdt.ops.reference``).  Everything here needs a GPU."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _ops():
+    from fdt import ops
+    return ops
+
+
+def _close(a, b, rtol, atol, what=""):
+    a, b = a.float(), b.float()
+    err = (a - b).abs().max().item()
+    ref = b.abs().max().item()
+    assert torch.allclose(a, b, rtol=rtol, atol=atol), f"{what}: max err {err:.4g} (ref max {ref:.4g})"
+
+
+@pytest.mark.parametrize("cin,cout,k,hw,act,res", [(64, 64, 3, 16, "relu", False), (64, 256, 1, 8, "relu", True),
+                                                    (16, 32, 3, 8, "celu", True), (128, 128, 3, 4, "none", False)])
+def test_conv_bnstat_act_fwd_bwd(cin, cout, k, hw, act, res):
+    ops = _ops()
+    torch.manual_seed(0)
+    N = 8
+    x = torch.randn(N, cin, hw, hw, device=DEV)
+    w = torch.randn(cout, cin, k, k, device=DEV) / math.sqrt(cin * k * k)
+    r = torch.randn(N, cout, hw, hw, device=DEV) if res else None
+    gout = torch.randn(N, cout, hw, hw, device=DEV)
+    # oracle in fp32 on bf16-rounded inputs
+    xr = x.bfloat16().float().requires_grad_(True)
+    wr = w.bfloat16().float().requires_grad_(True)
+    rr = r.bfloat16().float().requires_grad_(True) if res else None
+    out_ref = ops.ref.conv_bnstat_act(xr, wr, 1, k // 2, 1e-3, act, rr)
+    out_ref.backward(gout.bfloat16().float())
+    xn = x.bfloat16().to(memory_format=torch.channels_last).requires_grad_(True)
+    wn = w.clone().requires_grad_(True)
+    rn = r.bfloat16().to(memory_format=torch.channels_last).requires_grad_(True) if res else None
+    out = ops.conv_bnstat_act(xn, wn, 1, k // 2, 1e-3, act, rn)
+    assert out.dtype == torch.bfloat16
+    out.backward(gout.bfloat16().to(memory_format=torch.channels_last))
+    _close(out, out_ref, 3e-2, 3e-2, "out")
+    _close(xn.grad, xr.grad, 5e-2, 5e-2 * xr.grad.abs().max().item(), "dx")
+    _close(wn.grad, wr.grad, 5e-2, 5e-2 * wr.grad.abs().max().item(), "dw")
+    if res:
+        _close(rn.grad, rr.grad, 3e-2, 3e-2, "dres")
+
+
+@pytest.mark.parametrize("training", [True, False])
+def test_conv_bnaffine_act(training):
+    ops = _ops()
+    torch.manual_seed(1)
+    N, cin, cout, hw = 8, 32, 64, 8
+    x = torch.randn(N, cin, hw, hw, device=DEV)
+    w = torch.randn(cout, cin, 3, 3, device=DEV) / math.sqrt(cin * 9)
+    gamma = torch.rand(cout, device=DEV) + 0.5
+    beta = torch.randn(cout, device=DEV) * 0.1
+    gout = torch.randn(N, cout, hw // 2, hw // 2, device=DEV)
+
+    def run(native):
+        rm, rv, nb = torch.zeros(cout, device=DEV), torch.ones(cout, device=DEV), torch.zeros((), dtype=torch.long, device=DEV)
+        g, b = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+        if native:
+            xi = x.bfloat16().to(memory_format=torch.channels_last).requires_grad_(True)
+            wi = w.clone().requires_grad_(True)
+            o = ops.conv_bnaffine_act(xi, wi, g, b, rm, rv, nb, 2, 1, 1e-5, 0.1, training, "relu", None)
+            o.backward(gout.bfloat16().to(memory_format=torch.channels_last))
+        else:
+            xi = x.bfloat16().float().requires_grad_(True)
+            wi = w.bfloat16().float().requires_grad_(True)
+            o = ops.ref.conv_bnaffine_act(xi, wi, g, b, rm, rv, nb, 2, 1, 1e-5, 0.1, training, "relu", None)
+            o.backward(gout.bfloat16().float())
+        return o, xi.grad, wi.grad, g.grad, b.grad, rm, rv
+
+    a, b_ = run(True), run(False)
+    names = ["out", "dx", "dw", "dgamma", "dbeta", "running_mean", "running_var"]
+    for n, u, v in zip(names, a, b_):
+        _close(u, v, 5e-2, 5e-2 * max(v.abs().max().item(), 1e-3), n)
+
+
+def test_layernorm_fwd_bwd():
+    ops = _ops()
+    torch.manual_seed(2)
+    x = torch.randn(6, 37, 512, device=DEV) * 2 + 0.3
+    a = torch.rand(512, device=DEV) + 0.5
+    b = torch.randn(512, device=DEV) * 0.1
+    g = torch.randn(6, 37, 512, device=DEV)
+    xr, ar, br = x.clone().requires_grad_(True), a.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ops.ref.layernorm_ref(xr, ar, br, 1e-6).backward(g.bfloat16().float())
+    xn, an, bn = x.clone().requires_grad_(True), a.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y = ops.layernorm_ref(xn, an, bn, 1e-6)
+    assert y.dtype == torch.bfloat16
+    y.backward(g.bfloat16())
+    _close(y, ops.ref.layernorm_ref(x, a, b, 1e-6), 1e-2, 2e-2, "y")
+    _close(xn.grad, xr.grad, 1e-3, 1e-3, "dx")
+    _close(an.grad, ar.grad, 1e-3, 1e-2, "da")
+    _close(bn.grad, br.grad, 1e-3, 1e-2, "db")
+
+
+@pytest.mark.parametrize("per_sample", [False, True])
+def test_mixup_ce(per_sample):
+    ops = _ops()
+    torch.manual_seed(3)
+    B, C = 77, 10
+    logits = torch.randn(B, C, device=DEV) * 3
+    ya, yb = torch.randint(0, C, (B,), device=DEV), torch.randint(0, C, (B,), device=DEV)
+    lam = torch.rand(B, device=DEV) if per_sample else torch.rand((), device=DEV)
+    lr_ = logits.clone().requires_grad_(True)
+    loss_ref = ops.ref.mixup_cross_entropy(lr_, ya, yb, lam)
+    loss_ref.backward()
+    ln = logits.clone().requires_grad_(True)
+    loss = ops.mixup_cross_entropy(ln, ya, yb, lam)
+    loss.backward()
+    _close(loss, loss_ref, 1e-5, 1e-5, "loss")
+    _close(ln.grad, lr_.grad, 1e-4, 1e-6, "dlogits")
+
+
+def test_embed_fwd_bwd():
+    ops = _ops()
+    torch.manual_seed(4)
+    B, L, D, V = 5, 33, 512, 1000
+    tok = torch.randint(0, V, (B, L), device=DEV)
+    typ = torch.randint(0, 3, (B, L), device=DEV)
+    ws = [torch.randn(V, D, device=DEV), torch.randn(512, D, device=DEV), torch.randn(3, D, device=DEV)]
+    g = torch.randn(B, L, D, device=DEV)
+    wr = [w.clone().requires_grad_(True) for w in ws]
+    wn = [w.clone().requires_grad_(True) for w in ws]
+    o_ref = ops.ref.embed(tok, typ, *wr, math.sqrt(D))
+    o_ref.backward(g)
+    o = ops.embed(tok, typ, *wn, math.sqrt(D))
+    o.backward(g)
+    _close(o, o_ref, 1e-6, 1e-5, "out")
+    for n, a, b in zip(["dtok", "dpos", "dseg"], wn, wr):
+        _close(a.grad, b.grad, 1e-4, 1e-3, n)
+
+
+def test_dropout_add():
+    ops = _ops()
+    torch.manual_seed(5)
+    x = torch.randn(64, 128, 512, device=DEV).bfloat16()
+    r = torch.randn(64, 128, 512, device=DEV)
+    o = ops.dropout_add(x, r, 0.1, False)
+    _close(o, r + x.float(), 1e-6, 1e-6, "eval")
+    xn = x.clone().requires_grad_(True)
+    o = ops.dropout_add(xn, r, 0.1, True)
+    kept = ((o - r).abs() > 0) | (x.float() == 0)
+    frac = 1.0 - kept.float().mean().item()
+    assert abs(frac - 0.1) < 5e-3, frac
+    o.backward(torch.ones_like(o))
+    mask_b = xn.grad.float() != 0
+    assert torch.equal(mask_b, (o - r).abs() > 0) or (mask_b ^ ((o - r).abs() > 0)).float().mean() < 1e-3
+    _close(xn.grad[mask_b], torch.full_like(xn.grad[mask_b], 1 / 0.9), 1e-2, 1e-2, "scale")
+
+
+@pytest.mark.parametrize("n,N,D", [(3, 200, 64), (2, 30, 160), (4, 576, 64), (2, 27, 3), (1, 7, 5)])
+def test_ngd_eig_update(n, N, D):
+    ops = _ops()
+    from fdt.optim import ngd as M
+    torch.manual_seed(6)
+    fb_a = M.FactorBatch(n, N, D, 4.0, -1, 4, 0.1, torch.float32, DEV)
+    fb_b = M.FactorBatch(n, N, D, 4.0, -1, 4, 0.1, torch.float32, DEV)
+    for it in range(5):
+        X = torch.randn(n, N, D, device=DEV) * (1 + it)
+        ops.force_torch(True)
+        out_b = M.precondition(fb_b, X, left=False)
+        ops.force_torch(False)
+        out_a = M.precondition(fb_a, X, left=False)
+        _close(out_a, out_b, 2e-3, 2e-3 * out_b.abs().max().item(), f"precond it{it}")
+        _close(fb_a.d, fb_b.d, 5e-3, 5e-3 * fb_b.d.abs().max().item(), f"d it{it}")
+        _close(fb_a.rho, fb_b.rho, 5e-3, 1e-6, f"rho it{it}")
+        WtWa = torch.bmm(fb_a.W.transpose(1, 2), fb_a.W)
+        WtWb = torch.bmm(fb_b.W.transpose(1, 2), fb_b.W)
+        _close(WtWa, WtWb, 1e-2, 1e-2 * WtWb.abs().max().item(), f"WtW it{it}")
+
+
+def test_flat_kernels():
+    ops = _ops()
+    cu = ops._cu()
+    torch.manual_seed(7)
+    n = 1_000_003
+    g = torch.randn(n, device=DEV)
+    sq = cu.sqnorm(g)
+    _close(sq, (g.double() ** 2).sum().float(), 1e-4, 0, "sqnorm")
+    g2 = g.clone()
+    sk = torch.zeros((), device=DEV)
+    cu.clip_scale_(g2, sq, 10.0, sk)
+    _close(g2, g * (10.0 / (sq.sqrt() + 1e-6)), 1e-5, 1e-7, "clip")
+    p, buf = torch.randn(n, device=DEV), torch.zeros(n, device=DEV)
+    p_ref = p.clone()
+    lr = torch.tensor(0.1, device=DEV)
+    cu.sgd_momentum_(p, g, buf, lr, 0.9, 0.0, False, True)
+    cu.sgd_momentum_(p, g, buf, lr, 0.9, 0.0, False, False)
+    b = g.clone(); p_ref -= 0.1 * b; b = 0.9 * b + g; p_ref -= 0.1 * b
+    _close(p, p_ref, 1e-5, 1e-6, "sgd")
+    y = torch.empty(n, dtype=torch.bfloat16, device=DEV)
+    cu.cast_bf16_(g, y)
+    assert torch.equal(y, g.bfloat16())
+    bad = torch.full((8,), float("nan"), device=DEV)
+    cu.clip_scale_(bad, cu.sqnorm(bad), 10.0, sk)
+    assert sk.item() == 1 and (bad == 0).all()
