@@ -146,6 +146,10 @@ def bench(args, rank, local, world, timed_steps, barrier_sync, max_over_ranks, C
     def step_dev(i):
         body(*dev[i % len(dev)])
 
+    # settle: the reference refreshes every Fisher factor on each of its first 10 steps and every
+    # 4th step afterwards (ngd_optimizer.py:347-354); both arms are measured in that steady state
+    for i in range(0 if args.no_settle else 12):
+        step_dev(i)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()

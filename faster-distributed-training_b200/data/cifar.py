@@ -79,6 +79,17 @@ def get_dataset(root: str = "./data", synthetic: bool = False, n_train: int = 50
     return SyntheticCIFAR(n_train, seed=0), SyntheticCIFAR(n_test, seed=1)
 
 
+_CONST = {}
+
+
+def _mean_std(dev):
+    """Per-device normalisation constants, created once (no H2D copy inside CUDA-graph capture)."""
+    key = str(dev)
+    if key not in _CONST:
+        _CONST[key] = (torch.tensor(MEAN, device=dev).view(1, 3, 1, 1), torch.tensor(STD, device=dev).view(1, 3, 1, 1))
+    return _CONST[key]
+
+
 def gpu_transform(images_u8: torch.Tensor, train: bool, generator: Optional[torch.Generator] = None,
                   pad: int = 4) -> torch.Tensor:
     """uint8 NHWC → float NCHW, random-crop(pad 4) + horizontal flip (train) + normalise.
@@ -88,8 +99,7 @@ def gpu_transform(images_u8: torch.Tensor, train: bool, generator: Optional[torc
     B, H, W, C = images_u8.shape
     dev = images_u8.device
     x = images_u8.permute(0, 3, 1, 2).float() / 255.0
-    mean = torch.tensor(MEAN, device=dev).view(1, 3, 1, 1)
-    std = torch.tensor(STD, device=dev).view(1, 3, 1, 1)
+    mean, std = _mean_std(dev)
     if train:
         dx = torch.randint(0, 2 * pad + 1, (B,), device=dev, generator=generator) - pad
         dy = torch.randint(0, 2 * pad + 1, (B,), device=dev, generator=generator) - pad

@@ -107,6 +107,11 @@ class Trainer:
                     s.copy_(b, non_blocking=True)
         return self._static_in
 
+    def _prime_constants(self, batch):
+        """Hook for anything that must exist before capture (device constants are created lazily
+        during the eager warm-up steps, so nothing to do by default)."""
+        return None
+
     def step(self, batch) -> Tuple[torch.Tensor, Any]:
         """``batch`` is a tuple of device tensors.  Returns ``(loss, aux)`` (device tensors; with
         graphs they are static buffers overwritten by the next step)."""
@@ -117,7 +122,10 @@ class Trainer:
             return self._eager_step(batch)
         kind = self._kind()
         if kind == "warm" or self._steps <= self.graph_warmup:
-            return self._eager_step(batch)
+            out = self._eager_step(batch)
+            if self._steps == self.graph_warmup:
+                self._prime_constants(batch)
+            return out
         static = self._copy_in(batch)
         if kind not in self._graphs:
             torch.cuda.synchronize()
