@@ -228,3 +228,24 @@ FDT_API int fdt_bn_finalize_bwd(const float* sums, const float* ctx, float* coef
     FDT_CHECK_LAUNCH();
     return 0;
 }
+
+// Fused forward of one normalisation unit: statistics → per-channel coefficients → normalise
+// [+ residual] + activation, as three stream-ordered launches behind ONE call.  `scratch` is
+// caller-provided working memory of 5*C floats (sums[2C] | coef[3C]); its contents on entry do not
+// matter and are garbage afterwards.  `ctx` (5*C floats) is an OUTPUT the backward pass reads.
+// form 0: reference FusedConvBN (gamma/beta/running_* unused) · 1: BatchNorm2d train · 2: BatchNorm2d eval.
+FDT_API int fdt_bn_act_fwd(const void* y, const void* res, void* out, float* ctx, float* scratch,
+                           const float* gamma, const float* beta, float* running_mean, float* running_var,
+                           int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st) {
+    if (C % 8) return -1;
+    float* sums = scratch;
+    float* coef = scratch + 2 * (size_t)C;
+    int rc;
+    if (form != 2) {
+        rc = fdt_chan_reduce2(y, y, nullptr, nullptr, sums, P, C, ACT_NONE, st);
+        if (rc) return rc;
+    }
+    rc = fdt_bn_finalize_fwd(sums, coef, ctx, gamma, beta, running_mean, running_var, C, (float)P, eps, momentum, form, st);
+    if (rc) return rc;
+    return fdt_chan_affine_act(y, nullptr, res, out, coef, P, C, act, st);
+}

@@ -41,11 +41,11 @@ __device__ __forceinline__ float block_max(float v, float* scratch) {
     return t;
 }
 
-__global__ void __launch_bounds__(kThreads)
-ngd_eig_kernel(const float* __restrict__ Kg, const float* __restrict__ Lg, const float* __restrict__ dg,
-               const float* __restrict__ rhog, const float* __restrict__ trg,
-               float* __restrict__ Ag, float* __restrict__ wcg, float* __restrict__ d1g, float* __restrict__ rho1g,
-               int R, int D, float N, float alpha, float eta, int max_sweeps) {
+__device__ __forceinline__ void
+ngd_eig_body(const float* __restrict__ Kg, const float* __restrict__ Lg, const float* __restrict__ dg,
+             const float* __restrict__ rhog, const float* __restrict__ trg,
+             float* __restrict__ Ag, float* __restrict__ wcg, float* __restrict__ d1g, float* __restrict__ rho1g,
+             const int f, int R, int D, float N, float alpha, float eta, int max_sweeps) {
     extern __shared__ float sm[];
     const int ld = R + 1 + ((R & 1) ? 1 : 0);        // padded leading dim, odd => conflict-free column walks
     const int n2 = (R + 1) & ~1;                     // even problem size (dummy index R when R is odd)
@@ -60,7 +60,7 @@ ngd_eig_kernel(const float* __restrict__ Kg, const float* __restrict__ Lg, const
     __shared__ int order[kMaxR];
     __shared__ int pp[kMaxR / 2 + 1], qq[kMaxR / 2 + 1];
 
-    const int f = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x;
     const float* K = Kg + (int64_t)f * R * R;
     const float* L = Lg + (int64_t)f * R * R;
     const float* d = dg + (int64_t)f * R;
@@ -195,6 +195,30 @@ ngd_eig_kernel(const float* __restrict__ Kg, const float* __restrict__ Lg, const
     }
 }
 
+__global__ void __launch_bounds__(kThreads)
+ngd_eig_kernel(const float* __restrict__ Kg, const float* __restrict__ Lg, const float* __restrict__ dg,
+               const float* __restrict__ rhog, const float* __restrict__ trg,
+               float* __restrict__ Ag, float* __restrict__ wcg, float* __restrict__ d1g, float* __restrict__ rho1g,
+               int R, int D, float N, float alpha, float eta, int max_sweeps) {
+    ngd_eig_body(Kg, Lg, dg, rhog, trg, Ag, wcg, d1g, rho1g, blockIdx.x, R, D, N, alpha, eta, max_sweeps);
+}
+
+// One descriptor per factor (= per CTA): factors of every shape group of the model in ONE launch.
+struct NgdEigDesc {
+    const float *K, *L, *d, *rho, *tr;
+    float *A, *wc, *d1, *rho1;
+    int R, D;
+    float N, alpha, eta;
+    int pad;
+};
+static_assert(sizeof(NgdEigDesc) == 96, "descriptor layout is mirrored in fdt/ops/cuda_ops.py");
+
+__global__ void __launch_bounds__(kThreads)
+ngd_eig_multi_kernel(const NgdEigDesc* __restrict__ descs, int max_sweeps) {
+    const NgdEigDesc d = descs[blockIdx.x];
+    ngd_eig_body(d.K, d.L, d.d, d.rho, d.tr, d.A, d.wc, d.d1, d.rho1, 0, d.R, d.D, d.N, d.alpha, d.eta, max_sweeps);
+}
+
 }  // namespace
 
 // One launch refreshes `n` same-shaped factors.  K, L: [n,R,R]; d: [n,R]; rho, trXXt: [n];
@@ -206,13 +230,20 @@ FDT_API int fdt_ngd_eig_update(const float* K, const float* L, const float* d, c
     const int n2 = (R + 1) & ~1;
     const int ld = R + 1 + ((R & 1) ? 1 : 0);
     const size_t smem = sizeof(float) * (2 * (size_t)n2 * ld + 6 * kMaxR + 8);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(ngd_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    cudaError_t e = cudaFuncSetAttribute(ngd_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e != cudaSuccess) return (int)e;
     ngd_eig_kernel<<<n, kThreads, smem, st>>>(K, L, d, rho, trXXt, A, w_coeff, d1, rho1, R, D, N, alpha, eta, max_sweeps);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// Heterogeneous batch: `count` descriptors (device memory, 96 bytes each, see NgdEigDesc), one CTA each.
+FDT_API int fdt_ngd_eig_update_multi(const void* descs, int count, int max_sweeps, cudaStream_t st) {
+    if (count <= 0) return 0;
+    const size_t smem = sizeof(float) * (2 * (size_t)kMaxR * (kMaxR + 1) + 6 * kMaxR + 8);
+    cudaError_t e = cudaFuncSetAttribute(ngd_eig_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    ngd_eig_multi_kernel<<<count, kThreads, smem, st>>>((const NgdEigDesc*)descs, max_sweeps);
     FDT_CHECK_LAUNCH();
     return 0;
 }

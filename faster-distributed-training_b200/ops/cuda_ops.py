@@ -150,16 +150,12 @@ class _ConvBNAct(torch.autograd.Function):
         Nb, C, Ho, Wo = y.shape
         P = Nb * Ho * Wo
         dev = y.device
-        sums = torch.empty(2 * C, dtype=torch.float32, device=dev)
-        if form != 2:
-            call("fdt_chan_reduce2", y, y, None, None, sums, i64(P), C, 0, launches=2)
-        coef = torch.empty(3 * C, dtype=torch.float32, device=dev)
+        scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)      # sums[2C] | coef[3C]
         bnctx = torch.empty(5 * C, dtype=torch.float32, device=dev)
-        call("fdt_bn_finalize_fwd", sums, coef, bnctx, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
-             C, float(P), float(eps), float(cfg.get("momentum") or 0.0), form)
         out = torch.empty_like(y)
         res = _nhwc(residual) if residual is not None else None
-        call("fdt_chan_affine_act", y, None, res, out, coef, i64(P), C, act)
+        call("fdt_bn_act_fwd", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
+             i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=4 if form != 2 else 2)
         ctx.save_for_backward(x, weight, w16, y, out, bnctx)
         ctx.cfg = (stride, padding, act, form, residual is not None, gamma is not None)
         return out
@@ -411,3 +407,32 @@ def ngd_eig_update(fb, K, L, trXXt, max_sweeps: int = 12):
     call("fdt_ngd_eig_update", K.contiguous(), L.contiguous(), fb.d, fb.rho, trXXt.contiguous(), A, wc, d1, rho1,
          n, R, fb.D, float(fb.N), float(fb.alpha), float(fb.eta), int(max_sweeps))
     return A, wc, d1, rho1
+
+
+_desc_cache = {}
+
+
+def ngd_eig_update_multi(pending, max_sweeps: int = 12):
+    """Refresh every factor of every pending FactorBatch with ONE launch (csrc/ngd_eig.cu).
+    Inputs fb.K/L/d/rho/tr and outputs fb.A/wc/d1/rho1 are the batches' persistent buffers, so the
+    96-byte per-factor descriptors are built once per set of batches and cached on the device."""
+    import struct
+    key = tuple(id(fb) for fb in pending)
+    ent = _desc_cache.get(key)
+    if ent is None:
+        rows = []
+        for fb in pending:
+            R, D = fb.R, fb.D
+            for f in range(fb.n):
+                ptrs = (fb.K.data_ptr() + f * R * R * 4, fb.L.data_ptr() + f * R * R * 4, fb.d.data_ptr() + f * R * 4,
+                        fb.rho.data_ptr() + f * 4, fb.tr.data_ptr() + f * 4, fb.A.data_ptr() + f * R * R * 4,
+                        fb.wc.data_ptr() + f * R * 4, fb.d1.data_ptr() + f * R * 4, fb.rho1.data_ptr() + f * 4)
+                rows.append((R, struct.pack("<9Q2i3fi", *ptrs, R, D, float(fb.N), float(fb.alpha), float(fb.eta), 0)))
+        rows.sort(key=lambda r: -r[0])                     # biggest eigenproblems first
+        blob = b"".join(r[1] for r in rows)
+        host = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+        dev = torch.empty(len(blob), dtype=torch.uint8, device=pending[0].K.device)
+        dev.copy_(host)
+        ent = (dev, len(rows), [fb for fb in pending])     # keep the batches (and their buffers) alive
+        _desc_cache[key] = ent
+    call("fdt_ngd_eig_update_multi", ent[0], ent[1], int(max_sweeps))

@@ -133,19 +133,38 @@ def _fisher_update(fb: FactorBatch, J, K, L, trXXt):
     return fisher_update_torch(fb, J, K, L, trXXt)
 
 
-def _refresh(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor, trXXt: torch.Tensor):
-    """Update (W, d, rho) in place from the current gradient matrix and H (= X Wᵀ or its
-    transpose)."""
+def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
+    """J = HᵀX, L, K = JJᵀ into the factor batch's persistent work buffers."""
     W = fb.W
+    if not hasattr(fb, "J"):
+        n, R, D = fb.n, fb.R, fb.D
+        kw = dict(dtype=W.dtype, device=W.device)
+        fb.J = torch.empty(n, R, D, **kw)
+        fb.K = torch.empty(n, R, R, **kw)
+        fb.L = torch.empty(n, R, R, **kw)
+        fb.A = torch.empty(n, R, R, **kw)
+        fb.wc = torch.empty(n, R, **kw)
+        fb.d1 = torch.empty(n, R, **kw)
+        fb.rho1 = torch.empty(n, **kw)
+        fb.tr = torch.empty(n, **kw)
     if left:   # Xm: [n, D, N], H: [n, R, N]
-        J = torch.bmm(H, Xm.transpose(1, 2))
-        L = torch.bmm(J, W.transpose(1, 2)) if fb.N > fb.D else torch.bmm(H, H.transpose(1, 2))
+        torch.bmm(H, Xm.transpose(1, 2), out=fb.J)
+        if fb.N > fb.D:
+            torch.bmm(fb.J, W.transpose(1, 2), out=fb.L)
+        else:
+            torch.bmm(H, H.transpose(1, 2), out=fb.L)
     else:      # Xm: [n, N, D], H: [n, N, R]
-        J = torch.bmm(H.transpose(1, 2), Xm)
-        L = torch.bmm(J, W.transpose(1, 2)) if fb.N > fb.D else torch.bmm(H.transpose(1, 2), H)
-    K = torch.bmm(J, J.transpose(1, 2))
-    A, w_coeff, d1, rho1 = _fisher_update(fb, J, K, L, trXXt)
-    B = torch.addcmul(J, w_coeff.unsqueeze(2), W)
+        torch.bmm(H.transpose(1, 2), Xm, out=fb.J)
+        if fb.N > fb.D:
+            torch.bmm(fb.J, W.transpose(1, 2), out=fb.L)
+        else:
+            torch.bmm(H.transpose(1, 2), H, out=fb.L)
+    torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+
+
+def _apply_refresh(fb: FactorBatch, A, w_coeff, d1, rho1):
+    W = fb.W
+    B = torch.addcmul(fb.J, w_coeff.unsqueeze(2), W)
     W1 = torch.bmm(A, B)
     # device-side guard: a factor whose refresh produced non-finite numbers keeps its old state
     ok = torch.isfinite(W1).flatten(1).all(1) & torch.isfinite(d1).all(1) & torch.isfinite(rho1)
@@ -155,13 +174,49 @@ def _refresh(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor, trX
     fb.rho.copy_(torch.where(ok, rho1, fb.rho))
 
 
-def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool) -> torch.Tensor:
+def _refresh(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor, trXXt: torch.Tensor):
+    """Update (W, d, rho) in place from the current gradient matrix and H (= X Wᵀ or its
+    transpose)."""
+    _statistics(fb, Xm, left, H)
+    A, w_coeff, d1, rho1 = _fisher_update(fb, fb.J, fb.K, fb.L, trXXt)
+    _apply_refresh(fb, A, w_coeff, d1, rho1)
+
+
+def flush_refreshes(pending: List[FactorBatch]):
+    """Finish the deferred Fisher refreshes of a whole optimizer step.  The statistics (J, K, L,
+    tr) of every pending factor batch are already in its work buffers; on CUDA all eigenproblems —
+    every factor of every shape group — run in ONE kernel launch (one CTA per factor)."""
+    if not pending:
+        return
+    fb0 = pending[0]
+    native = False
+    if fb0.K.is_cuda and fb0.K.dtype == torch.float32:
+        from .. import ops
+        native = ops.use_native(fb0.K)
+    if native:
+        from .. import ops
+        ops._cu().ngd_eig_update_multi(pending)
+        for fb in pending:
+            _apply_refresh(fb, fb.A, fb.wc, fb.d1, fb.rho1)
+    else:
+        for fb in pending:
+            A, w_coeff, d1, rho1 = fisher_update_torch(fb, fb.J, fb.K, fb.L, fb.tr)
+            _apply_refresh(fb, A, w_coeff, d1, rho1)
+    pending.clear()
+
+
+def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optional[List[FactorBatch]] = None) -> torch.Tensor:
     """Apply (and, on refresh steps, update) the inverse-Fisher factor.
 
     ``Xm`` is ``[n, N, D]`` (``left=False``) or its transpose ``[n, D, N]`` (``left=True``, used
     when the preconditioned axis is the tensor's first axis so no transpose copy is needed).
     Returns the preconditioned matrix in the same layout with its Frobenius norm restored
-    (ngd_optimizer.py:138-168)."""
+    (ngd_optimizer.py:138-168).
+
+    The output only depends on the *current* W (the reference also projects with W_t before it
+    computes W_{t+1}, ngd_optimizer.py:195-203), so when ``pending`` is given the refresh is
+    deferred: its statistics are computed here and the factor batch is appended to ``pending``
+    for :func:`flush_refreshes`."""
     p0 = (Xm * Xm).sum((1, 2))
 
     def project():
@@ -181,7 +236,12 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool) -> torch.Tensor:
     fb.t += 1
     H, Xhat = project()
     if updating:
-        _refresh(fb, Xm, left, H, p0)
+        if pending is None:
+            _refresh(fb, Xm, left, H, p0)
+        else:
+            _statistics(fb, Xm, left, H)
+            fb.tr.copy_(p0)
+            pending.append(fb)
     p1 = (Xhat * Xhat).sum((1, 2))
     scale = torch.sqrt(p0 / (p1 + 1.0e-30))
     out = Xhat * scale[:, None, None]
@@ -332,7 +392,7 @@ class NGD(Optimizer):
                 t.fill_(float(group["lr"]))
 
     # ------------------------------------------------------------------ step
-    def _precondition_group(self, sg: _ShapeGroup, group, d_p: torch.Tensor) -> torch.Tensor:
+    def _precondition_group(self, sg: _ShapeGroup, group, d_p: torch.Tensor, pending=None) -> torch.Tensor:
         """Sequentially precondition every (logical) axis of the stacked physical tensor."""
         n = d_p.shape[0]
         nd = len(sg.shape)
@@ -348,13 +408,13 @@ class NGD(Optimizer):
                 fb = sg.factors[axis] = FactorBatch(n, N, D, group["alpha"], group["rank"], group["update_period"],
                                                     group["eta"], d_p.dtype, d_p.device)
             if pa == nd - 1:
-                d_p = precondition(fb, d_p.reshape(n, N, D), left=False).reshape(n, *phys_shape)
+                d_p = precondition(fb, d_p.reshape(n, N, D), False, pending).reshape(n, *phys_shape)
             elif pa == 0:
-                d_p = precondition(fb, d_p.reshape(n, D, N), left=True).reshape(n, *phys_shape)
+                d_p = precondition(fb, d_p.reshape(n, D, N), True, pending).reshape(n, *phys_shape)
             else:
                 Xm = d_p.movedim(pa + 1, -1)
                 mid = Xm.shape
-                d_p = precondition(fb, Xm.reshape(n, N, D), left=False).reshape(mid).movedim(-1, pa + 1)
+                d_p = precondition(fb, Xm.reshape(n, N, D), False, pending).reshape(mid).movedim(-1, pa + 1)
         return d_p
 
     def _flat_span(self, gi: int, sgs: List[_ShapeGroup]):
@@ -382,6 +442,7 @@ class NGD(Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        pending: List[FactorBatch] = []
         for gi, group in enumerate(self.param_groups):
             wd, mom, damp = group["weight_decay"], group["momentum"], group["dampening"]
             sgs = self._shape_groups(gi, group)
@@ -398,7 +459,7 @@ class NGD(Optimizer):
                 P = sg.values()
                 if wd != 0 and not fused:
                     G.add_(P, alpha=wd)
-                d_p = self._precondition_group(sg, group, G) if group["ngd"] else G
+                d_p = self._precondition_group(sg, group, G, pending) if group["ngd"] else G
                 if fused:
                     if d_p is not G:
                         G.copy_(d_p)                      # result lands in the flat gradient buffer
@@ -417,6 +478,7 @@ class NGD(Optimizer):
                 sg.write_back(P)
             if span is not None:
                 self._fused_update(gi, group, gflat, pflat)
+        flush_refreshes(pending)
         return loss
 
     def _fused_update(self, gi: int, group, gflat: torch.Tensor, pflat: torch.Tensor):
