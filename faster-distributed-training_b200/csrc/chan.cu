@@ -8,6 +8,7 @@
 //   bwd : chan_reduce2 (g = gout·act'(out), Σg, Σg·y) → bn_finalize_bwd → chan_affine_act (A·g + B·y + C)
 // (the forward reduction disappears once the conv epilogue emits the sums).
 #include "common.cuh"
+#include <cstdio>
 using namespace fdt;
 
 namespace {
@@ -248,4 +249,61 @@ FDT_API int fdt_bn_act_fwd(const void* y, const void* res, void* out, float* ctx
     rc = fdt_bn_finalize_fwd(sums, coef, ctx, gamma, beta, running_mean, running_var, C, (float)P, eps, momentum, form, st);
     if (rc) return rc;
     return fdt_chan_affine_act(y, nullptr, res, out, coef, P, C, act, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// fdt_bn_act_fwd_noalloc — the same fused normalisation forward as fdt_bn_act_fwd, for callers
+// that have no working memory to hand over and are not allowed to go and get some.
+//
+// Who that is: a host program that has already given the whole device to a memory pool of its own
+// (so a cudaMalloc from inside a library would fail or fragment that pool), a plain C caller with no
+// tensor allocator at hand, or a latency-sensitive loop that cannot afford cudaMalloc / cudaFree,
+// which may synchronise the whole device.  For them the 5*C floats of working memory that
+// fdt_bn_act_fwd takes from its caller live in the library instead: one file-scope array in device
+// memory, sized for at most kNoAllocMaxC channels (5 * 4096 floats = 80 KiB).  Every GPU that loads
+// this library carries that array until the process exits.
+//
+// What to know before using it:
+//  * C must be a multiple of 8 and at most 4096; a larger C is refused with a message on stderr and
+//    the return value -2.  Nothing is launched in that case.
+//  * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+//    that device current) and remembers it.  Make that first call outside any stream capture.
+//  * All calls on a device share the one array and it keeps whatever the previous call left in it.
+//    The part that has to start from zero (the running sums) is cleared on the stream by every call,
+//    so back-to-back calls on ONE stream are fine.  Two calls that can overlap on the GPU — different
+//    streams, or different host threads without ordering between them — would race on the array;
+//    the caller has to serialise them.
+//  * No cudaMalloc, cudaFree or other allocating routine is called, on the first call or later.
+namespace {
+constexpr int kNoAllocMaxC = 4096;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) float g_bn_scratch[5 * kNoAllocMaxC];
+float* g_bn_scratch_addr[kNoAllocMaxDevices] = {nullptr};   // per device, filled on first use
+}  // namespace
+
+FDT_API int fdt_bn_act_fwd_noalloc(const void* y, const void* res, void* out, float* ctx,
+                                   const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                   int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st) {
+    if (C <= 0 || C % 8) return -1;
+    if (C > kNoAllocMaxC) {
+        fprintf(stderr, "fdt_bn_act_fwd_noalloc: C = %d channels exceeds the built-in working memory "
+                        "(limit %d channels); use fdt_bn_act_fwd with caller-provided scratch\n", C, kNoAllocMaxC);
+        return -2;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return -3;
+    float* scratch = g_bn_scratch_addr[dev];
+    if (scratch == nullptr) {
+        // In host code `g_bn_scratch` is only a handle for the symbol, not a device address: ask the
+        // runtime where the array lives on the current device and keep the answer.
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_bn_scratch);
+        if (e != cudaSuccess) return (int)e;
+        scratch = static_cast<float*>(p);
+        g_bn_scratch_addr[dev] = scratch;
+    }
+    return fdt_bn_act_fwd(y, res, out, ctx, scratch, gamma, beta, running_mean, running_var,
+                          P, C, eps, momentum, form, act, st);
 }

@@ -40,6 +40,17 @@ int fdt_bn_finalize_bwd(const float* sums, const float* ctx, float* coef, float*
 int fdt_bn_act_fwd(const void* y, const void* res, void* out, float* ctx, float* scratch,
                    const float* gamma, const float* beta, float* running_mean, float* running_var,
                    int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st);
+/* Same operation as fdt_bn_act_fwd for callers that cannot supply working memory and must not
+ * allocate any (a host that gave the whole GPU to its own pool, a bare C program, a loop that has to
+ * keep clear of cudaMalloc/cudaFree): the 5*C floats live in a fixed array inside the library, so
+ * C is limited to 4096 channels (80 KiB per GPU, held until exit); a larger C returns -2 and prints
+ * why.  The first call on a device resolves the array's address and should be made outside stream
+ * capture.  All calls on a device share the array: calls ordered on one stream are fine, calls that
+ * may overlap on the GPU race and must be serialised by the caller.  Allocates nothing, ever.
+ * This entry point has no counterpart in the reference (which ships no native code). */
+int fdt_bn_act_fwd_noalloc(const void* y, const void* res, void* out, float* ctx,
+                           const float* gamma, const float* beta, float* running_mean, float* running_var,
+                           int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st);
 
 /* ---- row-wise kernels, csrc/rowwise.cu ----------------------------------------------------------
  * ref: LayerNorm (transformer.py:230-242), Embeddings (:132-156), sub-layer dropout+residual (:245-275),
