@@ -70,7 +70,7 @@ def build_native(verbose: bool = True, force: bool = False) -> pathlib.Path:
         objs = list(ex.map(_compile, srcs))
     newest = max(o.stat().st_mtime for o in objs)
     if force or not LIB.exists() or LIB.stat().st_mtime < newest:
-        cmd = [nvcc_path(), "-shared", "-gencode", GENCODE, "-o", str(LIB), *map(str, objs), "-lcuda"]
+        cmd = [nvcc_path(), "-shared", "-gencode", GENCODE, "-o", str(LIB), *map(str, objs)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -15,102 +15,123 @@ namespace {
 
 constexpr int kThreads = 256;
 
-// Σ_p a[p,c]  and  Σ_p a[p,c]·b[p,c]   where a = g (optionally g = gout·act'(out), optionally stored)
-// grid.x blocks each own a slab of rows; thread → fixed 8-channel vector, loops over rows.
-template <bool kMask>
+// Σ_p a[p,c]  and  Σ_p a[p,c]·b[p,c]   where a = g (optionally g = gout·act'(out), optionally stored).
+// 2-D grid: blockIdx.y = tile of kTPR·8 channels, blockIdx.x = slab of rows.  A thread owns one
+// 8-channel vector column (16-byte loads) and walks its slab two rows at a time; partial sums are
+// combined with warp shuffles (threads of a warp that share a column), then across the 8 warps in
+// shared memory, and leave the block as one atomicAdd per channel.
+template <int kTPR, bool kMask, bool kSame>
 __global__ void __launch_bounds__(kThreads)
 chan_reduce2_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
                     const __nv_bfloat16* __restrict__ out_act, __nv_bfloat16* __restrict__ g_store,
                     float* __restrict__ sums /*[2,C]*/, int64_t P, int C, int act, int rows_per_block) {
-    const int vecC = C >> 3;
-    const int tpr = vecC < kThreads ? vecC : kThreads;      // threads per row
-    const int lanes = kThreads / tpr;                       // rows processed concurrently
-    const int cv = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    constexpr int kLanes = kThreads / kTPR;
+    const int cv = threadIdx.x % kTPR, rl = threadIdx.x / kTPR;
+    const int c0 = (blockIdx.y * kTPR + cv) * 8;
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     const int64_t r1 = min(P, r0 + rows_per_block);
-    __shared__ float red[2][kThreads][8 + 1];
-    for (int cbase = cv; cbase < vecC; cbase += tpr) {
-        float s1[8], s2[8];
+    float s1[8], s2[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s1[i] = s2[i] = 0.f;
-        if (rl < lanes) {
-            for (int64_t r = r0 + rl; r < r1; r += lanes) {
-                const int64_t off = r * C + (int64_t)cbase * 8;
-                float fa[8], fb[8];
-                unpack8(ld8(a + off), fa);
-                unpack8(ld8(b + off), fb);
-                if (kMask) {
-                    float fo[8];
-                    unpack8(ld8(out_act + off), fo);
+    for (int i = 0; i < 8; ++i) s1[i] = s2[i] = 0.f;
+
+    auto body = [&](int64_t r) {
+        const int64_t off = r * C + c0;
+        float fa[8], fb[8];
+        unpack8(ld8(a + off), fa);
+        if (!kSame) unpack8(ld8(b + off), fb);
+        if (kMask) {
+            float fo[8];
+            unpack8(ld8(out_act + off), fo);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) fa[i] *= act_bwd_from_out(fo[i], act);
-                    if (g_store) {
-                        bf16x8 pk = pack8(fa);
-                        st8(g_store + off, pk);
-                        unpack8(pk, fa);          // reduce exactly what later passes will read
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) { s1[i] += fa[i]; s2[i] += fa[i] * fb[i]; }
+            for (int i = 0; i < 8; ++i) fa[i] *= act_bwd_from_out(fo[i], act);
+            if (g_store) {
+                bf16x8 pk = pack8(fa);
+                st8(g_store + off, pk);
+                unpack8(pk, fa);          // reduce exactly what later passes will read
             }
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { red[0][threadIdx.x][i] = s1[i]; red[1][threadIdx.x][i] = s2[i]; }
-        __syncthreads();
-        if (rl == 0) {
+        for (int i = 0; i < 8; ++i) { s1[i] += fa[i]; s2[i] += fa[i] * (kSame ? fa[i] : fb[i]); }
+    };
+    int64_t r = r0 + rl;
+    for (; r + kLanes < r1; r += 2 * kLanes) { body(r); body(r + kLanes); }
+    if (r < r1) body(r);
+
+    // threads of one warp that share a channel column: lane = k·kTPR + cv
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                float t1 = 0.f, t2 = 0.f;
-                for (int l = 0; l < lanes; ++l) { t1 += red[0][l * tpr + cv][i]; t2 += red[1][l * tpr + cv][i]; }
-                atomicAdd(&sums[cbase * 8 + i], t1);
-                atomicAdd(&sums[C + cbase * 8 + i], t2);
-            }
+    for (int off = kTPR; off < 32; off <<= 1) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], off);
+            s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], off);
         }
-        __syncthreads();
+    }
+    constexpr int kCols = (kTPR < 32 ? kTPR : 32) * 8;       // channels covered by one warp
+    __shared__ float red[2][kThreads / 32][kCols];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane < kTPR) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { red[0][warp][(lane % kTPR) * 8 + i] = s1[i]; red[1][warp][(lane % kTPR) * 8 + i] = s2[i]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < kCols) {
+        float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) { t1 += red[0][w][threadIdx.x]; t2 += red[1][w][threadIdx.x]; }
+        const int c = blockIdx.y * kTPR * 8 + threadIdx.x;
+        atomicAdd(&sums[c], t1);
+        atomicAdd(&sums[C + c], t2);
     }
 }
 
-// out = act(A[c]·x1 + B[c]·x2 + Cc[c] + res);  x2 / res optional.
+// out = act(A[c]·x1 + B[c]·x2 + Cc[c] + res);  x2 / res optional.  Grid-stride over 16-byte vectors,
+// four independent vectors in flight per thread, coefficients staged in shared memory.
+template <bool kX2, bool kRes>
 __global__ void __launch_bounds__(kThreads)
 chan_affine_act_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
                        const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
-                       const float* __restrict__ coef /*[3,C]: A,B,Cc*/, int64_t P, int C, int act, int rows_per_block) {
+                       const float* __restrict__ coef /*[3,C]: A,B,Cc*/, int64_t total_vecs, int C, int act) {
+    extern __shared__ float sc[];
+    for (int i = threadIdx.x; i < 3 * C; i += kThreads) sc[i] = coef[i];
+    __syncthreads();
     const int vecC = C >> 3;
-    const int tpr = vecC < kThreads ? vecC : kThreads;
-    const int lanes = kThreads / tpr;
-    const int cv = threadIdx.x % tpr, rl = threadIdx.x / tpr;
-    if (rl >= lanes) return;
-    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
-    const int64_t r1 = min(P, r0 + rows_per_block);
-    for (int cbase = cv; cbase < vecC; cbase += tpr) {
-        float A[8], B[8], Cc[8];
+    const int64_t stride = (int64_t)gridDim.x * kThreads * 4;
+    for (int64_t base = (int64_t)blockIdx.x * kThreads * 4 + threadIdx.x; base < total_vecs; base += stride) {
+        bf16x8 v1[4], v2[4], vr[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            A[i] = coef[cbase * 8 + i];
-            B[i] = x2 ? coef[C + cbase * 8 + i] : 0.f;
-            Cc[i] = coef[2 * C + cbase * 8 + i];
+        for (int j = 0; j < 4; ++j) {
+            const int64_t v = base + (int64_t)j * kThreads;
+            if (v < total_vecs) {
+                v1[j] = ld8(x1 + v * 8);
+                if (kX2) v2[j] = ld8(x2 + v * 8);
+                if (kRes) vr[j] = ld8(res + v * 8);
+            }
         }
-        for (int64_t r = r0 + rl; r < r1; r += lanes) {
-            const int64_t off = r * C + (int64_t)cbase * 8;
-            float f1[8], o[8];
-            unpack8(ld8(x1 + off), f1);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] = fmaf(A[i], f1[i], Cc[i]);
-            if (x2) {
-                float f2[8];
-                unpack8(ld8(x2 + off), f2);
+        for (int j = 0; j < 4; ++j) {
+            const int64_t v = base + (int64_t)j * kThreads;
+            if (v < total_vecs) {
+                const int c = (int)(v % vecC) * 8;
+                float f1[8], o[8];
+                unpack8(v1[j], f1);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) o[i] = fmaf(B[i], f2[i], o[i]);
+                for (int i = 0; i < 8; ++i) o[i] = fmaf(sc[c + i], f1[i], sc[2 * C + c + i]);
+                if (kX2) {
+                    float f2[8];
+                    unpack8(v2[j], f2);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = fmaf(sc[C + c + i], f2[i], o[i]);
+                }
+                if (kRes) {
+                    float fr[8];
+                    unpack8(vr[j], fr);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] += fr[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = act_fwd(o[i], act);
+                st8(out + v * 8, pack8(o));
             }
-            if (res) {
-                float fr[8];
-                unpack8(ld8(res + off), fr);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) o[i] += fr[i];
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] = act_fwd(o[i], act);
-            st8(out + off, pack8(o));
         }
     }
 }
@@ -173,43 +194,59 @@ __global__ void bn_finalize_bwd_kernel(const float* __restrict__ sums, const flo
     coef[2 * C + c] = -a * b + a * cc * inv * mean;
 }
 
-int pick_rows_per_block(int64_t P, int C, int* grid) {
-    const int vecC = C >> 3;
-    const int tpr = vecC < kThreads ? vecC : kThreads;
-    const int lanes = kThreads / tpr;
-    int64_t target_blocks = 148 * 8;
-    int64_t rpb = (P + target_blocks - 1) / target_blocks;
-    int64_t min_rows = (int64_t)lanes * 4;
-    if (rpb < min_rows) rpb = min_rows;
-    rpb = (rpb + lanes - 1) / lanes * lanes;
-    *grid = (int)((P + rpb - 1) / rpb);
-    return (int)rpb;
+template <int kTPR>
+int launch_reduce2(const void* a, const void* b, const void* out_act, void* g_store, float* sums,
+                   int64_t P, int C, int act, cudaStream_t st) {
+    constexpr int kLanes = kThreads / kTPR;
+    const int ctiles = (C / 8) / kTPR;
+    int64_t slabs = (148 * 4 + ctiles - 1) / ctiles;
+    int64_t rpb = (P + slabs - 1) / slabs;
+    const int64_t unit = 2 * kLanes;
+    if (rpb < 2 * unit) rpb = 2 * unit;
+    rpb = (rpb + unit - 1) / unit * unit;
+    dim3 grid((unsigned)((P + rpb - 1) / rpb), ctiles);
+    auto A = (const __nv_bfloat16*)a; auto B = (const __nv_bfloat16*)b; auto O = (const __nv_bfloat16*)out_act;
+    auto G = (__nv_bfloat16*)g_store;
+    if (out_act && act != ACT_NONE)
+        chan_reduce2_kernel<kTPR, true, false><<<grid, kThreads, 0, st>>>(A, B, O, G, sums, P, C, act, (int)rpb);
+    else if (a == b)
+        chan_reduce2_kernel<kTPR, false, true><<<grid, kThreads, 0, st>>>(A, B, nullptr, nullptr, sums, P, C, act, (int)rpb);
+    else
+        chan_reduce2_kernel<kTPR, false, false><<<grid, kThreads, 0, st>>>(A, B, nullptr, nullptr, sums, P, C, act, (int)rpb);
+    return 0;
 }
 
 }  // namespace
 
-// sums[2,C] must be zero on entry (the wrapper memsets it on the same stream).
+// sums[2,C] is cleared by this call (stream-ordered memset) before the reduction.
 FDT_API int fdt_chan_reduce2(const void* a, const void* b, const void* out_act, void* g_store, float* sums,
                              int64_t P, int C, int act, cudaStream_t st) {
-    if (C % 8) return -1;
-    int grid; int rpb = pick_rows_per_block(P, C, &grid);
+    if (C % 8 || C <= 0) return -1;
     cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
-    if (out_act && act != ACT_NONE)
-        chan_reduce2_kernel<true><<<grid, kThreads, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
-            (const __nv_bfloat16*)out_act, (__nv_bfloat16*)g_store, sums, P, C, act, rpb);
-    else
-        chan_reduce2_kernel<false><<<grid, kThreads, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
-            nullptr, nullptr, sums, P, C, act, rpb);
+    const int vecC = C / 8;
+    if (vecC % 32 == 0) launch_reduce2<32>(a, b, out_act, g_store, sums, P, C, act, st);
+    else if (vecC % 16 == 0) launch_reduce2<16>(a, b, out_act, g_store, sums, P, C, act, st);
+    else if (vecC % 8 == 0) launch_reduce2<8>(a, b, out_act, g_store, sums, P, C, act, st);
+    else if (vecC % 4 == 0) launch_reduce2<4>(a, b, out_act, g_store, sums, P, C, act, st);
+    else if (vecC % 2 == 0) launch_reduce2<2>(a, b, out_act, g_store, sums, P, C, act, st);
+    else launch_reduce2<1>(a, b, out_act, g_store, sums, P, C, act, st);
     FDT_CHECK_LAUNCH();
     return 0;
 }
 
 FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res, void* out, const float* coef,
                                 int64_t P, int C, int act, cudaStream_t st) {
-    if (C % 8) return -1;
-    int grid; int rpb = pick_rows_per_block(P, C, &grid);
-    chan_affine_act_kernel<<<grid, kThreads, 0, st>>>((const __nv_bfloat16*)x1, (const __nv_bfloat16*)x2,
-        (const __nv_bfloat16*)res, (__nv_bfloat16*)out, coef, P, C, act, rpb);
+    if (C % 8 || C <= 0 || 3 * (size_t)C * sizeof(float) > 48 * 1024) return -1;
+    const int64_t total = P * (C / 8);
+    int64_t blocks = (total + kThreads * 4 - 1) / (kThreads * 4);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    const size_t smem = 3 * (size_t)C * sizeof(float);
+    auto X1 = (const __nv_bfloat16*)x1; auto X2 = (const __nv_bfloat16*)x2; auto R = (const __nv_bfloat16*)res;
+    auto O = (__nv_bfloat16*)out;
+    if (x2 && res) chan_affine_act_kernel<true, true><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
+    else if (x2) chan_affine_act_kernel<true, false><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
+    else if (res) chan_affine_act_kernel<false, true><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
+    else chan_affine_act_kernel<false, false><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -1,0 +1,280 @@
+// tcgen05 / TMEM / TMA GEMM and implicit-GEMM convolution for sm_100a.
+//
+//   D[M, N] = A[M, K] · B[N, K]ᵀ        bf16 operands (K-major), fp32 accumulation in tensor memory
+//
+// * plain mode : A is a row-major [M, K] matrix (linear layers, 1x1 convolutions on NHWC activations);
+// * conv mode  : A is gathered on the fly from an NHWC activation tensor — for every filter tap (r, s)
+//   and 64-channel slice the TMA engine loads the 4-D box {64 ch, W, bh rows, bn images} shifted by
+//   (s - pad, r - pad); out-of-bounds pixels are zero-filled by the hardware, which implements the
+//   padding.  B is the weight tensor physically laid out [Cout][kh][kw][Cin] (K-major, K = kh·kw·Cin).
+//
+// Parity: F.conv2d / F.linear call sites of the reference (resnet.py:83,108,204,221; transformer.py:
+// 168-176,213-226), which run cuDNN / cuBLAS kernels.
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads):
+//   warp 0      TMA producer   — fills a kStages-deep ring of {A 128x64, B BNx64} bf16 tiles (128B swizzle)
+//   warp 1      MMA issuer     — allocates BN TMEM columns, one elected lane issues tcgen05.mma
+//                                (M=128, N=BN, K=16) x4 per stage, tcgen05.commit frees the stage
+//   warps 2..5  epilogue       — tcgen05.ld the fp32 accumulator (warp w owns TMEM lanes 32·(w%4)..),
+//                                bias + activation, bf16 pack, 16-byte global stores; optional per-column
+//                                Σ and Σ² (batch-norm statistics) reduced by warp shuffles + atomics.
+#include "common.cuh"
+#include "sm100.cuh"
+#include <cstdio>
+#include <mutex>
+#include <unordered_map>
+
+using namespace fdt;
+using namespace sm100;
+
+namespace {
+
+constexpr int BM = 128, BK = 64, kThreads = 192;
+
+struct GemmParams {
+    int M, N, num_kb;
+    __nv_bfloat16* out;      // [M, N] bf16 (may be null)
+    float* out_f32;          // [M, N] fp32 (may be null)
+    const float* bias;       // [N] or null
+    float* sums;             // [2N] Σ, Σ² per column (atomics) or null
+    int act;
+    // conv geometry (conv mode only)
+    int H, W, bh, bn, pad, kw, cpb;   // cpb = Cin / 64 (k-blocks per tap)
+};
+
+template <int BN, int kStages>
+struct SmemLayout {
+    static constexpr int kABytes = BM * BK * 2;
+    static constexpr int kBBytes = BN * BK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kBarOff = kStages * kStageBytes;
+    static constexpr int kTotal = kBarOff + (2 * kStages + 1) * 8 + 16 + 1024;   // + alignment slack
+};
+
+template <int BN, int kStages, bool kConv>
+__global__ void __launch_bounds__(kThreads, 2)
+gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    using L = SmemLayout<BN, kStages>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<BN>(tmem_ptr);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int n0 = 0, h0 = 0;
+            if (kConv) {
+                if (p.bn == 1) { const int tpi = p.H / p.bh; n0 = m_tile / tpi; h0 = (m_tile % tpi) * p.bh; }
+                else { n0 = m_tile * p.bn; }
+            }
+            for (int kb = 0; kb < p.num_kb; ++kb) {
+                const int s = kb % kStages;
+                const uint32_t ph = (kb / kStages) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                uint8_t* sA = smem + s * L::kStageBytes;
+                uint8_t* sB = sA + L::kABytes;
+                mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+                if (kConv) {
+                    const int tap = kb / p.cpb, cb = kb - tap * p.cpb;
+                    const int r = tap / p.kw, sx = tap - r * p.kw;
+                    tma_load_4d(sA, &tmA, &full_bar[s], cb * BK, sx - p.pad, h0 + r - p.pad, n0);
+                } else {
+                    tma_load_2d(sA, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+                }
+                tma_load_2d(sB, &tmB, &full_bar[s], kb * BK, n_tile * BN);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
+            for (int kb = 0; kb < p.num_kb; ++kb) {
+                const int s = kb % kStages;
+                const uint32_t ph = (kb / kStages) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+                const uint32_t b_addr = a_addr + L::kABytes;
+                const uint64_t da = make_smem_desc(a_addr, 16, 1024);
+                const uint64_t db = make_smem_desc(b_addr, 16, 1024);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k)      // +32 bytes (= 2 in the >>4 address field) per K=16 slice
+                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(tmem_full_bar);
+        }
+    } else {
+        // ---------------- epilogue warps
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int row = m_tile * BM + q * 32 + lane;
+        const bool row_ok = row < p.M;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
+            tmem_ld_wait();
+            const int col0 = n_tile * BN + c * 32;
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            if (p.bias) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
+            }
+            if (p.act != ACT_NONE) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
+            }
+            if (p.sums) {
+                // per-column Σ and Σ² over the 32 rows of this warp: butterfly transpose-reduce —
+                // after 5 exchange steps lane j holds the total of column j.
+                float s1[32], s2[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) { const float t = row_ok ? v[j] : 0.f; s1[j] = t; s2[j] = t * t; }
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) {
+                    const bool upper = (lane & off) != 0;
+#pragma unroll
+                    for (int j = 0; j < off; ++j) {
+                        // keep half of the columns, hand the other half to the partner lane
+                        const float send1 = upper ? s1[j] : s1[j + off];
+                        const float send2 = upper ? s2[j] : s2[j + off];
+                        const float recv1 = __shfl_xor_sync(0xffffffffu, send1, off);
+                        const float recv2 = __shfl_xor_sync(0xffffffffu, send2, off);
+                        s1[j] = (upper ? s1[j + off] : s1[j]) + recv1;
+                        s2[j] = (upper ? s2[j + off] : s2[j]) + recv2;
+                    }
+                }
+                // lane L now owns column bit-reversed?  No: at each step `upper` lanes keep the upper half
+                // of the remaining columns, so lane L ends with column L.
+                atomicAdd(p.sums + col0 + lane, s1[0]);
+                atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
+            }
+            if (row_ok) {
+                if (p.out) {
+                    __nv_bfloat16* o = p.out + (size_t)row * p.N + col0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) st8(o + j, pack8(v + j));
+                }
+                if (p.out_f32) {
+                    float* o = p.out_f32 + (size_t)row * p.N + col0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
+// ------------------------------------------------------------------ host side: tensor maps
+// cuTensorMapEncodeTiled is a driver-API function; it is resolved through the runtime
+// (cudaGetDriverEntryPoint) so the library has no link-time dependency on libcuda and can be
+// loaded (and built) on a machine without a GPU driver.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+#define cuTensorMapEncodeTiled(...) (get_encode() ? get_encode()(__VA_ARGS__) : CUDA_ERROR_NOT_INITIALIZED)
+
+bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint32_t box_inner, uint32_t box_outer) {
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {inner * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = cuTensorMapEncodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+bool encode_nhwc(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, int bw, int bh, int bn) {
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Nb};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = cuTensorMapEncodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+template <int BN, bool kConv>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t st) {
+    constexpr int kStages = (BN == 128) ? 3 : 4;      // ~96 KB of tiles → two CTAs per SM overlap prologue/epilogue
+    using L = SmemLayout<BN, kStages>;
+    auto kern = gemm_nt_kernel<BN, kStages, kConv>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    dim3 grid((p.M + BM - 1) / BM, p.N / BN);
+    kern<<<grid, kThreads, L::kTotal, st>>>(tmA, tmB, p);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace
+
+// out[M,N] (bf16 and/or fp32) = act(A[M,K] · B[N,K]ᵀ + bias).  K % 64 == 0, N % 64 == 0, 16-byte aligned rows.
+// sums (optional, [2N], zeroed by the caller): per-column Σ and Σ² of the stored values.
+FDT_API int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out_f32, const float* bias, float* sums,
+                        int M, int N, int K, int act, cudaStream_t st) {
+    if (M <= 0 || N % 64 || K % 64 || K <= 0) return -1;
+    CUtensorMap tmA, tmB;
+    const int BN = (N % 128 == 0) ? 128 : 64;
+    if (!encode_2d(&tmA, A, K, M, BK, BM) || !encode_2d(&tmB, B, K, N, BK, BN)) return -4;
+    GemmParams p{};
+    p.M = M; p.N = N; p.num_kb = K / BK; p.out = (__nv_bfloat16*)out_bf16; p.out_f32 = out_f32; p.bias = bias;
+    p.sums = sums; p.act = act;
+    return BN == 128 ? launch<128, false>(tmA, tmB, p, st) : launch<64, false>(tmA, tmB, p, st);
+}
+
+// y[Nb,H,W,Cout] = conv(x[Nb,H,W,Cin], w[Cout,kh,kw,Cin]), stride 1, "same" padding (pad = kh/2), NHWC bf16.
+// Cin % 64 == 0, Cout % 64 == 0, W a power of two <= 128, H·W a multiple of the 128-pixel tile or a divisor of it.
+FDT_API int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int Nb, int H, int W, int Cin, int Cout,
+                         int ksize, int pad, cudaStream_t st) {
+    if (Cin % 64 || Cout % 64 || W > 128 || (W & (W - 1)) || (128 % W)) return -1;
+    int bh = 128 / W, bn = 1;
+    if (bh > H) { if (bh % H) return -1; bn = bh / H; bh = H; }
+    else if (H % bh) return -1;
+    const int M = Nb * H * W;
+    CUtensorMap tmA, tmB;
+    const int BN = (Cout % 128 == 0) ? 128 : 64;
+    const int K = ksize * ksize * Cin;
+    if (!encode_nhwc(&tmA, x, Nb, H, W, Cin, W, bh, bn) || !encode_2d(&tmB, w, K, Cout, BK, BN)) return -4;
+    GemmParams p{};
+    p.M = M; p.N = Cout; p.num_kb = K / BK; p.out = (__nv_bfloat16*)y; p.sums = sums; p.act = ACT_NONE;
+    p.H = H; p.W = W; p.bh = bh; p.bn = bn; p.pad = pad; p.kw = ksize; p.cpb = Cin / BK;
+    return BN == 128 ? launch<128, true>(tmA, tmB, p, st) : launch<64, true>(tmA, tmB, p, st);
+}

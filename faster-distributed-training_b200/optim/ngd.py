@@ -133,6 +133,18 @@ def _fisher_update(fb: FactorBatch, J, K, L, trXXt):
     return fisher_update_torch(fb, J, K, L, trXXt)
 
 
+def _split_factor(N: int, target: int = 2048) -> int:
+    """Split count for the long reduction J = HᵀX (over the N rows).  Skinny factors (e.g. the 3-wide
+    kernel axes of a conv weight: N ~ 8e5, D = 3, R = 2) would otherwise run as a single CTA walking
+    the whole reduction; S independent partial products summed afterwards keep the GPU busy."""
+    if N <= 4 * target:
+        return 1
+    S = N // target
+    while S > 1 and N % S:
+        S -= 1
+    return S
+
+
 def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
     """J = HᵀX, L, K = JJᵀ into the factor batch's persistent work buffers."""
     W = fb.W
@@ -147,14 +159,27 @@ def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
         fb.d1 = torch.empty(n, R, **kw)
         fb.rho1 = torch.empty(n, **kw)
         fb.tr = torch.empty(n, **kw)
-    if left:   # Xm: [n, D, N], H: [n, R, N]
-        torch.bmm(H, Xm.transpose(1, 2), out=fb.J)
+    S = _split_factor(fb.N)
+    if left:   # Xm: [n, D, N], H: [n, R, N];  J = H Xᵀ reduces over N
+        if S > 1:
+            n, R, D, c = fb.n, fb.R, fb.D, fb.N // S
+            Hs = H.reshape(n, R, S, c).transpose(1, 2).reshape(n * S, R, c)
+            Xs = Xm.reshape(n, D, S, c).transpose(1, 2).reshape(n * S, D, c)
+            torch.sum(torch.bmm(Hs, Xs.transpose(1, 2)).view(n, S, R, D), dim=1, out=fb.J)
+        else:
+            torch.bmm(H, Xm.transpose(1, 2), out=fb.J)
         if fb.N > fb.D:
             torch.bmm(fb.J, W.transpose(1, 2), out=fb.L)
         else:
             torch.bmm(H, H.transpose(1, 2), out=fb.L)
-    else:      # Xm: [n, N, D], H: [n, N, R]
-        torch.bmm(H.transpose(1, 2), Xm, out=fb.J)
+    else:      # Xm: [n, N, D], H: [n, N, R];  J = Hᵀ X reduces over N
+        if S > 1:
+            n, R, D, c = fb.n, fb.R, fb.D, fb.N // S
+            Hs = H.reshape(n * S, c, R)
+            Xs = Xm.reshape(n * S, c, D)
+            torch.sum(torch.bmm(Hs.transpose(1, 2), Xs).view(n, S, R, D), dim=1, out=fb.J)
+        else:
+            torch.bmm(H.transpose(1, 2), Xm, out=fb.J)
         if fb.N > fb.D:
             torch.bmm(fb.J, W.transpose(1, 2), out=fb.L)
         else:

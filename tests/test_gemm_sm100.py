@@ -1,0 +1,71 @@
+"""tcgen05 GEMM / implicit-GEMM convolution against fp32 PyTorch references."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12)).item()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 64, 128), (1000, 256, 512), (8192, 512, 1024), (77, 1536, 512)])
+@pytest.mark.parametrize("act,bias", [("none", False), ("relu", True), ("gelu", True)])
+def test_gemm_nt(M, N, K, act, bias):
+    from fdt.ops import gemm_sm100 as g
+    torch.manual_seed(0)
+    a = (torch.randn(M, K, device="cuda") / math.sqrt(K)).bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bi = torch.randn(N, device="cuda") if bias else None
+    out = g.gemm_nt(a, b, bi, act)
+    assert out is not None and out.dtype == torch.bfloat16
+    ref = a.float() @ b.float().t()
+    if bias:
+        ref = ref + bi
+    ref = {"none": lambda t: t, "relu": F.relu, "gelu": F.gelu}[act](ref)
+    assert _rel(out, ref) < 6e-3, _rel(out, ref)
+    assert (out.float() - ref).abs().max() < 0.05 * max(ref.abs().max().item(), 1.0)
+
+
+def test_gemm_nt_fp32_out_and_stats():
+    from fdt.ops import gemm_sm100 as g
+    torch.manual_seed(1)
+    M, N, K = 4096 + 64, 256, 192
+    a = (torch.randn(M, K, device="cuda") / math.sqrt(K)).bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    sums = torch.zeros(2 * N, device="cuda")
+    out = g.gemm_nt(a, b, None, "none", torch.float32, sums)
+    ref = a.float() @ b.float().t()
+    assert _rel(out, ref) < 1e-4
+    assert _rel(sums[:N], ref.sum(0)) < 1e-3 and _rel(sums[N:], (ref * ref).sum(0)) < 1e-3
+
+
+@pytest.mark.parametrize("N,C,O,HW,k", [(4, 64, 64, 32, 3), (8, 128, 128, 16, 3), (16, 256, 256, 8, 3), (16, 512, 512, 4, 3),
+                                          (2, 64, 128, 32, 3), (4, 64, 256, 32, 1), (9, 128, 64, 16, 3)])
+def test_conv_fwd(N, C, O, HW, k):
+    from fdt.ops import gemm_sm100 as g
+    torch.manual_seed(2)
+    x = torch.randn(N, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(O, C, k, k, device="cuda") / math.sqrt(C * k * k)).bfloat16().contiguous(memory_format=torch.channels_last)
+    sums = torch.zeros(2 * O, device="cuda")
+    y = g.conv_fwd(x, w, 1, k // 2, sums)
+    assert y is not None and y.shape == (N, O, HW, HW) and y.is_contiguous(memory_format=torch.channels_last)
+    ref = F.conv2d(x.float(), w.float(), padding=k // 2)
+    assert _rel(y, ref) < 6e-3, _rel(y, ref)
+    assert _rel(sums[:O], ref.sum((0, 2, 3))) < 5e-3 or (sums[:O] - ref.sum((0, 2, 3))).abs().max() < 0.5
+    assert _rel(sums[O:], (ref * ref).sum((0, 2, 3))) < 5e-3
+
+
+@pytest.mark.parametrize("N,C,O,HW,k", [(4, 64, 64, 32, 3), (8, 256, 128, 8, 3), (4, 128, 256, 16, 1)])
+def test_conv_dgrad(N, C, O, HW, k):
+    from fdt.ops import gemm_sm100 as g
+    torch.manual_seed(3)
+    w = (torch.randn(O, C, k, k, device="cuda") / math.sqrt(C * k * k)).bfloat16().contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(N, O, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    dx = g.conv_dgrad(dy, w, (N, C, HW, HW), 1, k // 2)
+    assert dx is not None
+    ref = F.conv_transpose2d(dy.float(), w.float(), padding=k // 2)
+    assert _rel(dx, ref) < 6e-3, _rel(dx, ref)

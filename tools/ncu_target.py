@@ -1,0 +1,39 @@
+#!/usr/bin/env python
+"""Tiny single-kernel driver for `ncu` captures (one GPU, a handful of launches).
+usage: ncu_target.py {conv1x1|conv3x3|gemm|chan_affine|chan_reduce|ngd_eig}"""
+import math
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from fdt.ops import gemm_sm100 as g  # noqa: E402
+from fdt.ops._lib import call, i64  # noqa: E402
+
+what = sys.argv[1] if len(sys.argv) > 1 else "conv1x1"
+B = 128
+if what in ("conv1x1", "conv3x3"):
+    C, O, HW, k = (64, 256, 32, 1) if what == "conv1x1" else (128, 128, 16, 3)
+    x = torch.randn(B, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(O, C, k, k, device="cuda") / math.sqrt(C * k * k)).bfloat16().contiguous(memory_format=torch.channels_last)
+    for _ in range(5):
+        y = g.conv_fwd(x, w, 1, k // 2)
+elif what == "gemm":
+    a = torch.randn(8192, 8192, device="cuda").bfloat16()
+    b = torch.randn(8192, 8192, device="cuda").bfloat16()
+    for _ in range(4):
+        y = g.gemm_nt(a, b)
+elif what in ("chan_affine", "chan_reduce"):
+    P, C = 131072, 256
+    y = torch.randn(P, C, device="cuda").bfloat16()
+    o = torch.empty_like(y)
+    sums = torch.zeros(2 * C, device="cuda")
+    coef = torch.randn(3 * C, device="cuda")
+    for _ in range(5):
+        if what == "chan_affine":
+            call("fdt_chan_affine_act", y, None, None, o, coef, i64(P), C, 1)
+        else:
+            call("fdt_chan_reduce2", y, y, None, None, sums, i64(P), C, 0)
+torch.cuda.synchronize()
+print("ok", what)
