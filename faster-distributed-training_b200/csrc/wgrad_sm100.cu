@@ -1,0 +1,250 @@
+// Weight-gradient GEMM on tcgen05 with MN-major operands and split-K.
+//
+//   dW[co, tap, ci] = Σ_p dY[p, co] · X[p ⊕ tap, ci]          (p = pixel / token index, fp32 result)
+//
+// The reduction runs over pixels, and both operands are stored pixel-major with the channel index
+// contiguous (NHWC) — i.e. the *M/N* index is the contiguous one.  tcgen05.mma reads such tiles directly
+// (instruction-descriptor bits a_major = b_major = MN), so no transposed copy of the activations is ever
+// made: TMA drops {64 pixels x 64 channels} boxes (128-byte rows, 128B swizzle) into shared memory and
+// the matrix descriptors walk them 16 pixel-rows (one MMA K-step) at a time.  For a 3x3 filter the X box
+// of tap (r, s) is the 4-D NHWC box shifted by (s - pad, r - pad); the hardware zero-fills the halo.
+//
+// The pixel range is split over blockIdx.y (split-K) so that also a 64x64x9 weight fills the GPU; every
+// CTA adds its 128 x BN fp32 partial tile into dW (physical layout [Cout][kh][kw][Cin], the layout the
+// flat gradient buffer uses) with vectorised red.global.add.
+//
+// Parity: the dW half of convolution_backward (resnet.py:21-34, a cuDNN call on transposed tensors) and
+// the `grad_out_transpose @ activated` products of MLPScratch / nn.Linear (transformer.py:318-334).
+#include "common.cuh"
+#include "sm100.cuh"
+#include <mutex>
+
+using namespace fdt;
+using namespace sm100;
+
+namespace {
+
+constexpr int BM = 128, BKP = 64 /* pixels per stage */, kThreads = 192;
+
+struct WgradParams {
+    int Cout, Cin, taps, kw, pad;
+    int num_kb;            // total pixel blocks (P / 64)
+    int kb_per_split;
+    float* dw;             // [Cout][taps][Cin] fp32, accumulated into
+    int H, W, bh, bn;      // conv geometry of the 64-pixel box
+    int tiles_n;           // Cin tiles
+};
+
+template <int BN, int kStages>
+struct WSmem {
+    static constexpr int kABytes = BM * BKP * 2;       // two 8 KB atoms (64 px x 64 co)
+    static constexpr int kBBytes = BN * BKP * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kBarOff = kStages * kStageBytes;
+    static constexpr int kTotal = kBarOff + (2 * kStages + 1) * 8 + 16 + 1024;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int BN, int kStages, bool kConv>
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WgradParams p) {
+    using L = WSmem<BN, kStages>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // blockIdx.x = (m_tile * tiles_n + n_tile) * taps + tap ; blockIdx.y = split
+    const int tap = blockIdx.x % p.taps;
+    const int mn = blockIdx.x / p.taps;
+    const int n_tile = mn % p.tiles_n, m_tile = mn / p.tiles_n;
+    const int kb0 = blockIdx.y * p.kb_per_split;
+    const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+    const int nkb = kb1 - kb0;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmDY);
+        prefetch_tmap(&tmX);
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<BN>(tmem_ptr);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (nkb > 0) {
+        if (warp == 0) {
+            if (lane == 0) {
+                const int r = tap / p.kw, sx = tap - r * p.kw;
+                for (int i = 0; i < nkb; ++i) {
+                    const int kb = kb0 + i;
+                    const int s = i % kStages;
+                    const uint32_t ph = (i / kStages) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* sA = smem + s * L::kStageBytes;
+                    uint8_t* sB = sA + L::kABytes;
+                    mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+                    // A: dY[p0 .. p0+64, co0 .. co0+128] as two 64-channel atoms
+                    tma_load_2d(sA, &tmDY, &full_bar[s], m_tile * BM, kb * BKP);
+                    tma_load_2d(sA + 8192, &tmDY, &full_bar[s], m_tile * BM + 64, kb * BKP);
+                    // B: X (shifted by the tap) [64 px, ci0 .. ci0+BN]
+                    if (kConv) {
+                        int n0, h0;
+                        if (p.bn == 1) { const int tpi = p.H / p.bh; n0 = kb / tpi; h0 = (kb % tpi) * p.bh; }
+                        else { n0 = kb * p.bn; h0 = 0; }
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_4d(sB + j * 8192, &tmX, &full_bar[s], n_tile * BN + j * 64, sx - p.pad, h0 + r - p.pad, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(sB + j * 8192, &tmX, &full_bar[s], n_tile * BN + j * 64, kb * BKP);
+                    }
+                }
+            }
+        } else if (warp == 1) {
+            if (lane == 0) {
+                constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 1, 1);      // both operands MN-major
+                for (int i = 0; i < nkb; ++i) {
+                    const int s = i % kStages;
+                    const uint32_t ph = (i / kStages) & 1;
+                    mbar_wait(&full_bar[s], ph);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+                    const uint32_t b_addr = a_addr + L::kABytes;
+                    // MN-major, 128B swizzle: 8-pixel-row groups 1024 B apart (SBO), 64-channel atoms 8192 B apart (LBO)
+                    const uint64_t da = make_smem_desc(a_addr, 8192, 1024);
+                    const uint64_t db = make_smem_desc(b_addr, 8192, 1024);
+#pragma unroll
+                    for (int k = 0; k < BKP / 16; ++k)     // 16 pixel rows = 2048 B = 128 in the >>4 address field
+                        umma_bf16(tmem_base, da + 128 * k, db + 128 * k, idesc, (i | k) != 0);
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(tmem_full_bar);
+            }
+        } else {
+            mbar_wait(tmem_full_bar, 0);
+            tc_fence_after();
+            const int q = warp & 3;
+            const int co = m_tile * BM + q * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
+                tmem_ld_wait();
+                if (co < p.Cout) {
+                    float* dst = p.dw + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c * 32;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        red_add_v4(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                   __uint_as_float(r[j + 3]));
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+bool encode_pc(CUtensorMap* m, const void* ptr, uint64_t C, uint64_t P) {   // [P, C] bf16, box 64 ch x 64 px
+    if (!get_encode()) return false;
+    cuuint64_t dims[2] = {C, P};
+    cuuint64_t strides[1] = {C * 2};
+    cuuint32_t box[2] = {64, 64};
+    cuuint32_t estr[2] = {1, 1};
+    return get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+bool encode_nhwc64(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, int bw, int bh, int bn) {
+    if (!get_encode()) return false;
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Nb};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    return get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int BN, bool kConv>
+int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream_t st) {
+    constexpr int kStages = 4;
+    using L = WSmem<BN, kStages>;
+    auto kern = wgrad_kernel<BN, kStages, kConv>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    const int tiles_m = (p.Cout + BM - 1) / BM;
+    p.tiles_n = p.Cin / BN;
+    const int tiles = tiles_m * p.tiles_n * p.taps;
+    int splits = (148 * 2 + tiles - 1) / tiles;            // ~2 waves worth of CTAs
+    if (splits > p.num_kb) splits = p.num_kb;
+    if (splits < 1) splits = 1;
+    p.kb_per_split = (p.num_kb + splits - 1) / splits;
+    splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+    kern<<<dim3(tiles, splits), kThreads, L::kTotal, st>>>(a, b, p);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace
+
+// dw[Cout][k][k][Cin] (fp32) += dY[Nb,H,W,Cout]ᵀ ⊛ X[Nb,H,W,Cin]; stride 1, pad = k/2, NHWC bf16.
+// Cin % 64 == 0; W a power of two <= 64; (Nb·H·W) % 64 == 0.
+FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
+                           int pad, cudaStream_t st) {
+    if (Cin % 64 || Cout % 8 || W > 64 || (W & (W - 1)) || (64 % W)) return -1;
+    int bh = 64 / W, bn = 1;
+    if (bh > H) { if (bh % H) return -1; bn = bh / H; bh = H; }
+    else if (H % bh) return -1;
+    const int64_t P = (int64_t)Nb * H * W;
+    if (P % 64 || (bn > 1 && Nb % bn)) return -1;
+    CUtensorMap tmDY, tmX;
+    if (!encode_pc(&tmDY, dy, Cout, P)) return -4;
+    WgradParams p{};
+    p.Cout = Cout; p.Cin = Cin; p.taps = ksize * ksize; p.kw = ksize; p.pad = pad; p.num_kb = (int)(P / 64); p.dw = dw;
+    p.H = H; p.W = W; p.bh = bh; p.bn = bn;
+    const bool wide = (Cin % 128 == 0);
+    if (ksize == 1) {
+        if (!encode_pc(&tmX, x, Cin, P)) return -4;
+        return wide ? launch<128, false>(tmDY, tmX, p, st) : launch<64, false>(tmDY, tmX, p, st);
+    }
+    if (!encode_nhwc64(&tmX, x, Nb, H, W, Cin, W, bh, bn)) return -4;
+    return wide ? launch<128, true>(tmDY, tmX, p, st) : launch<64, true>(tmDY, tmX, p, st);
+}
+
+// dw[N][K] (fp32) += dY[M,N]ᵀ · X[M,K]   (linear layers).  K % 64 == 0, N % 8 == 0, M % 64 == 0.
+FDT_API int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, cudaStream_t st) {
+    if (K % 64 || N % 8 || M % 64) return -1;
+    CUtensorMap tmDY, tmX;
+    if (!encode_pc(&tmDY, dy, N, M) || !encode_pc(&tmX, x, K, M)) return -4;
+    WgradParams p{};
+    p.Cout = N; p.Cin = K; p.taps = 1; p.kw = 1; p.pad = 0; p.num_kb = M / 64; p.dw = dw;
+    return (K % 128 == 0) ? launch<128, false>(tmDY, tmX, p, st) : launch<64, false>(tmDY, tmX, p, st);
+}

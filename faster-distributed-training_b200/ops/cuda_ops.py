@@ -119,14 +119,26 @@ def _conv_fwd(x, w16, stride, padding):
     return F.conv2d(x, w16, stride=stride, padding=padding)
 
 
-def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape):
+def _grad_slot(weight) -> Optional[torch.Tensor]:
+    """The parameter's slice of the flat gradient buffer, as the physically contiguous
+    [Cout, kh, kw, Cin] fp32 tensor the wgrad kernel can accumulate into directly."""
+    if getattr(weight, "_fdt_flat", None) is None or weight.grad is None or weight.dim() != 4:
+        return None
+    g = weight.grad.permute(0, 2, 3, 1)
+    return g if g.is_contiguous() and g.dtype == torch.float32 else None
+
+
+def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=None):
     dx = dw = None
     if _native_gemm():
         from . import gemm_sm100
         if need_dx:
             dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding)
         if need_dw:
-            dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding)
+            slot = _grad_slot(weight) if weight is not None else None
+            dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, slot)
+            if dw is True:          # accumulated straight into the flat gradient buffer
+                need_dw, dw = False, None
     if (need_dx and dx is None) or (need_dw and dw is None):
         mask = [need_dx and dx is None, need_dw and dw is None, False]
         rdx, rdw, _ = torch.ops.aten.convolution_backward(dy, x, w16, None, [stride, stride], [padding, padding],
@@ -183,7 +195,7 @@ class _ConvBNAct(torch.autograd.Function):
         call("fdt_bn_finalize_bwd", sums, bnctx, coef, dgamma, dbeta, C, float(P), form)
         dy = torch.empty_like(y)
         call("fdt_chan_affine_act", g, y, None, dy, coef, i64(P), C, 0)
-        dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape)
+        dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape, weight)
         return dx, dw, dgamma, dbeta, (g if has_res else None), None
 
 

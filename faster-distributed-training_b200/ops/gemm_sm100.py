@@ -89,9 +89,9 @@ def conv_dgrad(dy: torch.Tensor, w16: torch.Tensor, x_shape, stride: int, paddin
     return conv_fwd(dy, wt, stride, padding)
 
 
-def conv_wgrad(dy, x, w_shape, stride, padding) -> Optional[torch.Tensor]:
+def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None):
     from . import wgrad_sm100
-    return wgrad_sm100.conv_wgrad(dy, x, w_shape, stride, padding)
+    return wgrad_sm100.conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into)
 
 
 def linear(x, weight, bias, act):

@@ -16,19 +16,47 @@ def available() -> bool:
         return False
 
 
-def conv_wgrad(dy, x, w_shape, stride, padding) -> Optional[torch.Tensor]:
-    if not available():
+def _conv_ok(x_shape, w_shape, stride, padding) -> bool:
+    Cout, Cin, kh, kw = w_shape
+    N, _, H, W = x_shape
+    if stride != 1 or kh != kw or padding != kh // 2 or Cin % 64 or Cout % 8:
+        return False
+    if W > 64 or W & (W - 1) or 64 % W:
+        return False
+    bh = 64 // W
+    if bh > H:
+        if bh % H or N % (bh // H):
+            return False
+    elif H % bh:
+        return False
+    return (N * H * W) % 64 == 0
+
+
+def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """fp32 weight gradient of a stride-1 "same" convolution.  ``accumulate_into`` (a physically
+    [Cout, kh, kw, Cin]-contiguous fp32 tensor, e.g. the parameter's slice of the flat gradient buffer)
+    receives the result by atomic accumulation and ``True`` is returned; otherwise a fresh tensor in the
+    logical [Cout, Cin, kh, kw] view comes back."""
+    if not available() or not _conv_ok(x.shape, w_shape, stride, padding):
         return None
     Cout, Cin, kh, kw = w_shape
     N, _, H, W = x.shape
-    if stride != 1 or kh != kw or padding != kh // 2 or Cin % 64 or Cout % 64:
-        return None
-    if W > 64 or W & (W - 1) or 64 % W:
-        return None
-    bh = 64 // W
-    if (bh > H and bh % H) or (bh <= H and H % bh):
-        return None
-    # fp32 gradient in the physical [Cout, kh, kw, Cin] layout, returned as the logical [Cout, Cin, kh, kw] view
+    if accumulate_into is not None:
+        call("fdt_conv_wgrad", dy, x, accumulate_into, N, H, W, Cin, Cout, kh, padding)
+        return True
     dw = torch.zeros((Cout, kh, kw, Cin), dtype=torch.float32, device=x.device)
     call("fdt_conv_wgrad", dy, x, dw, N, H, W, Cin, Cout, kh, padding)
     return dw.permute(0, 3, 1, 2)
+
+
+def linear_wgrad(gz: torch.Tensor, x16: torch.Tensor) -> Optional[torch.Tensor]:
+    """dW[N, K] = gzᵀ[N, M] · x[M, K] in fp32 (gz, x bf16 row-major)."""
+    if not available():
+        return None
+    M, N = gz.shape
+    K = x16.shape[1]
+    if K % 64 or N % 8 or M % 64 or not (gz.is_contiguous() and x16.is_contiguous()):
+        return None
+    dw = torch.zeros(N, K, dtype=torch.float32, device=gz.device)
+    call("fdt_linear_wgrad", gz, x16, dw, M, N, K)
+    return dw

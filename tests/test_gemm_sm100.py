@@ -69,3 +69,48 @@ def test_conv_dgrad(N, C, O, HW, k):
     assert dx is not None
     ref = F.conv_transpose2d(dy.float(), w.float(), padding=k // 2)
     assert _rel(dx, ref) < 6e-3, _rel(dx, ref)
+
+
+@pytest.mark.parametrize("N,C,O,HW,k", [(4, 64, 64, 32, 3), (8, 128, 128, 16, 3), (16, 256, 256, 8, 3), (16, 512, 512, 4, 3),
+                                          (4, 64, 256, 32, 1), (8, 256, 64, 16, 1), (8, 128, 192, 8, 3)])
+def test_conv_wgrad(N, C, O, HW, k):
+    from fdt.ops import wgrad_sm100 as wg
+    torch.manual_seed(4)
+    x = torch.randn(N, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(N, O, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    dw = wg.conv_wgrad(dy, x, (O, C, k, k), 1, k // 2)
+    assert dw is not None and dw.shape == (O, C, k, k) and dw.dtype == torch.float32
+    w = torch.zeros(O, C, k, k, device="cuda", requires_grad=True)
+    F.conv2d(x.float(), w, padding=k // 2).backward(dy.float())
+    assert _rel(dw, w.grad) < 2e-3, _rel(dw, w.grad)
+    # accumulate-into form adds on top of existing contents
+    slot = torch.ones(O, k, k, C, device="cuda")
+    assert wg.conv_wgrad(dy, x, (O, C, k, k), 1, k // 2, slot) is True
+    assert _rel(slot.permute(0, 3, 1, 2) - 1.0, w.grad) < 2e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(8192, 512, 512), (8192, 1024, 512), (64, 8, 64), (4096, 1536, 192)])
+def test_linear_wgrad(M, N, K):
+    from fdt.ops import wgrad_sm100 as wg
+    torch.manual_seed(5)
+    gz = torch.randn(M, N, device="cuda").bfloat16()
+    x = torch.randn(M, K, device="cuda").bfloat16()
+    dw = wg.linear_wgrad(gz, x)
+    assert dw is not None
+    ref = gz.float().t() @ x.float()
+    assert _rel(dw, ref) < 2e-3, _rel(dw, ref)
+
+
+def test_linear_autograd_native():
+    from fdt import ops
+    torch.manual_seed(6)
+    x = torch.randn(4, 128, 512, device="cuda", requires_grad=True)
+    w = (torch.randn(1024, 512, device="cuda") / 22).requires_grad_(True)
+    b = torch.randn(1024, device="cuda").requires_grad_(True)
+    g = torch.randn(4, 128, 1024, device="cuda")
+    out = ops.linear(x, w, b, "gelu")
+    out.backward(g.bfloat16())
+    xr, wr, br = [t.detach().clone().requires_grad_(True) for t in (x, w, b)]
+    ops.ref.linear(xr.bfloat16().float(), wr.bfloat16().float(), br, "gelu").backward(g.bfloat16().float())
+    assert _rel(out, ops.ref.linear(x.bfloat16().float(), w.bfloat16().float(), b, "gelu")) < 1e-2
+    assert _rel(w.grad, wr.grad) < 2e-2 and _rel(b.grad, br.grad) < 2e-2 and _rel(x.grad, xr.grad) < 2e-2
