@@ -1,0 +1,223 @@
+// In-kernel collectives over NVLink peer memory (symmetric heap), fused with the adjacent
+// element-wise work of the training step.
+//
+// Every rank maps every peer's copy of the flat buffer (torch symmetric memory does the CUDA-VMM
+// handle exchange; see fdt/parallel/symm.py).  The kernels below read and write those peer
+// addresses directly — P2P ld/st through NVSwitch, or `multimem` (in-switch reduction / multicast,
+// NVLS) when a multicast mapping exists — so a collective is ONE launch with the scaling, the
+// gradient-norm partial and the bf16 operand cast folded into the same pass:
+//
+//   fdt_comm_all_reduce_mean   DDP gradients: two-shot all-reduce; rank r reduces chunk r across all
+//                              peers, scales by 1/world, accumulates Σg² (for clipping) and stores the
+//                              result into every peer's buffer.
+//   fdt_comm_reduce_scatter_mean  FSDP gradients: rank r reduces its own region only (+ scale + Σg²,
+//                              the Σ is made global through peer atomics — the norm the reference gets
+//                              wrong under FSDP, transformer_test.py:269).
+//   fdt_comm_all_gather_cast   FSDP parameters: pull every peer's region into the local fp32 buffer and
+//                              emit the bf16 operand shadow in the same pass.
+//
+// Parity: DDP's bucketed NCCL all-reduce (resnet50_test.py:716), FSDP's all-gather / reduce-scatter
+// (transformer_test.py:387-392) and the separate clip_grad_norm_ pass.
+//
+// Synchronisation: per-block flag barriers in a dedicated symmetric signal buffer
+// (system-scope CAS: set my slot on the peer, consume the peer's slot on me).  Block b only talks
+// to block b of the peers, so grids must be identical on all ranks and small enough to be
+// co-resident (they are: <= 64 blocks).
+#include "common.cuh"
+using namespace fdt;
+
+namespace {
+
+constexpr int kMaxWorld = 8;
+constexpr int kBlock = 512;
+
+struct CommCtx {
+    float* buf[kMaxWorld];        // peer views of the data buffer
+    uint32_t* sig[kMaxWorld];     // peer views of the signal buffer
+    float* scratch[kMaxWorld];    // peer views of a small fp32 scratch (Σg² slots)
+    float* mc;                    // multicast view of the data buffer (NVLS) or null
+    int rank, world;
+    int pad0, pad1;
+};
+
+__device__ __forceinline__ void block_barrier(const CommCtx& c, int base) {
+    __syncthreads();
+    if (threadIdx.x < c.world) {
+        __threadfence_system();
+        uint32_t* remote = c.sig[threadIdx.x] + base + c.rank;
+        while (atomicCAS_system(remote, 0u, 1u) != 0u) {}
+        uint32_t* local = c.sig[c.rank] + base + threadIdx.x;
+        while (atomicCAS_system(local, 1u, 0u) != 1u) {}
+        __threadfence_system();
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_cg(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ void st_cg(float* p, float4 v) { __stcg(reinterpret_cast<float4*>(p), v); }
+
+__device__ __forceinline__ float4 mc_ld_reduce(const float* p) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st(float* p, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ float block_sum512(float v) {
+    __shared__ float red[kBlock / 32];
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = 0.f;
+    if (threadIdx.x < kBlock / 32) t = red[threadIdx.x];
+    if (threadIdx.x < 32) t = warp_sum(t);
+    return t;      // valid in thread 0
+}
+
+// kMode 0: all-reduce (result to every peer); 1: reduce-scatter (result to the local region only).
+// [lo, hi) is the element range this rank reduces (multiple of 4 elements, 16-byte aligned).
+template <int kMode, bool kMulticast>
+__global__ void __launch_bounds__(kBlock)
+reduce_kernel(const CommCtx c, int64_t lo, int64_t hi, float scale) {
+    const int nb = gridDim.x;
+    block_barrier(c, blockIdx.x * c.world);                                        // peers' data is complete
+    float sq = 0.f;
+    const int64_t stride = (int64_t)nb * kBlock * 4;
+    for (int64_t i = lo + ((int64_t)blockIdx.x * kBlock + threadIdx.x) * 4; i < hi; i += stride * 2) {
+        const int64_t j = i + stride;
+        const bool two = j < hi;
+        float4 a0, a1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (kMulticast) {
+            a0 = mc_ld_reduce(c.mc + i);
+            if (two) a1 = mc_ld_reduce(c.mc + j);
+        } else {
+            float4 v0[kMaxWorld], v1[kMaxWorld];
+#pragma unroll
+            for (int p = 0; p < kMaxWorld; ++p) {
+                if (p < c.world) {
+                    v0[p] = ld_cg(c.buf[p] + i);
+                    if (two) v1[p] = ld_cg(c.buf[p] + j);
+                }
+            }
+            a0 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int p = 0; p < kMaxWorld; ++p) {
+                if (p < c.world) {
+                    a0.x += v0[p].x; a0.y += v0[p].y; a0.z += v0[p].z; a0.w += v0[p].w;
+                    if (two) { a1.x += v1[p].x; a1.y += v1[p].y; a1.z += v1[p].z; a1.w += v1[p].w; }
+                }
+            }
+        }
+        a0.x *= scale; a0.y *= scale; a0.z *= scale; a0.w *= scale;
+        a1.x *= scale; a1.y *= scale; a1.z *= scale; a1.w *= scale;
+        sq += a0.x * a0.x + a0.y * a0.y + a0.z * a0.z + a0.w * a0.w;
+        sq += a1.x * a1.x + a1.y * a1.y + a1.z * a1.z + a1.w * a1.w;
+        if (kMode == 1) {
+            st_cg(c.buf[c.rank] + i, a0);
+            if (two) st_cg(c.buf[c.rank] + j, a1);
+        } else if (kMulticast) {
+            mc_st(c.mc + i, a0);
+            if (two) mc_st(c.mc + j, a1);
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxWorld; ++p) {
+                if (p < c.world) {
+                    st_cg(c.buf[p] + i, a0);
+                    if (two) st_cg(c.buf[p] + j, a1);
+                }
+            }
+        }
+    }
+    // Σg² of my range → every rank's scratch slot (so each rank ends with the global norm)
+    sq = block_sum512(sq);
+    if (threadIdx.x == 0) {
+        for (int p = 0; p < c.world; ++p) atomicAdd_system(c.scratch[p], sq);
+    }
+    block_barrier(c, (nb + blockIdx.x) * c.world);                                 // all writes have landed
+}
+
+// Pull region p ([p*region, (p+1)*region)) from peer p for every p != rank, write the local fp32 buffer
+// and the bf16 shadow of the WHOLE buffer (own region included).
+__global__ void __launch_bounds__(kBlock)
+all_gather_cast_kernel(const CommCtx c, int64_t region, __nv_bfloat16* __restrict__ shadow) {
+    const int nb = gridDim.x;
+    block_barrier(c, blockIdx.x * c.world);
+    const int64_t total = region * c.world;
+    const int64_t stride = (int64_t)nb * kBlock * 4;
+    float* mine = c.buf[c.rank];
+    for (int64_t i = ((int64_t)blockIdx.x * kBlock + threadIdx.x) * 4; i < total; i += stride) {
+        const int owner = (int)(i / region);
+        float4 v = ld_cg(c.buf[owner] + i);
+        if (owner != c.rank) st_cg(mine + i, v);
+        if (shadow) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+            uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+            *reinterpret_cast<uint2*>(shadow + i) = pk;
+        }
+    }
+    block_barrier(c, (nb + blockIdx.x) * c.world);
+}
+
+// The Σg² slot is complete only when the whole collective kernel has finished on this rank (every
+// local block has passed its end barrier).  This 1-thread kernel, stream-ordered right after it, moves
+// the value to ordinary memory and re-arms the slot for the next call.
+__global__ void take_scalar_kernel(float* slot, float* out) {
+    *out = *slot;
+    *slot = 0.f;
+}
+
+int pick_blocks(int64_t elems) {
+    int64_t b = (elems / 4 + kBlock * 2 - 1) / (kBlock * 2);
+    if (b < 1) b = 1;
+    if (b > 64) b = 64;
+    return (int)b;
+}
+
+}  // namespace
+
+// ctx: host pointer to a CommCtx (see fdt/parallel/symm.py for the mirrored ctypes layout).
+// `blocks` must be the same on every rank (0 = derive from n, which is the same everywhere).
+FDT_API int fdt_comm_all_reduce_mean(const void* ctx, int64_t n, int use_multicast, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld || n % 4) return -1;
+    int64_t chunk = ((n / 4 + c.world - 1) / c.world) * 4;
+    const int64_t lo = min(n, chunk * c.rank), hi = min(n, lo + chunk);
+    const int blocks = pick_blocks(chunk);
+    const float scale = 1.f / c.world;
+    if (use_multicast && c.mc) reduce_kernel<0, true><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    else reduce_kernel<0, false><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// [lo, hi): this rank's region; every rank must pass a region of the same length.
+FDT_API int fdt_comm_reduce_scatter_mean(const void* ctx, int64_t lo, int64_t hi, int use_multicast, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld || (lo % 4) || (hi % 4)) return -1;
+    const int blocks = pick_blocks(hi - lo);
+    const float scale = 1.f / c.world;
+    if (use_multicast && c.mc) reduce_kernel<1, true><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    else reduce_kernel<1, false><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld || region % 4) return -1;
+    const int blocks = pick_blocks(region * c.world);
+    all_gather_cast_kernel<<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// *out = *slot; *slot = 0   (slot: this rank's Σg² scratch word; call right after a reduce collective)
+FDT_API int fdt_comm_take_scalar(float* slot, float* out, cudaStream_t st) {
+    take_scalar_kernel<<<1, 1, 0, st>>>(slot, out);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

@@ -62,7 +62,7 @@ def _conv(a):
         return ctypes.c_int64(a) if abs(a) > 0x7FFFFFFF else ctypes.c_int(a)
     if isinstance(a, float):
         return ctypes.c_float(a)
-    return a
+    return a      # already a ctypes object (c_int64, byref(struct), ...)
 
 
 def i64(v: int):

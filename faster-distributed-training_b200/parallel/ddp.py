@@ -55,12 +55,18 @@ class DataParallelEngine(nn.Module):
         self._stale = True
 
     def reduce_gradients(self):
+        self._fused_sq = None
         self.comm.all_reduce_mean_(self.flat.grad_flat)
+        symm = self.comm.symm
+        if symm is not None and symm.owns(self.flat.grad_flat) and self.comm.world > 1:
+            self._fused_sq = symm.last_sqnorm         # Σg² of the averaged gradient, from the same kernel
 
     def local_grad(self) -> torch.Tensor:
         return self.flat.grad_flat
 
     def grad_sq_norm(self) -> torch.Tensor:
+        if getattr(self, "_fused_sq", None) is not None:
+            return self._fused_sq
         g = self.flat.grad_flat
         if g.is_cuda:
             from .. import ops

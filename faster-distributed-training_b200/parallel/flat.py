@@ -49,7 +49,8 @@ class ShapeGroupLayout:
 class FlatParameters:
     def __init__(self, params: Sequence[torch.nn.Parameter], device=None,
                  allocator: Optional[Callable[[int], torch.Tensor]] = None,
-                 world_size: int = 1, shard: bool = False):
+                 world_size: int = 1, shard: bool = False,
+                 param_allocator: Optional[Callable[[int], torch.Tensor]] = None):
         params = [p for p in params if p.requires_grad]
         assert params, "no trainable parameters"
         device = device or params[0].device
@@ -99,7 +100,11 @@ class FlatParameters:
             self.region = [(r * per, (r + 1) * per) for r in range(max(world_size, 1))]
         self.total = total
 
-        self.param_flat = torch.zeros(total, dtype=torch.float32, device=self.device)
+        if param_allocator is not None:
+            self.param_flat = param_allocator(total)
+            self.param_flat.zero_()
+        else:
+            self.param_flat = torch.zeros(total, dtype=torch.float32, device=self.device)
         if allocator is not None:
             self.grad_flat = allocator(total)
             assert self.grad_flat.numel() == total and self.grad_flat.dtype == torch.float32

@@ -39,7 +39,7 @@ class FullyShardedEngine(nn.Module):
         self.comm = comm or Communicator()
         dev = next(module.parameters()).device
         self.flat = FlatParameters(list(module.parameters()), dev, allocator=allocator,
-                                   world_size=self.comm.world, shard=True)
+                                   world_size=self.comm.world, shard=True, param_allocator=allocator)
         self.region = self.flat.local_region(self.comm.rank)
         self.comm.broadcast_(self.flat.param_flat, src=0)
         for b in module.buffers():
@@ -56,6 +56,14 @@ class FullyShardedEngine(nn.Module):
 
     def pre_forward(self):
         if not self._gathered:
+            symm = self.comm.symm
+            if symm is not None and symm.owns(self.flat.param_flat):
+                # one kernel: pull every peer's region over NVLink and emit the bf16 operand shadow
+                if self.flat.shadow_flat is None:
+                    self.flat.shadow_flat = torch.empty(self.flat.total, dtype=torch.bfloat16, device=self.flat.device)
+                symm.all_gather_(self.flat.param_flat, *self.region, shadow=self.flat.shadow_flat)
+                self._gathered, self._stale = True, False
+                return
             self.comm.all_gather_(self.flat.param_flat, self.region)
             self._gathered = True
             self._stale = True
@@ -64,7 +72,11 @@ class FullyShardedEngine(nn.Module):
             self._stale = False
 
     def reduce_gradients(self):
+        self._fused_sq = None
         self.comm.reduce_scatter_mean_(self.flat.grad_flat, self.region)
+        symm = self.comm.symm
+        if symm is not None and symm.owns(self.flat.grad_flat) and self.comm.world > 1:
+            self._fused_sq = symm.last_sqnorm         # global Σg², produced by the same kernel
 
     def post_step(self):
         """Call after the optimizer updated the owned region: remote regions are now stale."""
@@ -76,6 +88,8 @@ class FullyShardedEngine(nn.Module):
         return self.flat.grad_flat[lo:hi]
 
     def grad_sq_norm(self) -> torch.Tensor:
+        if getattr(self, "_fused_sq", None) is not None:
+            return self._fused_sq
         lo, hi = self.region
         g = self.flat.grad_flat[lo:hi]
         from .. import ops
