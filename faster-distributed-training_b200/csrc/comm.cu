@@ -140,26 +140,51 @@ reduce_kernel(const CommCtx c, int64_t lo, int64_t hi, float scale) {
     block_barrier(c, (nb + blockIdx.x) * c.world);                                 // all writes have landed
 }
 
-// Pull region p ([p*region, (p+1)*region)) from peer p for every p != rank, write the local fp32 buffer
-// and the bf16 shadow of the WHOLE buffer (own region included).
+// All-gather by PUSH, fused with the bf16 operand cast.  Block b of rank r owns sub-slice b of region r:
+// it pushes it to every peer (one multimem.st per 16 bytes when a multicast mapping exists, else one
+// P2P store per peer), meets block b of every peer at a flag barrier — at which point sub-slice b of
+// EVERY region has landed locally — and then converts exactly those sub-slices to bf16.
+template <bool kMulticast>
 __global__ void __launch_bounds__(kBlock)
 all_gather_cast_kernel(const CommCtx c, int64_t region, __nv_bfloat16* __restrict__ shadow) {
     const int nb = gridDim.x;
-    block_barrier(c, blockIdx.x * c.world);
-    const int64_t total = region * c.world;
-    const int64_t stride = (int64_t)nb * kBlock * 4;
+    block_barrier(c, blockIdx.x * c.world);               // peers no longer read the stale regions
+    const int64_t per = ((region / 4 + nb - 1) / nb) * 4;  // elements of one sub-slice (multiple of 4)
+    const int64_t s0 = min(region, per * blockIdx.x), s1 = min(region, s0 + per);
     float* mine = c.buf[c.rank];
-    for (int64_t i = ((int64_t)blockIdx.x * kBlock + threadIdx.x) * 4; i < total; i += stride) {
-        const int owner = (int)(i / region);
-        float4 v = ld_cg(c.buf[owner] + i);
-        if (owner != c.rank) st_cg(mine + i, v);
-        if (shadow) {
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
-            uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
-            *reinterpret_cast<uint2*>(shadow + i) = pk;
+    const int64_t base = region * c.rank;
+    for (int64_t i = s0 + threadIdx.x * 4; i < s1; i += kBlock * 4 * 4) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t k = i + (int64_t)u * kBlock * 4;
+            if (k < s1) v[u] = ld_cg(mine + base + k);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t k = i + (int64_t)u * kBlock * 4;
+            if (k < s1) {
+                if (kMulticast) mc_st(c.mc + base + k, v[u]);
+                else {
+#pragma unroll
+                    for (int p = 0; p < kMaxWorld; ++p)
+                        if (p < c.world && p != c.rank) st_cg(c.buf[p] + base + k, v[u]);
+                }
+            }
         }
     }
-    block_barrier(c, (nb + blockIdx.x) * c.world);
+    block_barrier(c, (nb + blockIdx.x) * c.world);        // sub-slice b of every region is here
+    if (shadow) {
+        for (int r = 0; r < c.world; ++r) {
+            const int64_t rb = region * r;
+            for (int64_t i = s0 + threadIdx.x * 4; i < s1; i += kBlock * 4) {
+                float4 v = ld_cg(mine + rb + i);
+                __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+                uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+                *reinterpret_cast<uint2*>(shadow + rb + i) = pk;
+            }
+        }
+    }
 }
 
 // The Σg² slot is complete only when the whole collective kernel has finished on this rank (every
@@ -168,6 +193,19 @@ all_gather_cast_kernel(const CommCtx c, int64_t region, __nv_bfloat16* __restric
 __global__ void take_scalar_kernel(float* slot, float* out) {
     *out = *slot;
     *slot = 0.f;
+}
+
+__global__ void barrier_kernel(const CommCtx c) { block_barrier(c, blockIdx.x * c.world); }
+
+// dst_mc[i] += alpha * src[i] on EVERY rank (multimem.red); for gradients produced outside the fused wgrad kernel
+__global__ void __launch_bounds__(256)
+mc_red_add_kernel(float* __restrict__ dst_mc, const float* __restrict__ src, int64_t n, float alpha) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+        float4 v = *reinterpret_cast<const float4*>(src + i);
+        asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(dst_mc + i), "f"(alpha * v.x), "f"(alpha * v.y), "f"(alpha * v.z), "f"(alpha * v.w) : "memory");
+    }
 }
 
 int pick_blocks(int64_t elems) {
@@ -206,11 +244,12 @@ FDT_API int fdt_comm_reduce_scatter_mean(const void* ctx, int64_t lo, int64_t hi
     return 0;
 }
 
-FDT_API int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16, cudaStream_t st) {
+FDT_API int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16, int use_multicast, cudaStream_t st) {
     CommCtx c = *static_cast<const CommCtx*>(ctx);
     if (c.world < 2 || c.world > kMaxWorld || region % 4) return -1;
-    const int blocks = pick_blocks(region * c.world);
-    all_gather_cast_kernel<<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
+    const int blocks = pick_blocks(region * 2);
+    if (use_multicast && c.mc) all_gather_cast_kernel<true><<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
+    else all_gather_cast_kernel<false><<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
     FDT_CHECK_LAUNCH();
     return 0;
 }
@@ -218,6 +257,26 @@ FDT_API int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shad
 // *out = *slot; *slot = 0   (slot: this rank's Σg² scratch word; call right after a reduce collective)
 FDT_API int fdt_comm_take_scalar(float* slot, float* out, cudaStream_t st) {
     take_scalar_kernel<<<1, 1, 0, st>>>(slot, out);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// Cross-rank barrier on the stream (one block): everything the peers enqueued before their call has completed.
+FDT_API int fdt_comm_barrier(const void* ctx, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld) return -1;
+    barrier_kernel<<<1, 32, 0, st>>>(c);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// dst_mc (multicast address, 16-byte aligned, n % 4 == 0) += alpha * src on every rank.
+FDT_API int fdt_comm_mc_red_add(float* dst_mc, const float* src, int64_t n, float alpha, cudaStream_t st) {
+    if (n % 4) return -1;
+    int64_t b = (n / 4 + 255) / 256;
+    if (b > 148 * 4) b = 148 * 4;
+    if (b < 1) b = 1;
+    mc_red_add_kernel<<<(int)b, 256, 0, st>>>(dst_mc, src, n, alpha);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -30,7 +30,9 @@ struct WgradParams {
     int Cout, Cin, taps, kw, pad;
     int num_kb;            // total pixel blocks (P / 64)
     int kb_per_split;
-    float* dw;             // [Cout][taps][Cin] fp32, accumulated into
+    float* dw;             // [Cout][taps][Cin] fp32, accumulated into (local, peer or multicast address)
+    float alpha;           // scale applied to the tile before it is added (1/world for a fused all-reduce)
+    int multicast;         // 1: dw is a multicast (NVLS) address → multimem.red adds into EVERY rank's buffer
     int H, W, bh, bn;      // conv geometry of the 64-pixel box
     int tiles_n;           // Cin tiles
 };
@@ -46,6 +48,13 @@ struct WSmem {
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// In-switch all-reduce of a finished tile: one instruction adds 4 floats into the same offset of every
+// GPU's gradient buffer (the address is a multicast mapping of the symmetric heap).
+__device__ __forceinline__ void mc_red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
 }
 
 template <int BN, int kStages, bool kConv>
@@ -143,10 +152,18 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ C
                 tmem_ld_wait();
                 if (co < p.Cout) {
                     float* dst = p.dw + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c * 32;
+                    const float al = p.alpha;
+                    if (p.multicast) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        red_add_v4(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                   __uint_as_float(r[j + 3]));
+                        for (int j = 0; j < 32; j += 4)
+                            mc_red_add_v4(dst + j, al * __uint_as_float(r[j]), al * __uint_as_float(r[j + 1]),
+                                          al * __uint_as_float(r[j + 2]), al * __uint_as_float(r[j + 3]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            red_add_v4(dst + j, al * __uint_as_float(r[j]), al * __uint_as_float(r[j + 1]),
+                                       al * __uint_as_float(r[j + 2]), al * __uint_as_float(r[j + 3]));
+                    }
                 }
             }
         }
@@ -217,8 +234,10 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream
 
 // dw[Cout][k][k][Cin] (fp32) += dY[Nb,H,W,Cout]ᵀ ⊛ X[Nb,H,W,Cin]; stride 1, pad = k/2, NHWC bf16.
 // Cin % 64 == 0; W a power of two <= 64; (Nb·H·W) % 64 == 0.
+// alpha scales the result; multicast != 0 means `dw` is an NVLS multicast address and the accumulation is a
+// fused all-reduce (every rank's buffer receives alpha·tile).
 FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
-                           int pad, cudaStream_t st) {
+                           int pad, float alpha, int multicast, cudaStream_t st) {
     if (Cin % 64 || Cout % 8 || W > 64 || (W & (W - 1)) || (64 % W)) return -1;
     int bh = 64 / W, bn = 1;
     if (bh > H) { if (bh % H) return -1; bn = bh / H; bh = H; }
@@ -229,7 +248,7 @@ FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int
     if (!encode_pc(&tmDY, dy, Cout, P)) return -4;
     WgradParams p{};
     p.Cout = Cout; p.Cin = Cin; p.taps = ksize * ksize; p.kw = ksize; p.pad = pad; p.num_kb = (int)(P / 64); p.dw = dw;
-    p.H = H; p.W = W; p.bh = bh; p.bn = bn;
+    p.H = H; p.W = W; p.bh = bh; p.bn = bn; p.alpha = alpha; p.multicast = multicast;
     const bool wide = (Cin % 128 == 0);
     if (ksize == 1) {
         if (!encode_pc(&tmX, x, Cin, P)) return -4;
@@ -240,11 +259,13 @@ FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int
 }
 
 // dw[N][K] (fp32) += dY[M,N]ᵀ · X[M,K]   (linear layers).  K % 64 == 0, N % 8 == 0, M % 64 == 0.
-FDT_API int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, cudaStream_t st) {
+FDT_API int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, float alpha, int multicast,
+                             cudaStream_t st) {
     if (K % 64 || N % 8 || M % 64) return -1;
     CUtensorMap tmDY, tmX;
     if (!encode_pc(&tmDY, dy, N, M) || !encode_pc(&tmX, x, K, M)) return -4;
     WgradParams p{};
     p.Cout = N; p.Cin = K; p.taps = 1; p.kw = 1; p.pad = 0; p.num_kb = M / 64; p.dw = dw;
+    p.alpha = alpha; p.multicast = multicast;
     return (K % 128 == 0) ? launch<128, false>(tmDY, tmX, p, st) : launch<64, false>(tmDY, tmX, p, st);
 }

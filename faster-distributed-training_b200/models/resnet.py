@@ -35,6 +35,8 @@ class ConvBNStat(nn.Module):
         self.in_channels, self.out_channels = in_channels, out_channels
         self.kernel_size, self.stride, self.padding, self.eps = kernel_size, stride, padding, eps
         self.conv_weight = nn.Parameter(torch.empty(out_channels, in_channels, kernel_size, kernel_size))
+        # eligible for the tcgen05 wgrad kernel → its gradient can be all-reduced inside that kernel
+        self.conv_weight._fdt_wgrad_fused = in_channels % 64 == 0 and out_channels % 8 == 0
         self.reset_parameters()
 
     def reset_parameters(self):

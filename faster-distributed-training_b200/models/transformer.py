@@ -178,6 +178,9 @@ class Transformer(nn.Module):
         self.p_post = 0.1
         self.classifier = Classifier(d_model, d_hidden, n_class, bias_grad_mean_compat)
         self.n_layers, self.alpha = n_layers, alpha
+        for m in self.modules():
+            if isinstance(m, nn.Linear) and m.in_features % 64 == 0 and m.out_features % 8 == 0:
+                m.weight._fdt_wgrad_fused = True      # gradient all-reduced inside the wgrad kernel (DDP)
         self.init_params()
 
     def init_params(self):

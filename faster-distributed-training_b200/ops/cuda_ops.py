@@ -128,16 +128,37 @@ def _grad_slot(weight) -> Optional[torch.Tensor]:
     return g if g.is_contiguous() and g.dtype == torch.float32 else None
 
 
+def _mc_slot(weight):
+    """(multicast address, alpha) when this parameter's gradient is all-reduced inside the wgrad
+    kernel (DDP engine with an NVLS-mapped gradient buffer), else None."""
+    return getattr(weight, "_fdt_mc_grad", None) if weight is not None else None
+
+
+def _mc_accumulate(weight, dw_logical: torch.Tensor):
+    """Fallback for a fused-reduce parameter whose gradient was produced by a library kernel: add it
+    (scaled) into every rank's buffer with one multimem.red pass."""
+    addr, alpha = weight._fdt_mc_grad
+    src = dw_logical.float()
+    if weight.dim() == 4:
+        src = src.permute(0, 2, 3, 1)
+    src = src.contiguous()
+    call("fdt_comm_mc_red_add", _lib.ctypes.c_void_p(int(addr)), src, i64(src.numel()), float(alpha))
+
+
 def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=None):
     dx = dw = None
+    mc = _mc_slot(weight)
     if _native_gemm():
         from . import gemm_sm100
         if need_dx:
             dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding)
         if need_dw:
-            slot = _grad_slot(weight) if weight is not None else None
-            dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, slot)
-            if dw is True:          # accumulated straight into the flat gradient buffer
+            if mc is not None:      # tile-by-tile in-switch all-reduce fused into the wgrad epilogue
+                dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, mc[0], mc[1], True)
+            else:
+                slot = _grad_slot(weight) if weight is not None else None
+                dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, slot)
+            if dw is True:          # accumulated straight into the flat gradient buffer(s)
                 need_dw, dw = False, None
     if (need_dx and dx is None) or (need_dw and dw is None):
         mask = [need_dx and dx is None, need_dw and dw is None, False]
@@ -145,6 +166,9 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
                                                           [1, 1], False, [0, 0], 1, mask)
         dx = rdx if dx is None else dx
         dw = rdw if dw is None else dw
+    if dw is not None and mc is not None:
+        _mc_accumulate(weight, dw)
+        dw = None
     return dx, dw
 
 

@@ -89,9 +89,9 @@ def conv_dgrad(dy: torch.Tensor, w16: torch.Tensor, x_shape, stride: int, paddin
     return conv_fwd(dy, wt, stride, padding)
 
 
-def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None):
+def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha=1.0, multicast=False):
     from . import wgrad_sm100
-    return wgrad_sm100.conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into)
+    return wgrad_sm100.conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into, alpha, multicast)
 
 
 def linear(x, weight, bias, act):

@@ -31,14 +31,14 @@ class _Linear(torch.autograd.Function):
         else:
             out = g.gemm_nt(x16, w16, b32, act)
             saved = out
-        ctx.save_for_backward(x16, w16, saved)
+        ctx.save_for_backward(x16, w16, saved, weight)
         ctx.act, ctx.shp, ctx.xdtype = act, shp, x.dtype
         ctx.bshape = None if bias is None else bias.shape
         return out.view(*shp[:-1], w16.shape[0])
 
     @staticmethod
     def backward(ctx, gout):
-        x16, w16, saved = ctx.saved_tensors
+        x16, w16, saved, weight = ctx.saved_tensors
         N = w16.shape[0]
         gz = gout.to(BF16).reshape(-1, N)
         if ctx.act == "gelu":
@@ -58,9 +58,19 @@ class _Linear(torch.autograd.Function):
             dx = dx.view(ctx.shp).to(ctx.xdtype)
         if ctx.needs_input_grad[1]:
             from . import wgrad_sm100
-            dw = wgrad_sm100.linear_wgrad(gz, x16) if hasattr(wgrad_sm100, "linear_wgrad") else None
-            if dw is None:
-                dw = (gz.t() @ x16).float()
+            mc = getattr(weight, "_fdt_mc_grad", None)
+            if mc is not None:      # in-switch all-reduce fused into the wgrad epilogue
+                dw = wgrad_sm100.linear_wgrad(gz, x16, mc[0], mc[1], True)
+                if dw is True:
+                    dw = None
+                else:
+                    from .cuda_ops import _mc_accumulate
+                    _mc_accumulate(weight, (gz.t() @ x16).float())
+                    dw = None
+            else:
+                dw = wgrad_sm100.linear_wgrad(gz, x16)
+                if dw is None:
+                    dw = (gz.t() @ x16).float()
         if ctx.bshape is not None and ctx.needs_input_grad[2]:
             db = gz.float().sum(0).view(ctx.bshape)
         return dx, dw, db, None

@@ -32,7 +32,7 @@ def _conv_ok(x_shape, w_shape, stride, padding) -> bool:
     return (N * H * W) % 64 == 0
 
 
-def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha: float = 1.0, multicast: bool = False):
     """fp32 weight gradient of a stride-1 "same" convolution.  ``accumulate_into`` (a physically
     [Cout, kh, kw, Cin]-contiguous fp32 tensor, e.g. the parameter's slice of the flat gradient buffer)
     receives the result by atomic accumulation and ``True`` is returned; otherwise a fresh tensor in the
@@ -42,14 +42,16 @@ def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into: Optional[torch.
     Cout, Cin, kh, kw = w_shape
     N, _, H, W = x.shape
     if accumulate_into is not None:
-        call("fdt_conv_wgrad", dy, x, accumulate_into, N, H, W, Cin, Cout, kh, padding)
+        # a tensor, or a raw (possibly multicast) device address
+        dst = accumulate_into if torch.is_tensor(accumulate_into) else _lib.ctypes.c_void_p(int(accumulate_into))
+        call("fdt_conv_wgrad", dy, x, dst, N, H, W, Cin, Cout, kh, padding, float(alpha), int(multicast))
         return True
     dw = torch.zeros((Cout, kh, kw, Cin), dtype=torch.float32, device=x.device)
-    call("fdt_conv_wgrad", dy, x, dw, N, H, W, Cin, Cout, kh, padding)
+    call("fdt_conv_wgrad", dy, x, dw, N, H, W, Cin, Cout, kh, padding, 1.0, 0)
     return dw.permute(0, 3, 1, 2)
 
 
-def linear_wgrad(gz: torch.Tensor, x16: torch.Tensor) -> Optional[torch.Tensor]:
+def linear_wgrad(gz: torch.Tensor, x16: torch.Tensor, accumulate_into=None, alpha: float = 1.0, multicast: bool = False):
     """dW[N, K] = gzᵀ[N, M] · x[M, K] in fp32 (gz, x bf16 row-major)."""
     if not available():
         return None
@@ -57,6 +59,10 @@ def linear_wgrad(gz: torch.Tensor, x16: torch.Tensor) -> Optional[torch.Tensor]:
     K = x16.shape[1]
     if K % 64 or N % 8 or M % 64 or not (gz.is_contiguous() and x16.is_contiguous()):
         return None
+    if accumulate_into is not None:
+        dst = accumulate_into if torch.is_tensor(accumulate_into) else _lib.ctypes.c_void_p(int(accumulate_into))
+        call("fdt_linear_wgrad", gz, x16, dst, M, N, K, float(alpha), int(multicast))
+        return True
     dw = torch.zeros(N, K, dtype=torch.float32, device=gz.device)
-    call("fdt_linear_wgrad", gz, x16, dw, M, N, K)
+    call("fdt_linear_wgrad", gz, x16, dw, M, N, K, 1.0, 0)
     return dw

@@ -365,7 +365,8 @@ class NGD(Optimizer):
         for p in group["params"]:
             if p.grad is None:
                 continue
-            key = (tuple(p.shape), p.dtype, p.device)
+            f = getattr(p, "_fdt_flat", None)
+            key = (tuple(p.shape), p.dtype, p.device, f[0].group_id_of(p) if f is not None else None)
             buckets.setdefault(key, []).append(p)
         sgs = [_ShapeGroup(ps) for ps in buckets.values()]
         for sg in sgs:

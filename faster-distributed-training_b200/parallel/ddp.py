@@ -14,6 +14,7 @@ Replaces ``torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank])``
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -31,12 +32,40 @@ class DataParallelEngine(nn.Module):
         self.module = module
         self.comm = comm or Communicator()
         dev = next(module.parameters()).device
+        fused_pred = None
+        symm = self.comm.symm
+        want_fused = (symm is not None and allocator is not None and self.comm.world > 1
+                      and os.environ.get("FDT_FUSED_WGRAD", "1") == "1")
+        if want_fused:
+            fused_pred = lambda p: bool(getattr(p, "_fdt_wgrad_fused", False))
         self.flat = flat or FlatParameters(list(module.parameters()), dev, allocator=allocator,
-                                           world_size=self.comm.world)
+                                           world_size=self.comm.world, fused_first=fused_pred)
         self.comm.broadcast_(self.flat.param_flat, src=0)
         for b in module.buffers():
             self.comm.broadcast_(b, src=0)
         self._stale = True
+        self._fused_end = 0
+        self._tail_ctx = None
+        if want_fused and symm.owns(self.flat.grad_flat) and symm.multicast_addr(self.flat.grad_flat) and self.flat.fused_end:
+            self._enable_fused_wgrad()
+
+    def _enable_fused_wgrad(self):
+        """Gradients of GEMM-shaped parameters are all-reduced INSIDE the wgrad kernels: every finished
+        fp32 tile is scaled by 1/world and added into all ranks' gradient buffers with multimem.red
+        (in-switch reduction), overlapping the transfer with the rest of backward tile by tile.  Only
+        the small "tail" of the buffer (BN affine, biases, layers on the library path) still goes
+        through the stand-alone fused all-reduce."""
+        symm, flat = self.comm.symm, self.flat
+        mc = symm.multicast_addr(flat.grad_flat)
+        alpha = 1.0 / self.comm.world
+        for g in flat.groups:
+            if g.offset >= flat.fused_end:
+                continue
+            for i, p in enumerate(g.params):
+                p._fdt_mc_grad = (mc + 4 * (g.offset + i * g.numel), alpha)
+        self._fused_end = flat.fused_end
+        n_tail = flat.total - flat.fused_end
+        self._tail_ctx = symm.sub_ctx(flat.grad_flat, flat.fused_end) if n_tail > 0 else None
 
     def forward(self, *a, **kw):
         self.pre_forward()
@@ -56,6 +85,16 @@ class DataParallelEngine(nn.Module):
 
     def reduce_gradients(self):
         self._fused_sq = None
+        if self._fused_end:
+            symm, flat = self.comm.symm, self.flat
+            if self._tail_ctx is not None:      # its entry barrier also orders the peers' multimem.red traffic
+                sq_tail = symm.all_reduce_mean_ctx_(self._tail_ctx, flat.total - self._fused_end)
+            else:
+                symm.barrier_on_stream(flat.grad_flat)
+                sq_tail = 0.0
+            from .. import ops
+            self._fused_sq = ops._cu().sqnorm(flat.grad_flat[: self._fused_end]) + sq_tail
+            return
         self.comm.all_reduce_mean_(self.flat.grad_flat)
         symm = self.comm.symm
         if symm is not None and symm.owns(self.flat.grad_flat) and self.comm.world > 1:
@@ -80,6 +119,10 @@ class DataParallelEngine(nn.Module):
 
     def zero_grad(self):
         self.flat.zero_grad()
+        if self._fused_end:
+            # nobody may add into this rank's buffer before it is cleared (and nobody clears while a
+            # slower peer still reads last step's gradients)
+            self.comm.symm.barrier_on_stream(self.flat.grad_flat)
 
     def full_state_dict(self):
         return self.state_dict()

@@ -31,6 +31,7 @@ def _round_up(x: int, a: int) -> int:
 
 class ShapeGroupLayout:
     def __init__(self, shape, params, offset, owner=0):
+        shape = tuple(d for d in shape if not isinstance(d, str))      # drop the "fused" bucket tag
         self.shape = tuple(shape)
         self.params = params
         self.numel = params[0].numel()
@@ -50,7 +51,8 @@ class FlatParameters:
     def __init__(self, params: Sequence[torch.nn.Parameter], device=None,
                  allocator: Optional[Callable[[int], torch.Tensor]] = None,
                  world_size: int = 1, shard: bool = False,
-                 param_allocator: Optional[Callable[[int], torch.Tensor]] = None):
+                 param_allocator: Optional[Callable[[int], torch.Tensor]] = None,
+                 fused_first: Optional[Callable[[torch.nn.Parameter], bool]] = None):
         params = [p for p in params if p.requires_grad]
         assert params, "no trainable parameters"
         device = device or params[0].device
@@ -59,8 +61,19 @@ class FlatParameters:
         self.sharded = shard and world_size > 1
 
         buckets: "OrderedDict[Tuple, List[torch.nn.Parameter]]" = OrderedDict()
+        split_fused = fused_first is not None and not (shard and world_size > 1)
         for p in params:
-            buckets.setdefault(tuple(p.shape), []).append(p)
+            key = tuple(p.shape) + (("fused",) if split_fused and fused_first(p) else ())
+            buckets.setdefault(key, []).append(p)
+        # shape groups whose gradients are all-reduced inside the wgrad kernels go first, so that the
+        # remaining ("tail") gradients form one contiguous range for the stand-alone all-reduce
+        self.fused_end = 0
+        n_fused = 0
+        if fused_first is not None and not self.sharded:
+            front = OrderedDict((s, ps) for s, ps in buckets.items() if s and s[-1] == "fused")
+            n_fused = len(front)
+            rest = OrderedDict((s, ps) for s, ps in buckets.items() if s not in front)
+            buckets = OrderedDict(list(front.items()) + list(rest.items()))
 
         # owner assignment: greedy balance of element counts (largest groups first)
         owners: Dict[Tuple, int] = {s: 0 for s in buckets}
@@ -91,10 +104,12 @@ class FlatParameters:
                     off += _round_up(g.size, ALIGN)
             total = world_size * region_size
         else:
-            for s, ps in buckets.items():
+            for gi, (s, ps) in enumerate(buckets.items()):
                 g = ShapeGroupLayout(s, ps, off, 0)
                 self.groups.append(g)
                 off += _round_up(g.size, ALIGN)
+                if gi + 1 == n_fused:
+                    self.fused_end = off
             total = _round_up(off, ALIGN * max(world_size, 1))
             per = total // max(world_size, 1)
             self.region = [(r * per, (r + 1) * per) for r in range(max(world_size, 1))]
@@ -185,6 +200,9 @@ class FlatParameters:
 
     def zero_grad(self):
         self.grad_flat.zero_()
+
+    def group_id_of(self, p: torch.nn.Parameter) -> int:
+        return id(self._index[p._fdt_flat[1]][0])
 
     def owned_params(self, rank: int) -> List[torch.nn.Parameter]:
         return [p for g in self.groups if g.owner == rank for p in g.params]

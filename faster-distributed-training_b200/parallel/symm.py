@@ -89,6 +89,29 @@ class SymmetricHeap:
         self.bufs[t.data_ptr()] = (t, hdl, ctx)
         return t
 
+    def sub_ctx(self, t: torch.Tensor, offset: int) -> _CommCtx:
+        """Context whose data pointers start ``offset`` elements into buffer ``t`` (a tail range)."""
+        base = self._ctx(t)
+        c = _CommCtx()
+        for p in range(self.world):
+            c.buf[p] = base.buf[p] + 4 * offset
+            c.sig[p] = base.sig[p]
+            c.scratch[p] = base.scratch[p]
+        c.mc = (base.mc + 4 * offset) if base.mc else 0
+        c.rank, c.world = self.rank, self.world
+        return c
+
+    def multicast_addr(self, t: torch.Tensor) -> int:
+        return int(self._ctx(t).mc or 0)
+
+    def barrier_on_stream(self, t: torch.Tensor):
+        """Cross-rank barrier enqueued on the current stream (kernel-side flag barrier)."""
+        _lib.call("fdt_comm_barrier", ctypes.byref(self._ctx(t)))
+
+    def all_reduce_mean_ctx_(self, ctx: _CommCtx, n: int) -> torch.Tensor:
+        _lib.call("fdt_comm_all_reduce_mean", ctypes.byref(ctx), _lib.i64(n), int(self.use_multicast))
+        return self._take_sq()
+
     def owns(self, t: torch.Tensor) -> bool:
         return t.data_ptr() in self.bufs
 
@@ -116,5 +139,5 @@ class SymmetricHeap:
 
     def all_gather_(self, flat: torch.Tensor, lo: int, hi: int, shadow: Optional[torch.Tensor] = None) -> torch.Tensor:
         ctx = self._ctx(flat)
-        _lib.call("fdt_comm_all_gather_cast", ctypes.byref(ctx), _lib.i64(hi - lo), shadow)
+        _lib.call("fdt_comm_all_gather_cast", ctypes.byref(ctx), _lib.i64(hi - lo), shadow, int(self.use_multicast))
         return flat
