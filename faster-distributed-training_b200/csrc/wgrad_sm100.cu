@@ -33,6 +33,9 @@ struct WgradParams {
     float* dw;             // [Cout][taps][Cin] fp32, accumulated into (local, peer or multicast address)
     float alpha;           // scale applied to the tile before it is added (1/world for a fused all-reduce)
     int multicast;         // 1: dw is a multicast (NVLS) address → multimem.red adds into EVERY rank's buffer
+    float* acc;            // multicast + split-K: local fp32 staging ([Cout][taps][Cin], all zero between launches)
+    int* counters;         // multicast + split-K: per-tile arrival counters (all zero between launches)
+    int splits;
     int H, W, bh, bn;      // conv geometry of the 64-pixel box
     int tiles_n;           // Cin tiles
 };
@@ -154,15 +157,45 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ C
                     float* dst = p.dw + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c * 32;
                     const float al = p.alpha;
                     if (p.multicast) {
+                        // split-K partials meet in the LOCAL staging buffer; only the finished tile crosses NVLink
+                        float* loc = p.acc + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c * 32;
 #pragma unroll
                         for (int j = 0; j < 32; j += 4)
-                            mc_red_add_v4(dst + j, al * __uint_as_float(r[j]), al * __uint_as_float(r[j + 1]),
-                                          al * __uint_as_float(r[j + 2]), al * __uint_as_float(r[j + 3]));
+                            red_add_v4(loc + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                       __uint_as_float(r[j + 3]));
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; j += 4)
                             red_add_v4(dst + j, al * __uint_as_float(r[j]), al * __uint_as_float(r[j + 1]),
                                        al * __uint_as_float(r[j + 2]), al * __uint_as_float(r[j + 3]));
+                    }
+                }
+            }
+            if (p.multicast) {
+                // "last split in" detection: the CTA that completes the tile pushes it to every rank with
+                // one multimem.red per 16 bytes (in-switch all-reduce), then re-zeroes the staging tile.
+                __shared__ int s_last;
+                __threadfence();
+                asm volatile("bar.sync 1, 128;" ::: "memory");          // the 4 epilogue warps
+                if (threadIdx.x == 64) {
+                    const int old = atomicAdd(p.counters + blockIdx.x, 1);
+                    s_last = (old == p.splits - 1);
+                    if (s_last) p.counters[blockIdx.x] = 0;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (s_last) {
+                    __threadfence();
+                    // coalesced push: one warp per output row, 32 lanes x 16 B = 512 contiguous bytes per instruction
+                    const float al = p.alpha;
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const int co2 = m_tile * BM + q * 32 + rr;
+                        if (co2 >= p.Cout) break;
+                        const size_t off = ((size_t)co2 * p.taps + tap) * p.Cin + n_tile * BN;
+                        for (int j = lane * 4; j < BN; j += 128) {
+                            float4 v = __ldcg(reinterpret_cast<const float4*>(p.acc + off + j));
+                            __stcg(reinterpret_cast<float4*>(p.acc + off + j), make_float4(0.f, 0.f, 0.f, 0.f));
+                            mc_red_add_v4(p.dw + off + j, al * v.x, al * v.y, al * v.z, al * v.w);
+                        }
                     }
                 }
             }
@@ -210,6 +243,36 @@ bool encode_nhwc64(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Staging for the fused all-reduce (multicast destination + split-K): one fp32 buffer as large as the
+// largest weight seen so far and a tile-counter array, per device.  Both are all-zero between launches
+// (the kernels clean up after themselves), so launches on one stream can share them.  Allocated on
+// first use / growth — outside CUDA-graph capture, because the warm-up steps run eagerly first.
+struct Staging { float* acc = nullptr; size_t elems = 0; int* counters = nullptr; int ncounters = 0; };
+Staging g_staging[64];
+
+int get_staging(WgradParams& p, int tiles) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -5;
+    Staging& s = g_staging[dev];
+    const size_t need = (size_t)p.Cout * p.taps * p.Cin;
+    if (s.elems < need) {
+        if (s.acc) cudaFree(s.acc);
+        if (cudaMalloc(&s.acc, need * sizeof(float)) != cudaSuccess) return -6;
+        cudaMemset(s.acc, 0, need * sizeof(float));
+        s.elems = need;
+    }
+    if (s.ncounters < tiles) {
+        if (s.counters) cudaFree(s.counters);
+        const int n = tiles < 4096 ? 4096 : tiles;
+        if (cudaMalloc(&s.counters, n * sizeof(int)) != cudaSuccess) return -6;
+        cudaMemset(s.counters, 0, n * sizeof(int));
+        s.ncounters = n;
+    }
+    p.acc = s.acc;
+    p.counters = s.counters;
+    return 0;
+}
+
 template <int BN, bool kConv>
 int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream_t st) {
     constexpr int kStages = 4;
@@ -225,6 +288,11 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream
     if (splits < 1) splits = 1;
     p.kb_per_split = (p.num_kb + splits - 1) / splits;
     splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+    p.splits = splits;
+    if (p.multicast) {
+        int rc = get_staging(p, tiles);
+        if (rc) return rc;
+    }
     kern<<<dim3(tiles, splits), kThreads, L::kTotal, st>>>(a, b, p);
     FDT_CHECK_LAUNCH();
     return 0;

@@ -57,13 +57,15 @@ class BackgroundLoader:
 
 class TensorBatchLoader:
     def __init__(self, tensors: Sequence[torch.Tensor], batch_size: int, sampler: Optional[ShardedSampler] = None,
-                 shuffle: bool = True, drop_last: bool = True, pin: Optional[bool] = None, ring: int = 4, seed: int = 0):
+                 shuffle: bool = True, drop_last: bool = True, pin: Optional[bool] = None, ring: int = 8, seed: int = 0):
         self.tensors = [t.contiguous() for t in tensors]
         n = self.tensors[0].shape[0]
         self.sampler = sampler or ShardedSampler(n, 1, 0, shuffle=shuffle, seed=seed)
         self.batch_size, self.drop_last = batch_size, drop_last
         self.pin = torch.cuda.is_available() if pin is None else pin
-        self.ring = ring
+        # a staging buffer is rewritten `ring` batches later; BackgroundLoader (2 queued + 1 in hand) and
+        # DevicePrefetcher (1 ahead + 1 current) keep at most 5 batches alive, so 8 is safe
+        self.ring = max(ring, 8)
         self._stage: List[List[torch.Tensor]] = []
         for _ in range(ring):
             bufs = []

@@ -89,7 +89,8 @@ def main():
         if hasattr(eng, "pre_forward"):
             eng._gathered = getattr(eng, "_gathered", True)
             eng.pre_forward()
-        return losses, eng.flat.param_flat.clone()
+        return losses, torch.cat([v.detach().float().flatten() for k, v in sorted(eng.module.state_dict().items())
+                                  if v.dtype.is_floating_point])
 
     for cls in (DataParallelEngine, FullyShardedEngine):
         l_a, p_a = run(cls, True)
