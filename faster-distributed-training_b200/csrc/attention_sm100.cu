@@ -1,0 +1,458 @@
+// Fused multi-head attention forward / backward on tcgen05 for sequences of up to 128 tokens, d_head = 64.
+//
+//   P = dropout(softmax(Q Kᵀ / sqrt(d) + key mask)),   O = P V
+//
+// One CTA per (batch, head).  Q, K, V (and dO) are read straight out of the projection outputs —
+// [B·L, heads·64] matrices — with 2-D TMA boxes at column offset head·64, and O / dQ / dK / dV are written
+// back in the same layout, so there is no head transpose anywhere.  S = QKᵀ and all other products live in
+// tensor memory; the softmax warps (one thread per query row) read S with tcgen05.ld, write the bf16
+// probabilities into shared memory in the 128B-swizzled layout the next MMA expects, and the second MMA
+// consumes them.  Every product of the backward pass is expressed with K-major or MN-major operand
+// descriptors on the SAME shared-memory tiles (P and dS are read both ways), so nothing is transposed:
+//
+//   fwd : S = Q Kᵀ                 (A K-major, B K-major)         O  = P V      (A K-major, B MN-major)
+//   bwd : S = Q Kᵀ, dP = dO Vᵀ     (K-major / K-major)            dV = Pᵀ dO    (A MN-major, B MN-major)
+//         dQ = dS K                (A K-major, B MN-major)        dK = dSᵀ Q    (A MN-major, B MN-major)
+//
+// Parity: ScaledDotProduct / MultiheadAttention of the reference (transformer.py:180-227): two batched
+// cuBLAS GEMMs + softmax + dropout kernels that materialise the B·h·L·L probabilities.
+// The reference's mask fill value of -1e-9 (Q11) is available as `mask_compat`.
+#include "common.cuh"
+#include "sm100.cuh"
+#include <cstdio>
+#include <mutex>
+
+using namespace fdt;
+using namespace sm100;
+
+namespace {
+
+constexpr int kT = 128;        // tile: queries = keys = 128
+constexpr int kD = 64;         // head dim
+constexpr int kThreads = 192;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct AttnParams {
+    int B, H, L, ld;               // ld: row stride (elements) of the [B·L, H·64] matrices
+    const int64_t* key_mask;       // [B, L] (nonzero = keep) or null
+    int mask_compat;
+    float scale, p_drop;
+    const int64_t* seed_off;       // device (seed, offset) pair for Philox, or null when p_drop == 0
+    __nv_bfloat16* O;              // fwd out
+    float* lse;                    // [B, H, L]
+    const __nv_bfloat16* dO;       // bwd in (also via TMA)
+    const __nv_bfloat16* Oin;      // bwd in
+    __nv_bfloat16 *dQ, *dK, *dV;   // bwd out
+};
+
+// byte offset of element (row, col) inside a [128 rows][64 bf16] 128B-swizzled atom
+__device__ __forceinline__ uint32_t swz(int row, int col) {
+    return (uint32_t)(row * 128 + ((((col >> 3) ^ (row & 7)) << 4) | ((col & 7) << 1)));
+}
+
+__device__ __forceinline__ float drop_scale(const Philox& rng, uint64_t off, int bh, int row, int col4, float p, float inv_keep,
+                                            float* m4) {
+    uint4 r = rng(((uint64_t)bh * kT + row) * 32 + col4, off);
+    m4[0] = u32_to_unit(r.x) >= p ? inv_keep : 0.f;
+    m4[1] = u32_to_unit(r.y) >= p ? inv_keep : 0.f;
+    m4[2] = u32_to_unit(r.z) >= p ? inv_keep : 0.f;
+    m4[3] = u32_to_unit(r.w) >= p ? inv_keep : 0.f;
+    return 0.f;
+}
+
+// additive bias / replacement for key j of batch b (evaluated once per CTA into shared memory)
+__device__ __forceinline__ void load_key_bias(const AttnParams& p, int b, float* kbias, int* kfill) {
+    for (int j = threadIdx.x; j < kT; j += kThreads) {
+        float bias = 0.f; int fill = 0;
+        if (j >= p.L) bias = -INFINITY;
+        else if (p.key_mask && p.key_mask[(size_t)b * p.L + j] == 0) {
+            if (p.mask_compat) fill = 1; else bias = -INFINITY;
+        }
+        kbias[j] = bias; kfill[j] = fill;
+    }
+}
+
+// ------------------------------------------------------------------ forward
+__global__ void __launch_bounds__(kThreads, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;                 // 16 KB each
+    uint8_t* sK = smem + 16384;
+    uint8_t* sV = smem + 32768;
+    uint8_t* sP = smem + 49152;         // 2 atoms (keys 0-63 | 64-127), 32 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 81920);   // [0] qkv, [1] S ready, [2] P ready, [3] O ready
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 4);
+    float* kbias = reinterpret_cast<float*>(bars + 6);
+    int* kfill = reinterpret_cast<int*>(kbias + kT);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.x, b = bh / p.H, h = bh % p.H;
+    const int row0 = b * p.L, col0 = h * kD;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 128); mbar_init(&bars[3], 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<256>(tmem_ptr);
+    load_key_bias(p, b, kbias, kfill);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = *tmem_ptr;
+    const uint32_t tmS = tm, tmO = tm + 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(&bars[0], 3 * 16384);
+            tma_load_2d(sQ, &tmQ, &bars[0], col0, row0);
+            tma_load_2d(sK, &tmK, &bars[0], col0, row0);
+            tma_load_2d(sV, &tmV, &bars[0], col0, row0);
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            mbar_wait(&bars[0], 0);
+            tc_fence_after();
+            const uint64_t dq = make_smem_desc(smem_u32(sQ), 16, 1024), dk = make_smem_desc(smem_u32(sK), 16, 1024);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tmS, dq + 2 * k, dk + 2 * k, make_idesc_bf16(128, 128, 0, 0), k != 0);
+            umma_commit(&bars[1]);
+            mbar_wait(&bars[2], 0);                       // probabilities are in shared memory
+            tc_fence_after();
+            const uint64_t dv = make_smem_desc(smem_u32(sV), 8192, 1024);       // B = V, N(d)-major, K = keys
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint64_t dp = make_smem_desc(smem_u32(sP) + (k >> 2) * 16384, 16, 1024) + 2 * (k & 3);
+                umma_bf16(tmO, dp, dv + 128 * k, make_idesc_bf16(128, 64, 0, 1), k != 0);
+            }
+            umma_commit(&bars[3]);
+        }
+    } else {
+        const int q = warp & 3, row = q * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        const float sl2 = p.scale * kLog2e;
+        mbar_wait(&bars[1], 0);
+        tc_fence_after();
+        // pass 1: row maximum (in scaled log2 units)
+        float mx = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmS + lane_addr + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int key = c * 32 + j;
+                float s = kfill[key] ? -1e-9f : __uint_as_float(r[j]);
+                s = s * sl2 + kbias[key];
+                mx = fmaxf(mx, s);
+            }
+        }
+        if (mx == -INFINITY) mx = 0.f;
+        // pass 2: exponentials, row sum, dropout, bf16 P into swizzled shared memory
+        Philox rng(p.seed_off ? (uint64_t)p.seed_off[0] : 0ull);
+        const uint64_t off = p.seed_off ? (uint64_t)p.seed_off[1] : 0ull;
+        const float inv_keep = 1.f / (1.f - p.p_drop);
+        float sum = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmS + lane_addr + c * 32, r);
+            tmem_ld_wait();
+            float pv[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int key = c * 32 + j;
+                float s = kfill[key] ? -1e-9f : __uint_as_float(r[j]);
+                s = s * sl2 + kbias[key];
+                const float e = exp2f(s - mx);
+                sum += e;
+                pv[j] = e;
+            }
+            if (p.p_drop > 0.f) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    float m4[4];
+                    drop_scale(rng, off, bh, row, c * 8 + (j >> 2), p.p_drop, inv_keep, m4);
+                    pv[j] *= m4[0]; pv[j + 1] *= m4[1]; pv[j + 2] *= m4[2]; pv[j + 3] *= m4[3];
+                }
+            }
+            uint8_t* atom = sP + (c >> 1) * 16384;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                const int col = (c & 1) * 32 + j;
+                *reinterpret_cast<uint4*>(atom + swz(row, col)) = pack8(pv + j).u;
+            }
+        }
+        fence_proxy_async();                                // generic-proxy smem writes → visible to the MMA
+        mbar_arrive(&bars[2]);
+        mbar_wait(&bars[3], 0);
+        tc_fence_after();
+        const float inv = 1.f / sum;
+        const bool row_ok = row < p.L;
+        if (row_ok) p.lse[(size_t)bh * p.L + row] = (mx + log2f(sum)) / kLog2e;   // natural-log units of the SCALED scores
+        __nv_bfloat16* o = p.O + (size_t)(row0 + row) * p.ld + col0;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmO + lane_addr + c * 32, r);       // warp-collective: executed by every lane
+            tmem_ld_wait();
+            if (row_ok) {
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * inv;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) st8(o + c * 32 + j, pack8(v + j));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<256>(tm);
+}
+
+// ------------------------------------------------------------------ backward
+__global__ void __launch_bounds__(kThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO, const AttnParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + 16384;
+    uint8_t* sV = smem + 32768;
+    uint8_t* sdO = smem + 49152;
+    uint8_t* sP = smem + 65536;          // 32 KB
+    uint8_t* sdS = smem + 98304;         // 32 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 131072);   // [0] loads, [1] S & dP ready, [2] P & dS ready, [3] grads ready
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 4);
+    float* kbias = reinterpret_cast<float*>(bars + 6);
+    int* kfill = reinterpret_cast<int*>(kbias + kT);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.x, b = bh / p.H, h = bh % p.H;
+    const int row0 = b * p.L, col0 = h * kD;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV); prefetch_tmap(&tmdO);
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 128); mbar_init(&bars[3], 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_ptr);
+    load_key_bias(p, b, kbias, kfill);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = *tmem_ptr;
+    const uint32_t tmS = tm, tmdP = tm + 128, tmdV = tm + 256, tmdK = tm + 320, tmdQ = tm + 384;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(&bars[0], 4 * 16384);
+            tma_load_2d(sQ, &tmQ, &bars[0], col0, row0);
+            tma_load_2d(sK, &tmK, &bars[0], col0, row0);
+            tma_load_2d(sV, &tmV, &bars[0], col0, row0);
+            tma_load_2d(sdO, &tmdO, &bars[0], col0, row0);
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            mbar_wait(&bars[0], 0);
+            tc_fence_after();
+            const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV), adO = smem_u32(sdO);
+            const uint32_t aP = smem_u32(sP), adS = smem_u32(sdS);
+            const uint32_t iKK = make_idesc_bf16(128, 128, 0, 0);
+            {   // S = Q Kᵀ ; dP = dO Vᵀ   (all K-major, K = d = 64)
+                const uint64_t dq = make_smem_desc(aQ, 16, 1024), dk = make_smem_desc(aK, 16, 1024);
+                const uint64_t ddo = make_smem_desc(adO, 16, 1024), dv = make_smem_desc(aV, 16, 1024);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tmS, dq + 2 * k, dk + 2 * k, iKK, k != 0);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tmdP, ddo + 2 * k, dv + 2 * k, iKK, k != 0);
+            }
+            umma_commit(&bars[1]);
+            mbar_wait(&bars[2], 0);
+            tc_fence_after();
+            // MN-major views: tile [128 q rows (K)][128 keys (M)] = 2 atoms 16 KB apart; 8-row groups 1 KB apart
+            const uint64_t dPt = make_smem_desc(aP, 16384, 1024), dSt = make_smem_desc(adS, 16384, 1024);
+            const uint64_t ddoN = make_smem_desc(adO, 8192, 1024);     // B = dO, N(d)-major, K = q
+            const uint64_t dqN = make_smem_desc(aQ, 8192, 1024);       // B = Q,  N(d)-major, K = q
+            const uint64_t dkN = make_smem_desc(aK, 8192, 1024);       // B = K,  N(d)-major, K = keys
+            const uint32_t iMM = make_idesc_bf16(128, 64, 1, 1), iKM = make_idesc_bf16(128, 64, 0, 1);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) umma_bf16(tmdV, dPt + 128 * k, ddoN + 128 * k, iMM, k != 0);   // dV = Pᵀ dO
+#pragma unroll
+            for (int k = 0; k < 8; ++k) umma_bf16(tmdK, dSt + 128 * k, dqN + 128 * k, iMM, k != 0);    // dK = dSᵀ Q
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {                                                             // dQ = dS K
+                const uint64_t ds = make_smem_desc(adS + (k >> 2) * 16384, 16, 1024) + 2 * (k & 3);
+                umma_bf16(tmdQ, ds, dkN + 128 * k, iKM, k != 0);
+            }
+            umma_commit(&bars[3]);
+        }
+    } else {
+        const int q = warp & 3, row = q * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        const float sl2 = p.scale * kLog2e;
+        const bool row_ok = row < p.L;
+        // D_r = Σ_d dO[r,d]·O[r,d]
+        float Dr = 0.f, lse2 = 0.f;
+        if (row_ok) {
+            const __nv_bfloat16* o = p.Oin + (size_t)(row0 + row) * p.ld + col0;
+            const __nv_bfloat16* g = p.dO + (size_t)(row0 + row) * p.ld + col0;
+#pragma unroll
+            for (int j = 0; j < kD; j += 8) {
+                float fo[8], fg[8];
+                unpack8(ld8(o + j), fo);
+                unpack8(ld8(g + j), fg);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) Dr += fo[i] * fg[i];
+            }
+            lse2 = p.lse[(size_t)bh * p.L + row] * kLog2e;
+        }
+        Philox rng(p.seed_off ? (uint64_t)p.seed_off[0] : 0ull);
+        const uint64_t off = p.seed_off ? (uint64_t)p.seed_off[1] : 0ull;
+        const float inv_keep = 1.f / (1.f - p.p_drop);
+        mbar_wait(&bars[1], 0);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t rs[32], rp[32];
+            tmem_ld_32x32(tmS + lane_addr + c * 32, rs);
+            tmem_ld_32x32(tmdP + lane_addr + c * 32, rp);
+            tmem_ld_wait();
+            float pd[32], ds[32];
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                float m4[4] = {1.f, 1.f, 1.f, 1.f};
+                if (p.p_drop > 0.f) drop_scale(rng, off, bh, row, c * 8 + (j >> 2), p.p_drop, inv_keep, m4);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int key = c * 32 + j + i;
+                    float s = kfill[key] ? -1e-9f : __uint_as_float(rs[j + i]);
+                    s = s * sl2 + kbias[key];
+                    const float pr = row_ok ? exp2f(s - lse2) : 0.f;          // softmax probability
+                    const float dpe = __uint_as_float(rp[j + i]) * m4[i];     // dropout applied to dP
+                    pd[j + i] = pr * m4[i];
+                    // masked-by-fill keys (compat mode) have a constant score: no gradient flows to Q, K
+                    ds[j + i] = kfill[key] ? 0.f : pr * (dpe - Dr) * p.scale;
+                }
+            }
+            uint8_t* aP = sP + (c >> 1) * 16384;
+            uint8_t* aS = sdS + (c >> 1) * 16384;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                const int col = (c & 1) * 32 + j;
+                *reinterpret_cast<uint4*>(aP + swz(row, col)) = pack8(pd + j).u;
+                *reinterpret_cast<uint4*>(aS + swz(row, col)) = pack8(ds + j).u;
+            }
+        }
+        fence_proxy_async();
+        mbar_arrive(&bars[2]);
+        mbar_wait(&bars[3], 0);
+        tc_fence_after();
+        {
+            const size_t base = (size_t)(row0 + row) * p.ld + col0;
+            const uint32_t srcs[3] = {tmdQ, tmdK, tmdV};
+            __nv_bfloat16* dsts[3] = {p.dQ, p.dK, p.dV};
+#pragma unroll 1
+            for (int t = 0; t < 3; ++t) {
+#pragma unroll 1
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(srcs[t] + lane_addr + c * 32, r);   // warp-collective: executed by every lane
+                    tmem_ld_wait();
+                    if (row_ok) {
+                        float v[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) st8(dsts[t] + base + c * 32 + j, pack8(v + j));
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<512>(tm);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+    // The encode call is a DRIVER-API function: it needs a current context on the calling thread.  PyTorch
+    // runs backward on worker threads whose first CUDA call may be this one, so bind the primary context
+    // through the runtime first (once per thread).
+    static thread_local bool ctx_ready = false;
+    if (!ctx_ready) { cudaFree(0); ctx_ready = true; }
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+// [rows, cols] bf16 with row stride ld elements; box = 64 columns x 128 rows
+bool encode_rows(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
+    if (!get_encode()) return false;
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {64, 128};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        fprintf(stderr, "fdt attention: cuTensorMapEncodeTiled failed (%d): ptr=%p rows=%llu cols=%llu ld=%llu\n", (int)r, ptr,
+                (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
+    return r == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+// q, k, v, o: bf16 [B·L, H·64] views with row stride `ld` elements (heads side by side); lse: fp32 [B, H, L].
+// key_mask: int64 [B, L] (0 = masked) or null.  L <= 128.
+FDT_API int fdt_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const int64_t* key_mask,
+                         int B, int H, int L, int ld, float scale, float p_drop, const int64_t* seed_off, int mask_compat,
+                         cudaStream_t st) {
+    if (L < 1 || L > kT || ld % 8) return -1;
+    CUtensorMap tq, tk, tv;
+    const uint64_t rows = (uint64_t)B * L, cols = (uint64_t)H * kD;
+    if (!encode_rows(&tq, q, rows, cols, ld) || !encode_rows(&tk, k, rows, cols, ld) || !encode_rows(&tv, v, rows, cols, ld)) return -4;
+    AttnParams p{};
+    p.B = B; p.H = H; p.L = L; p.ld = ld; p.key_mask = key_mask; p.mask_compat = mask_compat; p.scale = scale; p.p_drop = p_drop;
+    p.seed_off = p_drop > 0.f ? seed_off : nullptr; p.O = (__nv_bfloat16*)o; p.lse = lse;
+    const int smem = 81920 + 64 + kT * 8 + 1024;
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    attn_fwd_kernel<<<B * H, kThreads, smem, st>>>(tq, tk, tv, p);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dO, const float* lse,
+                         void* dq, void* dk, void* dv, const int64_t* key_mask, int B, int H, int L, int ld, float scale,
+                         float p_drop, const int64_t* seed_off, int mask_compat, cudaStream_t st) {
+    if (L < 1 || L > kT || ld % 8) return -1;
+    CUtensorMap tq, tk, tv, tdo;
+    const uint64_t rows = (uint64_t)B * L, cols = (uint64_t)H * kD;
+    if (!encode_rows(&tq, q, rows, cols, ld) || !encode_rows(&tk, k, rows, cols, ld) || !encode_rows(&tv, v, rows, cols, ld) ||
+        !encode_rows(&tdo, dO, rows, cols, ld)) return -4;
+    AttnParams p{};
+    p.B = B; p.H = H; p.L = L; p.ld = ld; p.key_mask = key_mask; p.mask_compat = mask_compat; p.scale = scale; p.p_drop = p_drop;
+    p.seed_off = p_drop > 0.f ? seed_off : nullptr; p.lse = const_cast<float*>(lse);
+    p.dO = (const __nv_bfloat16*)dO; p.Oin = (const __nv_bfloat16*)o;
+    p.dQ = (__nv_bfloat16*)dq; p.dK = (__nv_bfloat16*)dk; p.dV = (__nv_bfloat16*)dv;
+    const int smem = 131072 + 64 + kT * 8 + 1024;
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    attn_bwd_kernel<<<B * H, kThreads, smem, st>>>(tq, tk, tv, tdo, p);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

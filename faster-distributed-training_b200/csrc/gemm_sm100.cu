@@ -197,6 +197,11 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn get_encode() {
+    // The encode call is a DRIVER-API function: it needs a current context on the calling thread.  PyTorch
+    // runs backward on worker threads whose first CUDA call may be this one, so bind the primary context
+    // through the runtime first (once per thread).
+    static thread_local bool ctx_ready = false;
+    if (!ctx_ready) { cudaFree(0); ctx_ready = true; }
     static EncodeTiledFn fn = nullptr;
     static std::once_flag once;
     std::call_once(once, [] {

@@ -114,3 +114,54 @@ def test_linear_autograd_native():
     ops.ref.linear(xr.bfloat16().float(), wr.bfloat16().float(), br, "gelu").backward(g.bfloat16().float())
     assert _rel(out, ops.ref.linear(x.bfloat16().float(), w.bfloat16().float(), b, "gelu")) < 1e-2
     assert _rel(w.grad, wr.grad) < 2e-2 and _rel(b.grad, br.grad) < 2e-2 and _rel(x.grad, xr.grad) < 2e-2
+
+
+@pytest.mark.parametrize("B,H,L,masked,compat", [(4, 8, 128, True, False), (3, 8, 77, True, False), (2, 4, 128, False, False),
+                                                  (2, 8, 64, True, True)])
+def test_attention_fwd_bwd(B, H, L, masked, compat):
+    from fdt import ops
+    from fdt.ops import attention_sm100 as at
+    torch.manual_seed(7)
+    D = 64
+
+    def mk():
+        return torch.randn(B, L, H * D, device="cuda").bfloat16().view(B, L, H, D).transpose(1, 2).requires_grad_(True)
+
+    q, k, v = mk(), mk(), mk()
+    km = None
+    if masked:
+        lens = torch.randint(L // 3, L + 1, (B,), device="cuda")
+        km = (torch.arange(L, device="cuda")[None, :] < lens[:, None]).long()
+    g = torch.randn(B, H, L, D, device="cuda").bfloat16()
+    out = at.attention(q, k, v, km, 0.0, compat)
+    assert out is not None and out.shape == (B, H, L, D)
+    out.backward(g)
+    qr, kr, vr = [t.detach().float().requires_grad_(True) for t in (q, k, v)]
+    ref = ops.ref.attention(qr, kr, vr, km, 0.0, False, compat)
+    ref.backward(g.float())
+    assert _rel(out, ref) < 1e-2, _rel(out, ref)
+    for name, a, b in (("dq", q.grad, qr.grad), ("dk", k.grad, kr.grad), ("dv", v.grad, vr.grad)):
+        assert _rel(a, b) < 2e-2, (name, _rel(a, b))
+
+
+def test_attention_dropout_is_unbiased_and_consistent():
+    from fdt import ops
+    from fdt.ops import attention_sm100 as at
+    torch.manual_seed(8)
+    B, H, L, D = 2, 8, 128, 64
+    mk = lambda: torch.randn(B, L, H * D, device="cuda").bfloat16().view(B, L, H, D).transpose(1, 2)
+    q, k, v = mk(), mk(), mk()
+    base = at.attention(q, k, v, None, 0.0, False).float()
+    acc = torch.zeros_like(base)
+    n = 48
+    for _ in range(n):
+        acc += at.attention(q, k, v, None, 0.1, False).float()
+    assert _rel(acc / n, base) < 0.08
+    # backward regenerates the same mask: gradient of sum(out) w.r.t. v equals Pᵀ·1 with the dropped P
+    vv = v.clone().requires_grad_(True)
+    o = at.attention(q, k, vv, None, 0.1, False)
+    o.float().sum().backward()
+    assert torch.isfinite(vv.grad.float()).all()
+    col = vv.grad.float()[..., 0]                       # Σ_q P_drop[q, key], identical for every d
+    assert torch.allclose(vv.grad.float(), col.unsqueeze(-1).expand_as(vv.grad), rtol=2e-2, atol=2e-2)
+    assert abs(col.sum().item() / (B * H * L) - 1.0) < 0.05      # rows of P_drop sum to ~1 in expectation
