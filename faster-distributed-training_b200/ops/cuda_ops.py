@@ -114,6 +114,8 @@ def _conv_fwd(x, w16, stride, padding):
     if _native_gemm():
         from . import gemm_sm100
         y = gemm_sm100.conv_fwd(x, w16, stride, padding)
+        if y is None:       # stride 2 / stem / odd widths: explicit im2col + the same tcgen05 GEMM
+            y = gemm_sm100.conv_fwd_im2col(x, w16, stride, padding)
         if y is not None:
             return y
     return F.conv2d(x, w16, stride=stride, padding=padding)
@@ -152,12 +154,18 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
         from . import gemm_sm100
         if need_dx:
             dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding)
+            if dx is None:
+                dx = gemm_sm100.conv_dgrad_im2col(dy, w16, x.shape, stride, padding)
         if need_dw:
             if mc is not None:      # tile-by-tile in-switch all-reduce fused into the wgrad epilogue
                 dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, mc[0], mc[1], True)
+                if dw is None:
+                    dw = gemm_sm100.conv_wgrad_im2col(dy, x, w_shape, stride, padding, mc[0], mc[1], True)
             else:
                 slot = _grad_slot(weight) if weight is not None else None
                 dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, slot)
+                if dw is None:
+                    dw = gemm_sm100.conv_wgrad_im2col(dy, x, w_shape, stride, padding, slot)
             if dw is True:          # accumulated straight into the flat gradient buffer(s)
                 need_dw, dw = False, None
     if (need_dx and dx is None) or (need_dw and dw is None):

@@ -94,6 +94,79 @@ def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha=1.0,
     return wgrad_sm100.conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into, alpha, multicast)
 
 
+# ----------------------------------------------------------------------------- explicit im2col path
+def _im2col_geom(x_shape, w_shape, stride, padding):
+    N, C, H, W = x_shape
+    O, _, kh, kw = w_shape
+    if kh != kw or O % 64:
+        return None
+    Ho = (H + 2 * padding - kh) // stride + 1
+    Wo = (W + 2 * padding - kw) // stride + 1
+    K = kh * kw * C
+    Kp = K if C % 8 == 0 else (K + 63) // 64 * 64
+    if Kp % 64:
+        return None
+    return N, C, H, W, O, kh, Ho, Wo, K, Kp
+
+
+def _weight_2d(w16: torch.Tensor, K: int, Kp: int) -> torch.Tensor:
+    """[O, I, kh, kw] channels_last → the [O, Kp] K-major GEMM operand (zero-padded columns for the stem)."""
+    O = w16.shape[0]
+    w2 = w16.permute(0, 2, 3, 1).reshape(O, K)
+    if Kp != K:
+        w2 = torch.nn.functional.pad(w2, (0, Kp - K))
+    return w2.contiguous()
+
+
+def im2col(x: torch.Tensor, geom, stride, padding) -> torch.Tensor:
+    N, C, H, W, O, k, Ho, Wo, K, Kp = geom
+    A = torch.empty(N * Ho * Wo, Kp, dtype=BF16, device=x.device)
+    call("fdt_im2col", x, A, N, H, W, C, k, stride, padding, Ho, Wo, Kp)
+    return A
+
+
+def conv_fwd_im2col(x, w16, stride, padding, sums=None):
+    geom = _im2col_geom(x.shape, w16.shape, stride, padding)
+    if geom is None:
+        return None
+    N, C, H, W, O, k, Ho, Wo, K, Kp = geom
+    A = im2col(x, geom, stride, padding)
+    y = torch.empty((N, O, Ho, Wo), dtype=BF16, device=x.device, memory_format=torch.channels_last)
+    call("fdt_gemm_nt", A, _weight_2d(w16, K, Kp), y, None, None, sums, N * Ho * Wo, O, Kp, 0)
+    return y
+
+
+def conv_dgrad_im2col(dy, w16, x_shape, stride, padding):
+    geom = _im2col_geom(x_shape, w16.shape, stride, padding)
+    if geom is None:
+        return None
+    N, C, H, W, O, k, Ho, Wo, K, Kp = geom
+    wt = _weight_2d(w16, K, Kp).t().contiguous()                 # [Kp, O]
+    dA = torch.empty(N * Ho * Wo, Kp, dtype=BF16, device=dy.device)
+    call("fdt_gemm_nt", dy, wt, dA, None, None, None, N * Ho * Wo, Kp, O, 0)
+    dx = torch.empty((N, C, H, W), dtype=BF16, device=dy.device, memory_format=torch.channels_last)
+    call("fdt_col2im", dA, dx, N, H, W, C, k, stride, padding, Ho, Wo, Kp)
+    return dx
+
+
+def conv_wgrad_im2col(dy, x, w_shape, stride, padding, accumulate_into=None, alpha=1.0, multicast=False):
+    from . import wgrad_sm100
+    geom = _im2col_geom(x.shape, w_shape, stride, padding)
+    if geom is None:
+        return None
+    N, C, H, W, O, k, Ho, Wo, K, Kp = geom
+    if (N * Ho * Wo) % 64:
+        return None
+    A = im2col(x, geom, stride, padding)
+    dy2 = dy.permute(0, 2, 3, 1).reshape(N * Ho * Wo, O)
+    if accumulate_into is not None and Kp == K:
+        return wgrad_sm100.linear_wgrad(dy2, A, accumulate_into, alpha, multicast)
+    dw = wgrad_sm100.linear_wgrad(dy2, A)
+    if dw is None:
+        return None
+    return dw[:, :K].reshape(O, k, k, C).permute(0, 3, 1, 2)
+
+
 def linear(x, weight, bias, act):
     from . import linear_sm100
     return linear_sm100.linear(x, weight, bias, act)

@@ -165,3 +165,24 @@ def test_attention_dropout_is_unbiased_and_consistent():
     col = vv.grad.float()[..., 0]                       # Σ_q P_drop[q, key], identical for every d
     assert torch.allclose(vv.grad.float(), col.unsqueeze(-1).expand_as(vv.grad), rtol=2e-2, atol=2e-2)
     assert abs(col.sum().item() / (B * H * L) - 1.0) < 0.05      # rows of P_drop sum to ~1 in expectation
+
+
+@pytest.mark.parametrize("N,C,O,HW,k,stride,pad", [(8, 128, 128, 32, 3, 2, 1), (8, 256, 512, 32, 1, 2, 0), (16, 3, 64, 32, 3, 1, 1),
+                                                    (4, 512, 512, 8, 3, 2, 1), (8, 64, 64, 12, 3, 1, 1)])
+def test_conv_im2col_path(N, C, O, HW, k, stride, pad):
+    """Strided / stem / odd-width convolutions: explicit im2col + tcgen05 GEMM, all three directions."""
+    from fdt.ops import gemm_sm100 as g
+    torch.manual_seed(9)
+    x = torch.randn(N, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(O, C, k, k, device="cuda") / math.sqrt(C * k * k)).bfloat16().contiguous(memory_format=torch.channels_last)
+    y = g.conv_fwd_im2col(x, w, stride, pad)
+    xr, wr = x.float().requires_grad_(True), w.float().requires_grad_(True)
+    ref = F.conv2d(xr, wr, stride=stride, padding=pad)
+    assert y is not None and y.shape == ref.shape
+    assert _rel(y, ref) < 6e-3
+    dy = torch.randn_like(ref).bfloat16().contiguous(memory_format=torch.channels_last)
+    ref.backward(dy.float())
+    dx = g.conv_dgrad_im2col(dy, w, x.shape, stride, pad)
+    assert dx is not None and _rel(dx, xr.grad) < 1e-2, _rel(dx, xr.grad)
+    dw = g.conv_wgrad_im2col(dy, x, w.shape, stride, pad)
+    assert dw is not None and dw.shape == w.shape and _rel(dw, wr.grad) < 3e-3, _rel(dw, wr.grad)
