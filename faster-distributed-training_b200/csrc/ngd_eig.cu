@@ -247,3 +247,98 @@ FDT_API int fdt_ngd_eig_update_multi(const void* descs, int count, int max_sweep
     FDT_CHECK_LAUNCH();
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Fused element-wise tails of the NGD step (ngd_optimizer.py:151-168 and the state hand-over at
+// :322-324), which in tensor-op form cost ~10 + ~15 tiny launches per factor batch.
+namespace {
+
+// sums[f] = Σ X_f², sums[n + f] = Σ X̂_f²  (sums zeroed by the caller); grid (chunks, n)
+__global__ void __launch_bounds__(256)
+ngd_sumsq2_kernel(const float* __restrict__ X, const float* __restrict__ Xh, float* __restrict__ sums, int n, int64_t M) {
+    const int f = blockIdx.y;
+    const float* x = X + (int64_t)f * M;
+    const float* xh = Xh + (int64_t)f * M;
+    float a = 0.f, b = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (int64_t)gridDim.x * blockDim.x) {
+        const float u = x[i], v = xh[i];
+        a += u * u; b += v * v;
+    }
+    a = warp_sum(a); b = warp_sum(b);
+    __shared__ float ra[8], rb[8];
+    if ((threadIdx.x & 31) == 0) { ra[threadIdx.x >> 5] = a; rb[threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float ta = 0.f, tb = 0.f;
+        for (int i = 0; i < 8; ++i) { ta += ra[i]; tb += rb[i]; }
+        atomicAdd(sums + f, ta);
+        atomicAdd(sums + n + f, tb);
+    }
+}
+// out_f = isnan(p1) ? X_f : X̂_f · sqrt(p0 / (p1 + 1e-30))
+__global__ void __launch_bounds__(256)
+ngd_rescale_kernel(const float* __restrict__ X, const float* __restrict__ Xh, const float* __restrict__ sums,
+                   float* __restrict__ out, int n, int64_t M) {
+    const int f = blockIdx.y;
+    const float p0 = sums[f], p1 = sums[n + f];
+    const bool bad = isnan(p1);
+    const float sc = sqrtf(p0 / (p1 + 1.0e-30f));
+    const float* x = X + (int64_t)f * M;
+    const float* xh = Xh + (int64_t)f * M;
+    float* o = out + (int64_t)f * M;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (int64_t)gridDim.x * blockDim.x)
+        o[i] = bad ? x[i] : xh[i] * sc;
+}
+
+struct NgdCommitDesc {          // one per factor; mirrored in fdt/ops/cuda_ops.py
+    const float *W1, *d1, *rho1;
+    float *W, *d, *rho;
+    int R, D;
+};
+static_assert(sizeof(NgdCommitDesc) == 56, "descriptor layout is mirrored in python");
+
+// a factor whose refresh produced a non-finite number keeps its previous (W, d, rho)
+__global__ void __launch_bounds__(256)
+ngd_commit_kernel(const NgdCommitDesc* __restrict__ descs) {
+    const NgdCommitDesc c = descs[blockIdx.x];
+    const int nW = c.R * c.D;
+    int bad = 0;
+    for (int i = threadIdx.x; i < nW; i += blockDim.x) bad |= !isfinite(c.W1[i]);
+    for (int i = threadIdx.x; i < c.R; i += blockDim.x) bad |= !isfinite(c.d1[i]);
+    if (threadIdx.x == 0) bad |= !isfinite(c.rho1[0]);
+    bad = __syncthreads_or(bad);
+    if (bad) return;
+    for (int i = threadIdx.x; i < nW; i += blockDim.x) c.W[i] = c.W1[i];
+    for (int i = threadIdx.x; i < c.R; i += blockDim.x) c.d[i] = c.d1[i];
+    if (threadIdx.x == 0) c.rho[0] = c.rho1[0];
+}
+
+}  // namespace
+
+// sums: [2n] zero on entry.  X, Xh: [n, M] contiguous fp32.
+FDT_API int fdt_ngd_sumsq2(const float* X, const float* Xh, float* sums, int n, int64_t M, cudaStream_t st) {
+    int chunks = (int)((M + 256 * 8 - 1) / (256 * 8));
+    if (chunks < 1) chunks = 1;
+    const int cap = (148 * 8 + n - 1) / n;
+    if (chunks > cap) chunks = cap;
+    ngd_sumsq2_kernel<<<dim3(chunks, n), 256, 0, st>>>(X, Xh, sums, n, M);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_ngd_rescale(const float* X, const float* Xh, const float* sums, float* out, int n, int64_t M, cudaStream_t st) {
+    int chunks = (int)((M + 256 * 4 - 1) / (256 * 4));
+    if (chunks < 1) chunks = 1;
+    const int cap = (148 * 8 + n - 1) / n;
+    if (chunks > cap) chunks = cap;
+    ngd_rescale_kernel<<<dim3(chunks, n), 256, 0, st>>>(X, Xh, sums, out, n, M);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_ngd_commit_multi(const void* descs, int count, cudaStream_t st) {
+    if (count <= 0) return 0;
+    ngd_commit_kernel<<<count, 256, 0, st>>>((const NgdCommitDesc*)descs);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

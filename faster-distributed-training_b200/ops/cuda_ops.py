@@ -480,3 +480,38 @@ def ngd_eig_update_multi(pending, max_sweeps: int = 12):
         ent = (dev, len(rows), [fb for fb in pending])     # keep the batches (and their buffers) alive
         _desc_cache[key] = ent
     call("fdt_ngd_eig_update_multi", ent[0], ent[1], int(max_sweeps))
+
+
+def ngd_norms_rescale(X: torch.Tensor, Xhat: torch.Tensor):
+    """(p0, out): p0[f] = ΣX_f², out_f = X̂_f·sqrt(p0/(p1+1e-30)) (X_f if p1 is NaN), written in place into
+    ``Xhat``.  Three launches (memset, reduce, rescale) instead of ~10 tensor ops."""
+    n = X.shape[0]
+    M = X[0].numel()
+    sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
+    call("fdt_ngd_sumsq2", X, Xhat, sums, n, i64(M))
+    call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(M))
+    return sums[:n], Xhat
+
+
+_commit_cache = {}
+
+
+def ngd_commit_multi(pending):
+    """Guarded hand-over W←W1, d←d1, rho←rho1 for every factor of every pending batch: one launch."""
+    import struct
+    key = tuple(id(fb) for fb in pending)
+    ent = _commit_cache.get(key)
+    if ent is None:
+        rows = []
+        for fb in pending:
+            R, D = fb.R, fb.D
+            for f in range(fb.n):
+                rows.append(struct.pack("<6Q2i", fb.W1.data_ptr() + f * R * D * 4, fb.d1.data_ptr() + f * R * 4,
+                                        fb.rho1.data_ptr() + f * 4, fb.W.data_ptr() + f * R * D * 4,
+                                        fb.d.data_ptr() + f * R * 4, fb.rho.data_ptr() + f * 4, R, D))
+        blob = b"".join(rows)
+        dev = torch.empty(len(blob), dtype=torch.uint8, device=pending[0].W.device)
+        dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
+        ent = (dev, len(rows), list(pending))
+        _commit_cache[key] = ent
+    call("fdt_ngd_commit_multi", ent[0], ent[1])

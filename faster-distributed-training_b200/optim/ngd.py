@@ -155,6 +155,7 @@ def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
         fb.K = torch.empty(n, R, R, **kw)
         fb.L = torch.empty(n, R, R, **kw)
         fb.A = torch.empty(n, R, R, **kw)
+        fb.W1 = torch.empty(n, R, D, **kw)
         fb.wc = torch.empty(n, R, **kw)
         fb.d1 = torch.empty(n, R, **kw)
         fb.rho1 = torch.empty(n, **kw)
@@ -220,9 +221,11 @@ def flush_refreshes(pending: List[FactorBatch]):
         native = ops.use_native(fb0.K)
     if native:
         from .. import ops
-        ops._cu().ngd_eig_update_multi(pending)
-        for fb in pending:
-            _apply_refresh(fb, fb.A, fb.wc, fb.d1, fb.rho1)
+        cu = ops._cu()
+        cu.ngd_eig_update_multi(pending)
+        for fb in pending:                              # W1 = A (J + w_coeff ∘ W)
+            torch.bmm(fb.A, torch.addcmul(fb.J, fb.wc.unsqueeze(2), fb.W), out=fb.W1)
+        cu.ngd_commit_multi(pending)                    # guarded W←W1, d←d1, rho←rho1: one launch for all factors
     else:
         for fb in pending:
             A, w_coeff, d1, rho1 = fisher_update_torch(fb, fb.J, fb.K, fb.L, fb.tr)
@@ -242,7 +245,12 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
     computes W_{t+1}, ngd_optimizer.py:195-203), so when ``pending`` is given the refresh is
     deferred: its statistics are computed here and the factor batch is appended to ``pending``
     for :func:`flush_refreshes`."""
-    p0 = (Xm * Xm).sum((1, 2))
+    native = False
+    if Xm.is_cuda and Xm.dtype == torch.float32:
+        from .. import ops
+        native = ops.use_native(Xm)
+    Xc = Xm.contiguous() if native else Xm
+    p0 = None if native else (Xm * Xm).sum((1, 2))
 
     def project():
         W = fb.W
@@ -254,12 +262,25 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
 
     if fb.t == 0:
         # warm start: 3 refreshes on the same gradient (ngd_optimizer.py:356-376)
+        if p0 is None:
+            p0 = (Xm * Xm).sum((1, 2))
         for _ in range(3):
             H, _ = project()
             _refresh(fb, Xm, left, H, p0)
     updating = fb.updating()
     fb.t += 1
     H, Xhat = project()
+    if native:
+        from .. import ops
+        p0, out = ops._cu().ngd_norms_rescale(Xc, Xhat)      # fused Σx², Σx̂², rescale + NaN guard
+        if updating:
+            if pending is None:
+                _refresh(fb, Xm, left, H, p0)
+            else:
+                _statistics(fb, Xm, left, H)
+                fb.tr.copy_(p0)
+                pending.append(fb)
+        return out
     if updating:
         if pending is None:
             _refresh(fb, Xm, left, H, p0)
