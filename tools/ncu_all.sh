@@ -1,0 +1,20 @@
+#!/usr/bin/env bash
+# One ncu --set full capture per named kernel (single GPU).  Each capture runs only after the same
+# command has exited 0 without ncu, as the profiling recipe requires.
+set -u
+mkdir -p gpurun_out
+cap() {  # name target regex skip
+  python tools/ncu_target.py "$2" > gpurun_out/plain_$1.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k "regex:$3" -s "$4" -c 1 -o gpurun_out/prof_$1 \
+      python tools/ncu_target.py "$2" > gpurun_out/ncu_$1.log 2>&1
+  tail -1 gpurun_out/ncu_$1.log
+}
+cap conv3x3 conv3x3 gemm_nt 2
+cap conv1x1 conv1x1 gemm_nt 2
+cap gemm gemm gemm_nt 1
+cap wgrad wgrad wgrad_kernel 2
+cap attn_fwd attn attn_fwd 1
+cap attn_bwd attn attn_bwd 1
+cap chan_affine chan_affine chan_affine 2
+cap chan_reduce chan_reduce chan_reduce2 2
+cap ngd_eig ngd_eig ngd_eig 2

@@ -35,5 +35,26 @@ elif what in ("chan_affine", "chan_reduce"):
             call("fdt_chan_affine_act", y, None, None, o, coef, i64(P), C, 1)
         else:
             call("fdt_chan_reduce2", y, y, None, None, sums, i64(P), C, 0)
+elif what == "wgrad":
+    from fdt.ops import wgrad_sm100 as wg
+    C, O, HW, k = 256, 256, 8, 3
+    x = torch.randn(B, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(B, O, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    for _ in range(5):
+        dw = wg.conv_wgrad(dy, x, (O, C, k, k), 1, 1)
+elif what == "attn":
+    from fdt.ops import attention_sm100 as at
+    Bt, H, L = 64, 8, 128
+    mk = lambda: torch.randn(Bt, L, H * 64, device="cuda").bfloat16().view(Bt, L, H, 64).transpose(1, 2).requires_grad_(True)
+    q, k_, v = mk(), mk(), mk()
+    for _ in range(4):
+        o = at.attention(q, k_, v, None, 0.1, False)
+        o.backward(torch.ones_like(o))
+elif what == "ngd_eig":
+    from fdt.optim import ngd as M
+    fb = M.FactorBatch(148, 576, 512, 4.0, -1, 4, 0.1, torch.float32, "cuda")
+    for it in range(6):
+        X = torch.randn(148, 576, 512, device="cuda")
+        M.precondition(fb, X, left=False)
 torch.cuda.synchronize()
 print("ok", what)
