@@ -53,7 +53,8 @@ struct SmemLayout {
 
 template <int BN, int kStages, bool kConv>
 __global__ void __launch_bounds__(kThreads, 2)
-gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
     using L = SmemLayout<BN, kStages>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -170,17 +171,34 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 atomicAdd(p.sums + col0 + lane, s1[0]);
                 atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
             }
-            if (row_ok) {
-                if (p.out) {
-                    __nv_bfloat16* o = p.out + (size_t)row * p.N + col0;
+            if (p.out) {
+                // bf16 tile → shared memory in the 128B-swizzled layout of the output tensor map (the operand
+                // ring is free: every MMA that read it has completed), stored below by TMA in full lines
+                uint8_t* atom = smem + (c >> 1) * 16384;
+                const int r_in = q * 32 + lane;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 8) st8(o + j, pack8(v + j));
+                for (int j = 0; j < 32; j += 8) {
+                    const int col = (c & 1) * 32 + j;
+                    const uint32_t off = (uint32_t)(r_in * 128 + ((((col >> 3) ^ (r_in & 7)) << 4)));
+                    *reinterpret_cast<uint4*>(atom + off) = pack8(v + j).u;
                 }
+            }
+            if (row_ok) {
                 if (p.out_f32) {
                     float* o = p.out_f32 + (size_t)row * p.N + col0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 }
+            }
+        }
+        if (p.out) {
+            fence_proxy_async();
+            asm volatile("bar.sync 1, 128;" ::: "memory");          // the 4 epilogue warps
+            if (threadIdx.x == 64) {
+#pragma unroll
+                for (int a = 0; a < BN / 64; ++a)
+                    tma_store_2d(&tmC, smem + a * 16384, n_tile * BN + a * 64, m_tile * BM);
+                tma_store_commit_and_wait_read();
             }
         }
     }
@@ -238,13 +256,16 @@ bool encode_nhwc(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, i
 
 template <int BN, bool kConv>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t st) {
+    CUtensorMap tmC;
+    if (p.out) { if (!encode_2d(&tmC, p.out, p.N, p.M, 64, BM)) return -4; }
+    else tmC = tmB;
     constexpr int kStages = (BN == 128) ? 3 : 4;      // ~96 KB of tiles → two CTAs per SM overlap prologue/epilogue
     using L = SmemLayout<BN, kStages>;
     auto kern = gemm_nt_kernel<BN, kStages, kConv>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return (int)e;
     dim3 grid((p.M + BM - 1) / BM, p.N / BN);
-    kern<<<grid, kThreads, L::kTotal, st>>>(tmA, tmB, p);
+    kern<<<grid, kThreads, L::kTotal, st>>>(tmA, tmB, tmC, p);
     FDT_CHECK_LAUNCH();
     return 0;
 }
