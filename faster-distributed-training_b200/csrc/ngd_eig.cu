@@ -297,20 +297,32 @@ struct NgdCommitDesc {          // one per factor; mirrored in fdt/ops/cuda_ops.
 };
 static_assert(sizeof(NgdCommitDesc) == 56, "descriptor layout is mirrored in python");
 
-// a factor whose refresh produced a non-finite number keeps its previous (W, d, rho)
+// a factor whose refresh produced a non-finite number keeps its previous (W, d, rho).
+// Two passes so that a large factor (the 80 x 30522 token-embedding factor) is spread over many CTAs:
+// pass 1 raises bad[f] if anything is non-finite, pass 2 copies where bad[f] == 0.   grid = (chunks, factors)
 __global__ void __launch_bounds__(256)
-ngd_commit_kernel(const NgdCommitDesc* __restrict__ descs) {
-    const NgdCommitDesc c = descs[blockIdx.x];
+ngd_check_kernel(const NgdCommitDesc* __restrict__ descs, int* __restrict__ bad_flags) {
+    const NgdCommitDesc c = descs[blockIdx.y];
     const int nW = c.R * c.D;
     int bad = 0;
-    for (int i = threadIdx.x; i < nW; i += blockDim.x) bad |= !isfinite(c.W1[i]);
-    for (int i = threadIdx.x; i < c.R; i += blockDim.x) bad |= !isfinite(c.d1[i]);
-    if (threadIdx.x == 0) bad |= !isfinite(c.rho1[0]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nW; i += gridDim.x * blockDim.x) bad |= !isfinite(c.W1[i]);
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < c.R; i += blockDim.x) bad |= !isfinite(c.d1[i]);
+        if (threadIdx.x == 0) bad |= !isfinite(c.rho1[0]);
+    }
     bad = __syncthreads_or(bad);
-    if (bad) return;
-    for (int i = threadIdx.x; i < nW; i += blockDim.x) c.W[i] = c.W1[i];
-    for (int i = threadIdx.x; i < c.R; i += blockDim.x) c.d[i] = c.d1[i];
-    if (threadIdx.x == 0) c.rho[0] = c.rho1[0];
+    if (bad && threadIdx.x == 0) atomicOr(bad_flags + blockIdx.y, 1);
+}
+__global__ void __launch_bounds__(256)
+ngd_copy_kernel(const NgdCommitDesc* __restrict__ descs, const int* __restrict__ bad_flags) {
+    if (bad_flags[blockIdx.y]) return;
+    const NgdCommitDesc c = descs[blockIdx.y];
+    const int nW = c.R * c.D;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nW; i += gridDim.x * blockDim.x) c.W[i] = c.W1[i];
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < c.R; i += blockDim.x) c.d[i] = c.d1[i];
+        if (threadIdx.x == 0) c.rho[0] = c.rho1[0];
+    }
 }
 
 }  // namespace
@@ -336,9 +348,15 @@ FDT_API int fdt_ngd_rescale(const float* X, const float* Xh, const float* sums, 
     return 0;
 }
 
-FDT_API int fdt_ngd_commit_multi(const void* descs, int count, cudaStream_t st) {
+// flags: `count` ints of caller-provided scratch.  max_elems = largest R*D among the factors (sizes the grid).
+FDT_API int fdt_ngd_commit_multi(const void* descs, int count, int* flags, int max_elems, cudaStream_t st) {
     if (count <= 0) return 0;
-    ngd_commit_kernel<<<count, 256, 0, st>>>((const NgdCommitDesc*)descs);
+    int chunks = (max_elems + 256 * 8 - 1) / (256 * 8);
+    if (chunks < 1) chunks = 1;
+    if (chunks > 64) chunks = 64;
+    cudaMemsetAsync(flags, 0, sizeof(int) * count, st);
+    ngd_check_kernel<<<dim3(chunks, count), 256, 0, st>>>((const NgdCommitDesc*)descs, flags);
+    ngd_copy_kernel<<<dim3(chunks, count), 256, 0, st>>>((const NgdCommitDesc*)descs, flags);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -512,6 +512,7 @@ def ngd_commit_multi(pending):
         blob = b"".join(rows)
         dev = torch.empty(len(blob), dtype=torch.uint8, device=pending[0].W.device)
         dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
-        ent = (dev, len(rows), list(pending))
+        flags = torch.zeros(len(rows), dtype=torch.int32, device=dev.device)
+        ent = (dev, len(rows), list(pending), flags, max(fb.R * fb.D for fb in pending))
         _commit_cache[key] = ent
-    call("fdt_ngd_commit_multi", ent[0], ent[1])
+    call("fdt_ngd_commit_multi", ent[0], ent[1], ent[3], ent[4], launches=3)
