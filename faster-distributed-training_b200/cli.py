@@ -136,8 +136,19 @@ class ResNetStep:
 
     def __call__(self, engine, batch):
         images, targets = batch
-        x = cifar_data.gpu_transform(images, train=True) if images.dtype == torch.uint8 else images
         targets = targets.long()
+        if self.meta is None and images.dtype == torch.uint8 and ops.use_native(images):
+            # one kernel: crop + flip + normalise of both partners, λ-blend, bf16 NHWC out
+            lam = mx.sample_beta(self.alpha, images.device)
+            index = mx.randperm(images.size(0), images.device)
+            x = ops._cu().input_aug_mixup(images, True, index, lam, cifar_data.MEAN, cifar_data.STD)
+            ya, yb = targets, targets[index]
+            logits = engine(x)
+            loss = mx.mixup_criterion(logits, ya, yb, lam)
+            with torch.no_grad():
+                correct = mx.mixup_correct(logits, ya, yb, lam)
+            return loss, correct
+        x = cifar_data.gpu_transform(images, train=True) if images.dtype == torch.uint8 else images
         if self.meta is not None:
             x, ya, yb, lam = self.meta(x, targets)
             lam = lam.reshape(-1)

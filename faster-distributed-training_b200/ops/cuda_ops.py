@@ -245,10 +245,56 @@ def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_bat
     return _ConvBNAct.apply(x, weight, gamma, beta, residual, cfg)
 
 
+class _PoolFC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        x = _nhwc(x)
+        N, C, H, W = x.shape
+        K = weight.shape[0]
+        w = weight.detach().float().contiguous()
+        pooled = torch.empty(N, C, dtype=torch.float32, device=x.device)
+        logits = torch.empty(N, K, dtype=torch.float32, device=x.device)
+        call("fdt_pool_fc_fwd", x, w, None if bias is None else bias.detach().float().contiguous(), pooled, logits,
+             N, H * W, C, K)
+        ctx.save_for_backward(w, pooled)
+        ctx.geom = (N, C, H, W, K, bias is not None)
+        return logits
+
+    @staticmethod
+    def backward(ctx, g):
+        w, pooled = ctx.saved_tensors
+        N, C, H, W, K, has_bias = ctx.geom
+        g = g.float().contiguous()
+        dx = torch.empty((N, C, H, W), dtype=BF16, device=g.device, memory_format=torch.channels_last) \
+            if ctx.needs_input_grad[0] else None
+        dW = torch.zeros(K, C, dtype=torch.float32, device=g.device)
+        db = torch.zeros(K, dtype=torch.float32, device=g.device) if has_bias else None
+        call("fdt_pool_fc_bwd", g, w, pooled, dx, dW, db, N, H * W, C, K)
+        return dx, dW, db
+
+
 def pool_fc(x, weight, bias):
-    # [N, C, H, W] bf16 NHWC → fp32 logits; tiny (B x 2048 x 10)
-    pooled = x.float().mean(dim=(2, 3))
-    return F.linear(pooled, weight, bias)
+    """[N, C, H, W] bf16 NHWC → fp32 logits: global average pool + Linear in one kernel each way."""
+    if weight.shape[0] > 32 or weight.shape[1] * 4 > 48 * 1024:
+        return F.linear(x.float().mean(dim=(2, 3)), weight, bias)
+    return _PoolFC.apply(x, weight, bias)
+
+
+def input_aug_mixup(images_u8: torch.Tensor, train: bool, perm=None, lam=None, mean=None, std=None, pad: int = 4):
+    """uint8 [B,H,W,3] → bf16 logical [B,3,H,W] (NHWC memory): crop + flip + normalise [+ mixup blend]."""
+    B, H, W, C = images_u8.shape
+    assert C == 3 and images_u8.dtype == torch.uint8
+    out = torch.empty((B, 3, H, W), dtype=BF16, device=images_u8.device, memory_format=torch.channels_last)
+    so = _next_seed_off(images_u8.device) if train else None
+    lam_t = None
+    if lam is not None:
+        lam_t = lam.detach().reshape(-1).float().contiguous()
+    import ctypes
+    m3 = (ctypes.c_float * 3)(*mean)
+    s3 = (ctypes.c_float * 3)(*std)
+    call("fdt_input_aug_mixup", images_u8.contiguous(), perm, lam_t, 0 if lam_t is None else lam_t.numel(), so, out,
+         B, H, W, pad, int(bool(train)), m3, s3)
+    return out
 
 
 # ----------------------------------------------------------------------------- mixup
@@ -404,8 +450,13 @@ def embed(tokens, token_types, tok_w, pos_w, seg_w, scale):
 
 
 def mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat):
-    # B x 512 → 1024 → n_class: negligible work; differentiable torch ops in fp32
-    return ref.mlp_head(x.float(), W1, b1, W2, b2, bias_grad_mean_compat)
+    """Linear → ReLU (tcgen05 GEMM with fused bias+ReLU epilogue) → Linear(hidden → n_class) (4-wide: torch)."""
+    if bias_grad_mean_compat:
+        B = x.shape[0]
+        b1 = ref._ScaleGrad.apply(b1, 1.0 / B)
+        b2 = ref._ScaleGrad.apply(b2, 1.0 / B)
+    h = linear(x, W1, b1, "relu")
+    return F.linear(h.float(), W2, b2.reshape(-1))
 
 
 class _DropoutAdd(torch.autograd.Function):

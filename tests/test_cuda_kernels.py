@@ -214,3 +214,50 @@ def test_flat_kernels():
     bad = torch.full((8,), float("nan"), device=DEV)
     cu.clip_scale_(bad, cu.sqnorm(bad), 10.0, sk)
     assert sk.item() == 1 and (bad == 0).all()
+
+
+def test_pool_fc_fwd_bwd():
+    ops = _ops()
+    torch.manual_seed(8)
+    x = torch.randn(32, 2048, 4, 4, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(10, 2048, device=DEV) / 45).requires_grad_(True)
+    b = torch.randn(10, device=DEV).requires_grad_(True)
+    g = torch.randn(32, 10, device=DEV)
+    xn = x.clone().requires_grad_(True)
+    out = ops.pool_fc(xn, w, b)
+    out.backward(g)
+    xr, wr, br = x.float().requires_grad_(True), w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    ref = ops.ref.pool_fc(xr, wr, br)
+    ref.backward(g)
+    _close(out, ref, 1e-4, 1e-4, "logits")
+    _relnorm(xn.grad, xr.grad, 1e-2, "dx")
+    _relnorm(w.grad, wr.grad, 1e-4, "dW")
+    _relnorm(b.grad, br.grad, 1e-5, "db")
+
+
+def test_input_aug_mixup_kernel():
+    ops = _ops()
+    from fdt.data import cifar
+    cu = ops._cu()
+    torch.manual_seed(9)
+    imgs = torch.randint(0, 256, (16, 32, 32, 3), dtype=torch.uint8, device=DEV)
+    # eval mode: plain normalise, exact against the torch definition
+    out = cu.input_aug_mixup(imgs, False, None, None, cifar.MEAN, cifar.STD)
+    ref = cifar.gpu_transform(imgs, train=False)
+    assert out.shape == (16, 3, 32, 32) and out.is_contiguous(memory_format=torch.channels_last)
+    _close(out, ref, 1e-2, 2e-2, "normalise")
+    # train + mixup: lam = 1 must return an augmented version of each image (values from the image or padding)
+    perm = torch.randperm(16, device=DEV)
+    one = torch.ones((), device=DEV)
+    aug = cu.input_aug_mixup(imgs, True, perm, one, cifar.MEAN, cifar.STD).float()
+    pad_val = torch.tensor([(0 - m) / s for m, s in zip(cifar.MEAN, cifar.STD)], device=DEV).view(1, 3, 1, 1)
+    frac_pad = ((aug - pad_val).abs() < 2e-2).float().mean().item()
+    assert 0.0 < frac_pad < 0.4
+    # blend linearity: lam=0.3 equals 0.3*T(x) + 0.7*T(x[perm]) when the same augmentation draw is used
+    st = cu._seed_state[imgs.device].clone()
+    a = cu.input_aug_mixup(imgs, True, perm, one, cifar.MEAN, cifar.STD).float()
+    cu._seed_state[imgs.device].copy_(st)
+    b = cu.input_aug_mixup(imgs, True, perm, torch.zeros((), device=DEV), cifar.MEAN, cifar.STD).float()
+    cu._seed_state[imgs.device].copy_(st)
+    c = cu.input_aug_mixup(imgs, True, perm, torch.full((), 0.3, device=DEV), cifar.MEAN, cifar.STD).float()
+    _close(c, 0.3 * a + 0.7 * b, 2e-2, 3e-2, "blend")
