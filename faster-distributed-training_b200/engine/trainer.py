@@ -127,15 +127,18 @@ class Trainer:
                 self._prime_constants(batch)
             return out
         static = self._copy_in(batch)
+        from ..ops import _lib
         if kind not in self._graphs:
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
+            n0 = _lib.LAUNCHES.count
             with torch.cuda.graph(g):
                 out = self._eager_step(static)
-            self._graphs[kind] = (g, out)
+            self._graphs[kind] = (g, out, _lib.LAUNCHES.count - n0)     # native launches recorded in this graph
             return out
-        g, out = self._graphs[kind]
+        g, out, n_native = self._graphs[kind]
         g.replay()
+        _lib.LAUNCHES.add("graph_replay", n_native)                      # they run again on every replay
         adv = getattr(self.optimizer, "advance_without_python", None)
         if adv is not None:
             adv()

@@ -160,6 +160,16 @@ def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
         fb.d1 = torch.empty(n, R, **kw)
         fb.rho1 = torch.empty(n, **kw)
         fb.tr = torch.empty(n, **kw)
+    if getattr(fb, "_h_rows", False):
+        # H is [n, N, R] for both layouts (tcgen05 path): J on the tensor cores, L / K are R x R
+        from .. import ops
+        ops._cu().ngd_stats_j(H, Xm, fb.J, left)
+        if fb.N > fb.D:
+            torch.bmm(fb.J, W.transpose(1, 2), out=fb.L)
+        else:
+            torch.bmm(H.transpose(1, 2), H, out=fb.L)
+        torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+        return
     S = _split_factor(fb.N)
     if left:   # Xm: [n, D, N], H: [n, R, N];  J = H Xᵀ reduces over N
         if S > 1:
@@ -264,11 +274,26 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
         # warm start: 3 refreshes on the same gradient (ngd_optimizer.py:356-376)
         if p0 is None:
             p0 = (Xm * Xm).sum((1, 2))
+        fb._h_rows = False
         for _ in range(3):
             H, _ = project()
             _refresh(fb, Xm, left, H, p0)
     updating = fb.updating()
     fb.t += 1
+    if native:
+        from .. import ops
+        cu = ops._cu()
+        if cu.ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, left):
+            fb._h_rows = True
+            H, out, p0, _ = cu.ngd_project(Xc, fb.W, left)   # tcgen05 tf32: H, X̂ (+Σx², Σx̂²), rescale
+            if updating:
+                if pending is None:
+                    _refresh(fb, Xc, left, H, p0)
+                else:
+                    _statistics(fb, Xc, left, H)
+                    fb.tr.copy_(p0)
+                    pending.append(fb)
+            return out
     H, Xhat = project()
     if native:
         from .. import ops

@@ -261,3 +261,27 @@ def test_input_aug_mixup_kernel():
     cu._seed_state[imgs.device].copy_(st)
     c = cu.input_aug_mixup(imgs, True, perm, torch.full((), 0.3, device=DEV), cifar.MEAN, cifar.STD).float()
     _close(c, 0.3 * a + 0.7 * b, 2e-2, 3e-2, "blend")
+
+
+@pytest.mark.parametrize("n,N,D,R,left", [(2, 256, 64, 32, False), (3, 200, 64, 32, True), (2, 100, 160, 80, False),
+                                           (1, 4608, 512, 80, True)])
+def test_ngd_tf32_tcgen05_gemms(n, N, D, R, left):
+    """Opt-in batched kind::tf32 kernels for H = XWᵀ, X̂ = X − HW (+norms) and J = HᵀX."""
+    ops = _ops()
+    cu = ops._cu()
+    torch.manual_seed(11)
+    X = torch.randn(n, N, D, device=DEV)
+    W = torch.randn(n, R, D, device=DEV) * 0.1
+    Xin = X.transpose(1, 2).contiguous() if left else X
+    H, out, p0, _ = cu.ngd_project(Xin, W, left)
+    Href = torch.bmm(X, W.transpose(1, 2))
+    Xhref = X - torch.bmm(Href, W)
+    scale = torch.sqrt((X * X).sum((1, 2)) / (Xhref * Xhref).sum((1, 2)))
+    want = Xhref * scale[:, None, None]
+    got = out.transpose(1, 2) if left else out
+    _relnorm(H, Href, 3e-3, "H")
+    _relnorm(got, want, 5e-3, "rescaled Xhat")
+    _relnorm(p0, (X * X).sum((1, 2)), 1e-5, "p0")
+    J = torch.zeros(n, R, D, device=DEV)
+    cu.ngd_stats_j(Href.contiguous(), Xin, J, left)
+    _relnorm(J, torch.bmm(Href.transpose(1, 2), X), 3e-3, "J")
