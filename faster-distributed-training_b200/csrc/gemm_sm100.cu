@@ -47,33 +47,42 @@ struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kBarOff = kStages * kStageBytes;
-    static constexpr int kTotal = kBarOff + (2 * kStages + 1) * 8 + 16 + 1024;   // + alignment slack
+    static constexpr int kCOff = kStages * kStageBytes;           // bf16 output staging: BN/64 atoms of 16 KB
+    static constexpr int kCBytes = (BN / 64) * 16384;
+    static constexpr int kBarOff = kCOff + kCBytes;
+    static constexpr int kTotal = kBarOff + (2 * kStages + 4) * 8 + 16 + 1024;   // + alignment slack
 };
 
+// Persistent: gridDim.x CTAs (<= #SMs) walk the tile list (m fastest, so neighbouring CTAs share the weight
+// tile in L2).  The accumulator is double-buffered in tensor memory (2 x BN columns): while the epilogue warps
+// drain tile i (tcgen05.ld → bias/act/stats → swizzled smem → TMA store), the MMA warp already runs tile i+1.
 template <int BN, int kStages, bool kConv>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 1)
 gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
     using L = SmemLayout<BN, kStages>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sC = smem + L::kCOff;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
     uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* tmem_full_bar = empty_bar + kStages;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    uint64_t* tmem_full_bar = empty_bar + kStages;       // [2]
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+    const int tiles_m = (p.M + BM - 1) / BM, tiles_n = p.N / BN;
+    const int num_tiles = tiles_m * tiles_n;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA);
         prefetch_tmap(&tmB);
+        prefetch_tmap(&tmC);
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        mbar_init(tmem_full_bar, 1);
+        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 128); }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc<BN>(tmem_ptr);
+    if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -81,130 +90,151 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     if (warp == 0) {
         if (lane == 0) {
-            int n0 = 0, h0 = 0;
-            if (kConv) {
-                if (p.bn == 1) { const int tpi = p.H / p.bh; n0 = m_tile / tpi; h0 = (m_tile % tpi) * p.bh; }
-                else { n0 = m_tile * p.bn; }
-            }
-            for (int kb = 0; kb < p.num_kb; ++kb) {
-                const int s = kb % kStages;
-                const uint32_t ph = (kb / kStages) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                uint8_t* sA = smem + s * L::kStageBytes;
-                uint8_t* sB = sA + L::kABytes;
-                mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+            uint32_t it = 0;                                        // running k-block counter across tiles
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m_tile = tile % tiles_m, n_tile = tile / tiles_m;
+                int n0 = 0, h0 = 0;
                 if (kConv) {
-                    const int tap = kb / p.cpb, cb = kb - tap * p.cpb;
-                    const int r = tap / p.kw, sx = tap - r * p.kw;
-                    tma_load_4d(sA, &tmA, &full_bar[s], cb * BK, sx - p.pad, h0 + r - p.pad, n0);
-                } else {
-                    tma_load_2d(sA, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+                    if (p.bn == 1) { const int tpi = p.H / p.bh; n0 = m_tile / tpi; h0 = (m_tile % tpi) * p.bh; }
+                    else { n0 = m_tile * p.bn; }
                 }
-                tma_load_2d(sB, &tmB, &full_bar[s], kb * BK, n_tile * BN);
+                for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* sA = smem + s * L::kStageBytes;
+                    uint8_t* sB = sA + L::kABytes;
+                    mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+                    if (kConv) {
+                        const int tap = kb / p.cpb, cb = kb - tap * p.cpb;
+                        const int r = tap / p.kw, sx = tap - r * p.kw;
+                        tma_load_4d(sA, &tmA, &full_bar[s], cb * BK, sx - p.pad, h0 + r - p.pad, n0);
+                    } else {
+                        tma_load_2d(sA, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+                    }
+                    tma_load_2d(sB, &tmB, &full_bar[s], kb * BK, n_tile * BN);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
-            for (int kb = 0; kb < p.num_kb; ++kb) {
-                const int s = kb % kStages;
-                const uint32_t ph = (kb / kStages) & 1;
-                mbar_wait(&full_bar[s], ph);
+            uint32_t it = 0, t = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+                const uint32_t acc = t & 1, use = t >> 1;           // accumulator buffer and how often it was used before
+                mbar_wait(&tmem_empty_bar[acc], (use & 1) ^ 1);     // epilogue has drained it
                 tc_fence_after();
-                const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
-                const uint32_t b_addr = a_addr + L::kABytes;
-                const uint64_t da = make_smem_desc(a_addr, 16, 1024);
-                const uint64_t db = make_smem_desc(b_addr, 16, 1024);
+                const uint32_t tm = tmem_base + acc * BN;
+                for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1;
+                    mbar_wait(&full_bar[s], ph);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+                    const uint32_t b_addr = a_addr + L::kABytes;
+                    const uint64_t da = make_smem_desc(a_addr, 16, 1024);
+                    const uint64_t db = make_smem_desc(b_addr, 16, 1024);
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k)      // +32 bytes (= 2 in the >>4 address field) per K=16 slice
-                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-                umma_commit(&empty_bar[s]);
+                    for (int k = 0; k < BK / 16; ++k)      // +32 bytes (= 2 in the >>4 address field) per K=16 slice
+                        umma_bf16(tm, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&tmem_full_bar[acc]);
             }
-            umma_commit(tmem_full_bar);
         }
     } else {
         // ---------------- epilogue warps
-        mbar_wait(tmem_full_bar, 0);
-        tc_fence_after();
         const int q = warp & 3;
-        const int row = m_tile * BM + q * 32 + lane;
-        const bool row_ok = row < p.M;
+        uint32_t t = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            const int m_tile = tile % tiles_m, n_tile = tile / tiles_m;
+            const uint32_t acc = t & 1, use = t >> 1;
+            mbar_wait(&tmem_full_bar[acc], use & 1);
+            tc_fence_after();
+            const uint32_t tm = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+            const int row = m_tile * BM + q * 32 + lane;
+            const bool row_ok = row < p.M;
+            if (p.out && t > 0) {
+                // the staging tile is still being read by the previous tile's TMA store
+                if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
-            tmem_ld_wait();
-            const int col0 = n_tile * BN + c * 32;
-            float v[32];
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(tm + c * 32, r);
+                tmem_ld_wait();
+                if (c == BN / 32 - 1) {                  // whole accumulator is in registers: hand it back to the MMA warp
+                    tc_fence_before();
+                    mbar_arrive(&tmem_empty_bar[acc]);
+                }
+                const int col0 = n_tile * BN + c * 32;
+                float v[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-            if (p.bias) {
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                if (p.bias) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
-            }
-            if (p.act != ACT_NONE) {
+                    for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
+                }
+                if (p.act != ACT_NONE) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
-            }
-            if (p.sums) {
-                // per-column Σ and Σ² over the 32 rows of this warp: butterfly transpose-reduce —
-                // after 5 exchange steps lane j holds the total of column j.
-                float s1[32], s2[32];
+                    for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
+                }
+                if (p.sums) {
+                    // per-column Σ and Σ² over the 32 rows of this warp: butterfly transpose-reduce —
+                    // after 5 exchange steps lane j holds the total of column j.
+                    float s1[32], s2[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) { const float t = row_ok ? v[j] : 0.f; s1[j] = t; s2[j] = t * t; }
+                    for (int j = 0; j < 32; ++j) { const float tv = row_ok ? v[j] : 0.f; s1[j] = tv; s2[j] = tv * tv; }
 #pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) {
-                    const bool upper = (lane & off) != 0;
+                    for (int off = 16; off >= 1; off >>= 1) {
+                        const bool upper = (lane & off) != 0;
 #pragma unroll
-                    for (int j = 0; j < off; ++j) {
-                        // keep half of the columns, hand the other half to the partner lane
-                        const float send1 = upper ? s1[j] : s1[j + off];
-                        const float send2 = upper ? s2[j] : s2[j + off];
-                        const float recv1 = __shfl_xor_sync(0xffffffffu, send1, off);
-                        const float recv2 = __shfl_xor_sync(0xffffffffu, send2, off);
-                        s1[j] = (upper ? s1[j + off] : s1[j]) + recv1;
-                        s2[j] = (upper ? s2[j + off] : s2[j]) + recv2;
+                        for (int j = 0; j < off; ++j) {
+                            const float send1 = upper ? s1[j] : s1[j + off];
+                            const float send2 = upper ? s2[j] : s2[j + off];
+                            const float recv1 = __shfl_xor_sync(0xffffffffu, send1, off);
+                            const float recv2 = __shfl_xor_sync(0xffffffffu, send2, off);
+                            s1[j] = (upper ? s1[j + off] : s1[j]) + recv1;
+                            s2[j] = (upper ? s2[j + off] : s2[j]) + recv2;
+                        }
+                    }
+                    atomicAdd(p.sums + col0 + lane, s1[0]);
+                    atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
+                }
+                if (p.out) {
+                    // bf16 tile → shared memory in the 128B-swizzled layout of the output tensor map
+                    uint8_t* atom = sC + (c >> 1) * 16384;
+                    const int r_in = q * 32 + lane;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        const int col = (c & 1) * 32 + j;
+                        const uint32_t off = (uint32_t)(r_in * 128 + ((((col >> 3) ^ (r_in & 7)) << 4)));
+                        *reinterpret_cast<uint4*>(atom + off) = pack8(v + j).u;
                     }
                 }
-                // lane L now owns column bit-reversed?  No: at each step `upper` lanes keep the upper half
-                // of the remaining columns, so lane L ends with column L.
-                atomicAdd(p.sums + col0 + lane, s1[0]);
-                atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
-            }
-            if (p.out) {
-                // bf16 tile → shared memory in the 128B-swizzled layout of the output tensor map (the operand
-                // ring is free: every MMA that read it has completed), stored below by TMA in full lines
-                uint8_t* atom = smem + (c >> 1) * 16384;
-                const int r_in = q * 32 + lane;
-#pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    const int col = (c & 1) * 32 + j;
-                    const uint32_t off = (uint32_t)(r_in * 128 + ((((col >> 3) ^ (r_in & 7)) << 4)));
-                    *reinterpret_cast<uint4*>(atom + off) = pack8(v + j).u;
-                }
-            }
-            if (row_ok) {
-                if (p.out_f32) {
+                if (row_ok && p.out_f32) {
                     float* o = p.out_f32 + (size_t)row * p.N + col0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 }
             }
-        }
-        if (p.out) {
-            fence_proxy_async();
-            asm volatile("bar.sync 1, 128;" ::: "memory");          // the 4 epilogue warps
-            if (threadIdx.x == 64) {
+            if (p.out) {
+                fence_proxy_async();
+                asm volatile("bar.sync 1, 128;" ::: "memory");          // the 4 epilogue warps
+                if (threadIdx.x == 64) {
 #pragma unroll
-                for (int a = 0; a < BN / 64; ++a)
-                    tma_store_2d(&tmC, smem + a * 16384, n_tile * BN + a * 64, m_tile * BM);
-                tma_store_commit_and_wait_read();
+                    for (int a = 0; a < BN / 64; ++a)
+                        tma_store_2d(&tmC, sC + a * 16384, n_tile * BN + a * 64, m_tile * BM);
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
             }
         }
+        if (p.out && threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc<BN>(tmem_base);
+    if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
 // ------------------------------------------------------------------ host side: tensor maps
@@ -259,12 +289,15 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, 
     CUtensorMap tmC;
     if (p.out) { if (!encode_2d(&tmC, p.out, p.N, p.M, 64, BM)) return -4; }
     else tmC = tmB;
-    constexpr int kStages = (BN == 128) ? 3 : 4;      // ~96 KB of tiles → two CTAs per SM overlap prologue/epilogue
+    constexpr int kStages = (BN == 128) ? 5 : 6;      // one persistent CTA per SM: deep operand ring
     using L = SmemLayout<BN, kStages>;
     auto kern = gemm_nt_kernel<BN, kStages, kConv>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return (int)e;
-    dim3 grid((p.M + BM - 1) / BM, p.N / BN);
+    const int num_tiles = ((p.M + BM - 1) / BM) * (p.N / BN);
+    static int num_sms = 0;
+    if (!num_sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
+    const int grid = num_tiles < num_sms ? num_tiles : num_sms;
     kern<<<grid, kThreads, L::kTotal, st>>>(tmA, tmB, tmC, p);
     FDT_CHECK_LAUNCH();
     return 0;
