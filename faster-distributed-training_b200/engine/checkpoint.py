@@ -86,7 +86,16 @@ def load_optimizer_sidecar(name: str, optimizer, scheduler=None, directory: str 
     if not os.path.isfile(path):
         return False
     side = torch.load(path, map_location="cpu", weights_only=False)
-    optimizer.load_state_dict(side["optimizer"])
+    try:
+        optimizer.load_state_dict(side["optimizer"])
+    except (KeyError, ValueError, AssertionError) as e:
+        # the sidecar was written by a different optimizer (e.g. NGD vs MADGRAD): weights resume, state restarts
+        print(f"==> optimizer sidecar {path} not compatible with {type(optimizer).__name__} ({type(e).__name__}); "
+              f"starting with fresh optimizer state")
+        return False
     if scheduler is not None and side.get("scheduler") is not None:
-        scheduler.load_state_dict(side["scheduler"])
+        try:
+            scheduler.load_state_dict(side["scheduler"])
+        except Exception:
+            pass
     return True

@@ -87,7 +87,10 @@ class Trainer:
         eng.reduce_gradients()
         if self.scaler is not None:
             self.scaler.unscale_(self._local_grad())
+            skipped_before = self.skipped.clone()
         self._clip()
+        if self.scaler is not None:
+            self.scaler.update(self.skipped - skipped_before)     # device-side found-inf → scale back-off / growth
         self.optimizer.step()
         if hasattr(eng, "post_step"):
             eng.post_step()

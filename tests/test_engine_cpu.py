@@ -128,3 +128,30 @@ def test_cli_resnet_cpu_smoke(tmp_path):
                         "--no_plots", "--ckpt_dir", str(tmp_path)], capture_output=True, text=True, timeout=600, cwd=str(ROOT))
     assert r.returncode == 0, r.stderr[-2000:]
     assert (tmp_path / "resnet_ckpt.pth").exists() or "test acc" in r.stdout
+
+
+def test_fp16_loss_scaler_backs_off_and_grows():
+    from fdt.engine.amp import DynamicLossScaler
+    sc = DynamicLossScaler("cpu", init_scale=1024.0, growth_interval=3)
+    sc.update(torch.tensor(1.0))
+    assert sc.get_scale() == 512.0
+    for _ in range(3):
+        sc.update(torch.tensor(0.0))
+    assert sc.get_scale() == 1024.0
+    g = torch.ones(4) * 512.0
+    sc2 = DynamicLossScaler("cpu", init_scale=512.0)
+    sc2.unscale_(g)
+    assert torch.allclose(g, torch.ones(4))
+
+
+def test_resume_with_other_optimizer_skips_sidecar(tmp_path):
+    from fdt.engine import checkpoint as ck
+    from fdt.models.resnet import resnet18
+    from fdt.optim import MADGRAD, NGD
+    m = resnet18(10)
+    opt = NGD(m.parameters(), lr=0.1, momentum=0.9)
+    for p in m.parameters():
+        p.grad = torch.zeros_like(p)
+    ck.save_checkpoint("resnet", m, 50.0, 1, 0, str(tmp_path), opt, None)
+    assert ck.load_optimizer_sidecar("resnet", MADGRAD(m.parameters(), lr=1e-3), None, str(tmp_path)) is False
+    assert ck.load_optimizer_sidecar("resnet", NGD(m.parameters(), lr=0.1, momentum=0.9), None, str(tmp_path)) is True
