@@ -609,6 +609,8 @@ class NGD(Optimizer):
             if entry.get("flat_momentum") is not None:
                 dev = group["params"][0].device
                 self._lr_tensors[("mom", gi)] = entry["flat_momentum"].to(dev)
+            if not entry["shape_groups"]:
+                continue                       # saved before the first step: nothing to restore
             # shape groups need gradients to exist to be discovered; build them from params
             for p in group["params"]:
                 if p.grad is None:
