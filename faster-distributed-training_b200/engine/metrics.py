@@ -22,10 +22,12 @@ class DeviceMetrics:
     def __init__(self, device):
         self.acc = torch.zeros(3, dtype=torch.float32, device=device)
         self.steps = 0
+        self.ranks = 1          # how many ranks' loss sums are folded into acc[0] (after reduce)
 
     def reset(self):
         self.acc.zero_()
         self.steps = 0
+        self.ranks = 1
 
     @torch.no_grad()
     def update(self, loss: torch.Tensor, correct: torch.Tensor, batch: int):
@@ -36,12 +38,13 @@ class DeviceMetrics:
 
     def reduce(self, comm) -> "DeviceMetrics":
         comm.all_reduce_sum_(self.acc)
+        self.ranks = comm.world
         return self
 
     def read(self):
         """One host sync: returns (mean loss per step, accuracy %, correct, total)."""
         loss_sum, correct, total = self.acc.tolist()
-        return loss_sum / max(self.steps, 1), 100.0 * correct / max(total, 1.0), correct, total
+        return loss_sum / max(self.steps * self.ranks, 1), 100.0 * correct / max(total, 1.0), correct, total
 
 
 class StepTimer:
