@@ -84,6 +84,9 @@ class Trainer:
             self.scaler.scale(loss).backward()
         else:
             loss.backward()
+        if self.device.type == "cuda":
+            from ..ops import cuda_ops
+            cuda_ops.join_side_streams()              # side-stream weight gradients have landed
         eng.reduce_gradients()
         if self.scaler is not None:
             self.scaler.unscale_(self._local_grad())

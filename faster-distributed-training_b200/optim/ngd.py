@@ -489,6 +489,17 @@ class NGD(Optimizer):
                 d_p = precondition(fb, Xm.reshape(n, N, D), False, pending).reshape(mid).movedim(-1, pa + 1)
         return d_p
 
+    def _side_streams(self, sgs: List[_ShapeGroup]):
+        import os
+        k = int(os.environ.get("FDT_NGD_STREAMS", "16"))
+        if k <= 1 or not sgs or not sgs[0].params[0].is_cuda:
+            return None
+        key = ("streams", sgs[0].params[0].device)
+        st = self._lr_tensors.get(key)
+        if st is None:
+            st = self._lr_tensors[key] = [torch.cuda.Stream(sgs[0].params[0].device) for _ in range(k)]
+        return st
+
     def _flat_span(self, gi: int, sgs: List[_ShapeGroup]):
         """(flat, lo, hi) when this param group's flat-backed shape groups share one buffer."""
         key = ("span", gi)
@@ -525,8 +536,25 @@ class NGD(Optimizer):
                 gflat, pflat = flat.grad_flat[lo:hi], flat.param_flat[lo:hi]
                 if wd != 0:
                     gflat.add_(pflat, alpha=wd)
-            for sg in sgs:
+            # Shape groups are independent of each other (each is a chain of small batched kernels that
+            # cannot fill 148 SMs), so on CUDA they are spread over a few side streams: forked from and
+            # joined back into the current stream, which also works inside CUDA-graph capture.
+            streams = self._side_streams(sgs)
+            if streams:
+                main = torch.cuda.current_stream()
+                fork = torch.cuda.Event()
+                fork.record(main)
+            for si, sg in enumerate(sgs):
                 fused = span is not None and sg.flat_owner is not None
+                if streams and fused and group["ngd"]:
+                    st = streams[si % len(streams)]
+                    st.wait_event(fork)
+                    with torch.cuda.stream(st):
+                        G = sg.grads()
+                        d_p = self._precondition_group(sg, group, G, pending)
+                        if d_p is not G:
+                            G.copy_(d_p)
+                    continue
                 G = sg.grads()
                 P = sg.values()
                 if wd != 0 and not fused:
@@ -548,6 +576,11 @@ class NGD(Optimizer):
                 else:
                     P.add_(d_p, alpha=-lr)
                 sg.write_back(P)
+            if streams:
+                for st in streams:                         # join
+                    ev = torch.cuda.Event()
+                    ev.record(st)
+                    torch.cuda.current_stream().wait_event(ev)
             if span is not None:
                 self._fused_update(gi, group, gflat, pflat)
         flush_refreshes(pending)
