@@ -53,9 +53,40 @@ chan_reduce2_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __
 #pragma unroll
         for (int i = 0; i < 8; ++i) { s1[i] += fa[i]; s2[i] += fa[i] * (kSame ? fa[i] : fb[i]); }
     };
+    // four rows in flight per thread (issue the loads of all four before the dependent math)
+    auto load = [&](int64_t r, bf16x8& va, bf16x8& vb, bf16x8& vo) {
+        const int64_t off = r * C + c0;
+        va = ld8(a + off);
+        if (!kSame) vb = ld8(b + off);
+        if (kMask) vo = ld8(out_act + off);
+    };
+    auto consume = [&](int64_t r, const bf16x8& va, const bf16x8& vb, const bf16x8& vo) {
+        float fa[8], fb[8];
+        unpack8(va, fa);
+        if (!kSame) unpack8(vb, fb);
+        if (kMask) {
+            float fo[8];
+            unpack8(vo, fo);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) fa[i] *= act_bwd_from_out(fo[i], act);
+            if (g_store) {
+                bf16x8 pk = pack8(fa);
+                st8(g_store + r * C + c0, pk);
+                unpack8(pk, fa);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s1[i] += fa[i]; s2[i] += fa[i] * (kSame ? fa[i] : fb[i]); }
+    };
     int64_t r = r0 + rl;
-    for (; r + kLanes < r1; r += 2 * kLanes) { body(r); body(r + kLanes); }
-    if (r < r1) body(r);
+    for (; r + 3 * kLanes < r1; r += 4 * kLanes) {
+        bf16x8 va[4], vb[4], vo[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) load(r + u * kLanes, va[u], vb[u], vo[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) consume(r + u * kLanes, va[u], vb[u], vo[u]);
+    }
+    for (; r < r1; r += kLanes) body(r);
 
     // threads of one warp that share a channel column: lane = k·kTPR + cv
 #pragma unroll
@@ -136,6 +167,59 @@ chan_affine_act_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16
     }
 }
 
+// Fast path (C/8 divides 256, i.e. every power-of-two channel count up to 2048): with a grid stride that is a
+// multiple of C/8 vectors a thread always meets the SAME 8 channels, so its 24 coefficients live in registers
+// and the loop body is nothing but 128-bit loads, FMAs and 128-bit stores (no shared memory, no index division).
+template <bool kX2, bool kRes, int kAct>
+__global__ void __launch_bounds__(kThreads)
+chan_affine_act_fast_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
+                            const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
+                            const float* __restrict__ coef, int64_t total_vecs, int C) {
+    const int vecC = C >> 3;
+    const int c = (threadIdx.x % vecC) * 8;          // blockIdx.x * 1024 and j * 256 are multiples of vecC
+    float A[8], B[8], Cc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { A[i] = coef[c + i]; B[i] = kX2 ? coef[C + c + i] : 0.f; Cc[i] = coef[2 * C + c + i]; }
+    const int64_t stride = (int64_t)gridDim.x * kThreads * 4;
+    for (int64_t base = (int64_t)blockIdx.x * kThreads * 4 + threadIdx.x; base < total_vecs; base += stride) {
+        bf16x8 v1[4], v2[4], vr[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t v = base + (int64_t)j * kThreads;
+            if (v < total_vecs) {
+                v1[j] = ld8(x1 + v * 8);
+                if (kX2) v2[j] = ld8(x2 + v * 8);
+                if (kRes) vr[j] = ld8(res + v * 8);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t v = base + (int64_t)j * kThreads;
+            if (v < total_vecs) {
+                float f1[8], o[8];
+                unpack8(v1[j], f1);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaf(A[i], f1[i], Cc[i]);
+                if (kX2) {
+                    float f2[8];
+                    unpack8(v2[j], f2);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = fmaf(B[i], f2[i], o[i]);
+                }
+                if (kRes) {
+                    float fr[8];
+                    unpack8(vr[j], fr);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] += fr[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = act_fwd(o[i], kAct);
+                st8(out + v * 8, pack8(o));
+            }
+        }
+    }
+}
+
 // form 0: reference FusedConvBN  (unbiased var, eps added to the std, no affine)      resnet.py:85-100
 // form 1: nn.BatchNorm2d training (biased var, eps inside sqrt, affine, running-stat update)
 // form 2: nn.BatchNorm2d eval     (running stats)
@@ -201,8 +285,8 @@ int launch_reduce2(const void* a, const void* b, const void* out_act, void* g_st
     const int ctiles = (C / 8) / kTPR;
     int64_t slabs = (148 * 4 + ctiles - 1) / ctiles;
     int64_t rpb = (P + slabs - 1) / slabs;
-    const int64_t unit = 2 * kLanes;
-    if (rpb < 2 * unit) rpb = 2 * unit;
+    const int64_t unit = 4 * kLanes;
+    if (rpb < unit) rpb = unit;
     rpb = (rpb + unit - 1) / unit * unit;
     dim3 grid((unsigned)((P + rpb - 1) / rpb), ctiles);
     auto A = (const __nv_bfloat16*)a; auto B = (const __nv_bfloat16*)b; auto O = (const __nv_bfloat16*)out_act;
@@ -243,6 +327,18 @@ FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res,
     const size_t smem = 3 * (size_t)C * sizeof(float);
     auto X1 = (const __nv_bfloat16*)x1; auto X2 = (const __nv_bfloat16*)x2; auto R = (const __nv_bfloat16*)res;
     auto O = (__nv_bfloat16*)out;
+    if (kThreads % (C / 8) == 0 && (act == ACT_NONE || act == ACT_RELU || act == ACT_CELU)) {
+#define FDT_FAST(X2F, RF, ACTV) chan_affine_act_fast_kernel<X2F, RF, ACTV><<<(int)blocks, kThreads, 0, st>>>(X1, X2, R, O, coef, total, C)
+#define FDT_FAST_ACT(X2F, RF) do { if (act == ACT_RELU) FDT_FAST(X2F, RF, ACT_RELU); else if (act == ACT_CELU) FDT_FAST(X2F, RF, ACT_CELU); else FDT_FAST(X2F, RF, ACT_NONE); } while (0)
+        if (x2 && res) FDT_FAST_ACT(true, true);
+        else if (x2) FDT_FAST_ACT(true, false);
+        else if (res) FDT_FAST_ACT(false, true);
+        else FDT_FAST_ACT(false, false);
+#undef FDT_FAST_ACT
+#undef FDT_FAST
+        FDT_CHECK_LAUNCH();
+        return 0;
+    }
     if (x2 && res) chan_affine_act_kernel<true, true><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
     else if (x2) chan_affine_act_kernel<true, false><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
     else if (res) chan_affine_act_kernel<false, true><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);

@@ -430,6 +430,8 @@ class NGD(Optimizer):
         """'warm' (first call: factors are created and warm-started), 'update' (Fisher refresh)
         or 'plain'.  The kind decides which kernels a step launches, i.e. which captured graph
         can replay it."""
+        if not any(g["ngd"] for g in self.param_groups):
+            return "plain" if self._groups else "warm"      # plain SGD: one eager step builds the groups
         fbs = list(self._factor_batches())
         if not fbs or any(fb.t == 0 for fb in fbs):
             return "warm"
@@ -540,6 +542,7 @@ class NGD(Optimizer):
             # cannot fill 148 SMs), so on CUDA they are spread over a few side streams: forked from and
             # joined back into the current stream, which also works inside CUDA-graph capture.
             streams = self._side_streams(sgs)
+            used = []
             if streams:
                 main = torch.cuda.current_stream()
                 fork = torch.cuda.Event()
@@ -548,7 +551,9 @@ class NGD(Optimizer):
                 fused = span is not None and sg.flat_owner is not None
                 if streams and fused and group["ngd"]:
                     st = streams[si % len(streams)]
-                    st.wait_event(fork)
+                    if st not in used:
+                        st.wait_event(fork)                # fork (once per stream and step)
+                        used.append(st)
                     with torch.cuda.stream(st):
                         G = sg.grads()
                         d_p = self._precondition_group(sg, group, G, pending)
@@ -576,8 +581,8 @@ class NGD(Optimizer):
                 else:
                     P.add_(d_p, alpha=-lr)
                 sg.write_back(P)
-            if streams:
-                for st in streams:                         # join
+            if used:
+                for st in used:                            # join only the streams that took work
                     ev = torch.cuda.Event()
                     ev.record(st)
                     torch.cuda.current_stream().wait_event(ev)
