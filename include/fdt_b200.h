@@ -90,6 +90,67 @@ int fdt_madgrad(float* p, const float* g, float* v, float* s, float* x0, int64_t
                 float decay, float eps, int mirror, cudaStream_t st);
 int fdt_cast_bf16(const float* x, void* y_bf16, int64_t n, cudaStream_t st);
 
+/* ---- tcgen05 / TMEM / TMA GEMM and convolution, csrc/gemm_sm100.cu, wgrad_sm100.cu, im2col.cu ------------
+ * ref: F.conv2d / F.linear / convolution_backward call sites (resnet.py:21-34,83,108,204,221; transformer.py:168-176,213-226) */
+
+/* out[M,N] (bf16 and/or fp32) = act(A[M,K] · B[N,K]^T + bias); sums (optional, [2N], zero on entry) += per-column sum, sum^2.
+ * K % 64 == 0, N % 64 == 0.  Persistent kernel, 128 x {64,128} tiles, double-buffered TMEM accumulator, TMA-store epilogue. */
+int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out_f32, const float* bias, float* sums,
+                int M, int N, int K, int act, cudaStream_t st);
+/* y[Nb,H,W,Cout] = conv(x[Nb,H,W,Cin], w[Cout,k,k,Cin]), stride 1, pad = k/2, NHWC bf16 (implicit GEMM: shifted 4-D TMA boxes). */
+int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int Nb, int H, int W, int Cin, int Cout,
+                 int ksize, int pad, cudaStream_t st);
+/* dw[Cout][k][k][Cin] (fp32) += alpha * dY^T (*) X  (MN-major operands, split-K).  multicast != 0: dw is an NVLS multicast
+ * address and the accumulation is an in-switch all-reduce (multimem.red) of finished tiles. */
+int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
+                   int pad, float alpha, int multicast, cudaStream_t st);
+/* dw[N][K] (fp32) += alpha * dY[M,N]^T · X[M,K] */
+int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, float alpha, int multicast,
+                     cudaStream_t st);
+/* explicit im2col / col2im (strided convs, the 3-channel stem): A[N*Ho*Wo, Kp] <-> x[N,H,W,C] */
+int fdt_im2col(const void* x, void* A, int N, int H, int W, int C, int k, int stride, int pad, int Ho, int Wo, int Kp,
+               cudaStream_t st);
+int fdt_col2im(const void* dA, void* dx, int N, int H, int W, int C, int k, int stride, int pad, int Ho, int Wo, int Kp,
+               cudaStream_t st);
+
+/* ---- fused attention, csrc/attention_sm100.cu (one CTA per batch*head; L <= 128, d_head = 64) -----------------
+ * ref: ScaledDotProduct / MultiheadAttention (transformer.py:180-227).  q,k,v,o,dO,dq,dk,dv: bf16 [B*L, H*64] with row stride ld. */
+int fdt_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const int64_t* key_mask,
+                 int B, int H, int L, int ld, float scale, float p_drop, const int64_t* seed_off, int mask_compat,
+                 cudaStream_t st);
+int fdt_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dO, const float* lse,
+                 void* dq, void* dk, void* dv, const int64_t* key_mask, int B, int H, int L, int ld, float scale,
+                 float p_drop, const int64_t* seed_off, int mask_compat, cudaStream_t st);
+
+/* ---- input / head kernels, csrc/input_head.cu ------------------------------------------------------------------
+ * ref: loader transforms + mixup_data(_meta) (resnet50_test.py:301-318,355-401); AdaptiveAvgPool2d + Linear (resnet.py:279-281) */
+int fdt_input_aug_mixup(const void* x_u8, const int64_t* perm, const float* lam, int lam_n, const int64_t* seed_off,
+                        void* out_bf16, int B, int H, int W, int pad, int train, const float* mean3, const float* std3,
+                        cudaStream_t st);
+int fdt_pool_fc_fwd(const void* x, const float* W, const float* bias, float* pooled, float* logits, int N, int HW,
+                    int C, int K, cudaStream_t st);
+int fdt_pool_fc_bwd(const float* dlogits, const float* W, const float* pooled, void* dx, float* dW, float* db,
+                    int N, int HW, int C, int K, cudaStream_t st);
+
+/* ---- NGD element-wise tails and opt-in tf32 tensor-core products, csrc/ngd_eig.cu, ngd_gemm_sm100.cu ----------
+ * ref: ngd_optimizer.py:151-168,195-218,322-324 */
+int fdt_ngd_sumsq2(const float* X, const float* Xh, float* sums, int n, int64_t M, cudaStream_t st);
+int fdt_ngd_rescale(const float* X, const float* Xh, const float* sums, float* out, int n, int64_t M, cudaStream_t st);
+int fdt_ngd_commit_multi(const void* descs, int count, int* flags, int max_elems, cudaStream_t st);
+int fdt_ngd_project(const float* Xrows, const float* W, const float* Wt, float* H, const float* Cin, float* Xhat,
+                    float* sums, int n, int N, int D, int R, int c_trans, cudaStream_t st);
+int fdt_ngd_stats_j(const float* Ht, const float* Xt, float* J, int n, int N, int D, int R, cudaStream_t st);
+
+/* ---- in-kernel NVLink collectives over a symmetric heap, csrc/comm.cu -------------------------------------------
+ * ref: DDP bucket all-reduce (resnet50_test.py:716), FSDP all-gather / reduce-scatter (transformer_test.py:387-392).
+ * ctx: host pointer to {float* buf[8]; uint32_t* sig[8]; float* scratch[8]; float* mc; int rank, world, pad0, pad1;} */
+int fdt_comm_all_reduce_mean(const void* ctx, int64_t n, int use_multicast, cudaStream_t st);
+int fdt_comm_reduce_scatter_mean(const void* ctx, int64_t lo, int64_t hi, int use_multicast, cudaStream_t st);
+int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16, int use_multicast, cudaStream_t st);
+int fdt_comm_barrier(const void* ctx, cudaStream_t st);
+int fdt_comm_take_scalar(float* slot, float* out, cudaStream_t st);
+int fdt_comm_mc_red_add(float* dst_mc, const float* src, int64_t n, float alpha, cudaStream_t st);
+
 #ifdef __cplusplus
 }
 #endif
