@@ -56,6 +56,17 @@ struct SmemLayout {
 // Persistent: gridDim.x CTAs (<= #SMs) walk the tile list (m fastest, so neighbouring CTAs share the weight
 // tile in L2).  The accumulator is double-buffered in tensor memory (2 x BN columns): while the epilogue warps
 // drain tile i (tcgen05.ld → bias/act/stats → swizzled smem → TMA store), the MMA warp already runs tile i+1.
+// Tile rasterisation: bands of 16 M-tiles, N-tiles inner → the ~148 tiles in flight cover a 16 x ~9 patch of the
+// output, so both operands are re-used out of L2 instead of streaming one of them from HBM for every tile.
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& m_tile, int& n_tile) {
+    constexpr int kBand = 16;
+    const int per_band = kBand * tiles_n;
+    const int b = tile / per_band, r = tile - b * per_band;
+    const int rows = min(kBand, tiles_m - b * kBand);
+    m_tile = b * kBand + r % rows;
+    n_tile = r / rows;
+}
+
 template <int BN, int kStages, bool kConv>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -92,7 +103,8 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             uint32_t it = 0;                                        // running k-block counter across tiles
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m_tile = tile % tiles_m, n_tile = tile / tiles_m;
+                int m_tile, n_tile;
+                tile_coords(tile, tiles_m, tiles_n, m_tile, n_tile);
                 int n0 = 0, h0 = 0;
                 if (kConv) {
                     if (p.bn == 1) { const int tpi = p.H / p.bh; n0 = m_tile / tpi; h0 = (m_tile % tpi) * p.bh; }
@@ -147,7 +159,8 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;
         uint32_t t = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-            const int m_tile = tile % tiles_m, n_tile = tile / tiles_m;
+            int m_tile, n_tile;
+            tile_coords(tile, tiles_m, tiles_n, m_tile, n_tile);
             const uint32_t acc = t & 1, use = t >> 1;
             mbar_wait(&tmem_full_bar[acc], use & 1);
             tc_fence_after();
