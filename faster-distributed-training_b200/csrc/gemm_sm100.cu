@@ -29,7 +29,7 @@ using namespace sm100;
 
 namespace {
 
-constexpr int BM = 128, BK = 64, kThreads = 192;
+constexpr int BM = 128, BK = 64, kThreads = 320;   // TMA warp + MMA warp + 2 epilogue warpgroups (one per TMEM accumulator)
 
 struct GemmParams {
     int M, N, num_kb;
@@ -47,8 +47,8 @@ struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kCOff = kStages * kStageBytes;           // bf16 output staging: BN/64 atoms of 16 KB
-    static constexpr int kCBytes = (BN / 64) * 16384;
+    static constexpr int kCOff = kStages * kStageBytes;           // bf16 output staging: BN/64 atoms of 16 KB, per warpgroup
+    static constexpr int kCBytes = 2 * (BN / 64) * 16384;
     static constexpr int kBarOff = kCOff + kCBytes;
     static constexpr int kTotal = kBarOff + (2 * kStages + 4) * 8 + 16 + 1024;   // + alignment slack
 };
@@ -74,7 +74,6 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     using L = SmemLayout<BN, kStages>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sC = smem + L::kCOff;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
     uint64_t* empty_bar = full_bar + kStages;
     uint64_t* tmem_full_bar = empty_bar + kStages;       // [2]
@@ -155,10 +154,15 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
     } else {
-        // ---------------- epilogue warps
+        // ---------------- epilogue: warpgroup wg (warps 2-5 / 6-9) drains accumulator buffer wg, i.e. every other tile
         const int q = warp & 3;
+        const int wg = (warp - 2) >> 2;
+        const int bar_id = 1 + wg;
+        const int leader = 64 + wg * 128;                         // first thread of the warpgroup issues the TMA stores
+        uint8_t* sC = smem + L::kCOff + wg * (L::kCBytes / 2);
         uint32_t t = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            if ((int)(t & 1) != wg) continue;
             int m_tile, n_tile;
             tile_coords(tile, tiles_m, tiles_n, m_tile, n_tile);
             const uint32_t acc = t & 1, use = t >> 1;
@@ -167,10 +171,10 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t tm = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
             const int row = m_tile * BM + q * 32 + lane;
             const bool row_ok = row < p.M;
-            if (p.out && t > 0) {
-                // the staging tile is still being read by the previous tile's TMA store
-                if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (p.out && t > 1) {
+                // this warpgroup's staging tile is still being read by its previous TMA store
+                if (threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             }
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
@@ -234,8 +238,8 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             if (p.out) {
                 fence_proxy_async();
-                asm volatile("bar.sync 1, 128;" ::: "memory");          // the 4 epilogue warps
-                if (threadIdx.x == 64) {
+                asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");          // the 4 warps of this warpgroup
+                if (threadIdx.x == leader) {
 #pragma unroll
                     for (int a = 0; a < BN / 64; ++a)
                         tma_store_2d(&tmC, sC + a * 16384, n_tile * BN + a * 64, m_tile * BM);
@@ -243,7 +247,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             }
         }
-        if (p.out && threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (p.out && threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -302,7 +306,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, 
     CUtensorMap tmC;
     if (p.out) { if (!encode_2d(&tmC, p.out, p.N, p.M, 64, BM)) return -4; }
     else tmC = tmB;
-    constexpr int kStages = (BN == 128) ? 5 : 6;      // one persistent CTA per SM: deep operand ring
+    constexpr int kStages = (BN == 128) ? 4 : 7;      // one persistent CTA per SM: operand ring + 2 staging tiles
     using L = SmemLayout<BN, kStages>;
     auto kern = gemm_nt_kernel<BN, kStages, kConv>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
@@ -316,6 +320,14 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, 
     return 0;
 }
 
+// 128-wide N tiles unless that leaves more than half of the SMs without a tile (deep, narrow problems such as the
+// 4x4-feature-map convolutions): then 64-wide tiles double the tile count.
+int pick_bn(int M, int N) {
+    if (N % 128) return 64;
+    const int tiles128 = ((M + BM - 1) / BM) * (N / 128);
+    return tiles128 <= 74 ? 64 : 128;
+}
+
 }  // namespace
 
 // out[M,N] (bf16 and/or fp32) = act(A[M,K] · B[N,K]ᵀ + bias).  K % 64 == 0, N % 64 == 0, 16-byte aligned rows.
@@ -324,7 +336,7 @@ FDT_API int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out
                         int M, int N, int K, int act, cudaStream_t st) {
     if (M <= 0 || N % 64 || K % 64 || K <= 0) return -1;
     CUtensorMap tmA, tmB;
-    const int BN = (N % 128 == 0) ? 128 : 64;
+    const int BN = pick_bn(M, N);
     if (!encode_2d(&tmA, A, K, M, BK, BM) || !encode_2d(&tmB, B, K, N, BK, BN)) return -4;
     GemmParams p{};
     p.M = M; p.N = N; p.num_kb = K / BK; p.out = (__nv_bfloat16*)out_bf16; p.out_f32 = out_f32; p.bias = bias;
@@ -342,7 +354,7 @@ FDT_API int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int
     else if (H % bh) return -1;
     const int M = Nb * H * W;
     CUtensorMap tmA, tmB;
-    const int BN = (Cout % 128 == 0) ? 128 : 64;
+    const int BN = pick_bn(M, Cout);
     const int K = ksize * ksize * Cin;
     if (!encode_nhwc(&tmA, x, Nb, H, W, Cin, W, bh, bn) || !encode_2d(&tmB, w, K, Cout, BK, BN)) return -4;
     GemmParams p{};
