@@ -99,7 +99,10 @@ def test_resnet50_odd_batches_train_and_eval(bs):
     with torch.no_grad():
         ref = model(x)
     first = {}
-    model.conv2_x[0].register_forward_hook(lambda m, i, o: first.setdefault(o.device.type, o.detach().float().cpu()))
+
+    def _keep(m, i, o):     # must return None: a hook's return value replaces the module output
+        first.setdefault(o.device.type, o.detach().float().cpu())
+    model.conv2_x[0].register_forward_hook(_keep)
     with torch.no_grad():
         model(x)
     eng = DataParallelEngine(model.cuda())
