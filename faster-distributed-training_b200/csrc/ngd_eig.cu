@@ -14,7 +14,9 @@ using namespace fdt;
 namespace {
 
 constexpr int kMaxR = 80;
-constexpr int kThreads = 256;
+constexpr int kThreads = 1024;                               // one CTA per factor and ~100 long (R = 80) problems on 148 SMs:
+                                                              // the rotations of a step are spread over the whole SM
+constexpr int kMaxIt = (kMaxR / 2 * kMaxR + kThreads - 1) / kThreads;   // (pair, index) slots per thread and step
 constexpr float kEpsilon = 1.0e-10f;   // ngd_optimizer.py:37
 constexpr float kDelta = 5.0e-4f;      // ngd_optimizer.py:38
 
@@ -56,7 +58,7 @@ ngd_eig_body(const float* __restrict__ Kg, const float* __restrict__ Lg, const f
     float* cs = dpr + kMaxR;                         // rotation (c, s) per pair [n2]
     float* lam = cs + 2 * kMaxR;                     // eigenvalues, then sqrt_c
     float* leftv = lam + kMaxR;
-    float* scratch = leftv + kMaxR;                  // [8]
+    float* scratch = leftv + kMaxR;                  // [kThreads / 32]
     __shared__ int order[kMaxR];
     __shared__ int pp[kMaxR / 2 + 1], qq[kMaxR / 2 + 1];
 
@@ -98,6 +100,14 @@ ngd_eig_body(const float* __restrict__ Kg, const float* __restrict__ Lg, const f
 
     // ---- parallel cyclic Jacobi
     const int half = n2 / 2;
+    // the (pair k, index i) slots a thread updates are the same in every step: no divisions in the hot loop
+    int kk[kMaxIt], ii[kMaxIt];
+#pragma unroll
+    for (int it = 0; it < kMaxIt; ++it) {
+        const int idx = tid + it * kThreads;
+        kk[it] = idx < half * n2 ? idx / n2 : -1;
+        ii[it] = idx % n2;
+    }
     for (int sweep = 0; sweep < max_sweeps; ++sweep) {
         float off = 0.f, dia = 0.f;
         for (int idx = tid; idx < R * R; idx += kThreads) {
@@ -128,8 +138,10 @@ ngd_eig_body(const float* __restrict__ Kg, const float* __restrict__ Lg, const f
             }
             __syncthreads();
             // columns of Z and V:  [col_p, col_q] <- [c·col_p − s·col_q,  s·col_p + c·col_q]
-            for (int idx = tid; idx < half * n2; idx += kThreads) {
-                const int k = idx / n2, i = idx % n2;
+#pragma unroll
+            for (int it = 0; it < kMaxIt; ++it) {
+                const int k = kk[it], i = ii[it];
+                if (k < 0) continue;
                 const int p = pp[k], q = qq[k];
                 const float c = cs[2 * k], s = cs[2 * k + 1];
                 const float zp = Z[i * ld + p], zq = Z[i * ld + q];
@@ -141,8 +153,10 @@ ngd_eig_body(const float* __restrict__ Kg, const float* __restrict__ Lg, const f
             }
             __syncthreads();
             // rows of Z
-            for (int idx = tid; idx < half * n2; idx += kThreads) {
-                const int k = idx / n2, j = idx % n2;
+#pragma unroll
+            for (int it = 0; it < kMaxIt; ++it) {
+                const int k = kk[it], j = ii[it];
+                if (k < 0) continue;
                 const int p = pp[k], q = qq[k];
                 const float c = cs[2 * k], s = cs[2 * k + 1];
                 const float zp = Z[p * ld + j], zq = Z[q * ld + j];
@@ -229,7 +243,7 @@ FDT_API int fdt_ngd_eig_update(const float* K, const float* L, const float* d, c
     if (R < 1 || R > kMaxR || R >= D) return -1;
     const int n2 = (R + 1) & ~1;
     const int ld = R + 1 + ((R & 1) ? 1 : 0);
-    const size_t smem = sizeof(float) * (2 * (size_t)n2 * ld + 6 * kMaxR + 8);
+    const size_t smem = sizeof(float) * (2 * (size_t)n2 * ld + 6 * kMaxR + 32);
     cudaError_t e = cudaFuncSetAttribute(ngd_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     if (e != cudaSuccess) return (int)e;
     ngd_eig_kernel<<<n, kThreads, smem, st>>>(K, L, d, rho, trXXt, A, w_coeff, d1, rho1, R, D, N, alpha, eta, max_sweeps);
@@ -240,7 +254,7 @@ FDT_API int fdt_ngd_eig_update(const float* K, const float* L, const float* d, c
 // Heterogeneous batch: `count` descriptors (device memory, 96 bytes each, see NgdEigDesc), one CTA each.
 FDT_API int fdt_ngd_eig_update_multi(const void* descs, int count, int max_sweeps, cudaStream_t st) {
     if (count <= 0) return 0;
-    const size_t smem = sizeof(float) * (2 * (size_t)kMaxR * (kMaxR + 1) + 6 * kMaxR + 8);
+    const size_t smem = sizeof(float) * (2 * (size_t)kMaxR * (kMaxR + 1) + 6 * kMaxR + 32);
     cudaError_t e = cudaFuncSetAttribute(ngd_eig_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     if (e != cudaSuccess) return (int)e;
     ngd_eig_multi_kernel<<<count, kThreads, smem, st>>>((const NgdEigDesc*)descs, max_sweeps);
@@ -325,7 +339,93 @@ ngd_copy_kernel(const NgdCommitDesc* __restrict__ descs, const int* __restrict__
     }
 }
 
+
+// ---- W_{t+1} = A (J + w_coeff ∘ W_t) for every factor in one launch, fused with the finiteness check of the
+// hand-over (ngd_optimizer.py:311-324: torch.mm + add per factor).  grid = (column chunks, factors).
+struct NgdFinishDesc {          // NgdCommitDesc + the operands of W1; mirrored in fdt/ops/cuda_ops.py
+    float *W1;
+    const float *d1, *rho1;
+    float *W, *d, *rho;
+    const float *A, *J, *wc;
+    int R, D;
+};
+static_assert(sizeof(NgdFinishDesc) == 80, "descriptor layout is mirrored in python");
+constexpr int kW1Cols = 64;
+
+__global__ void __launch_bounds__(256)
+ngd_w1_check_kernel(const NgdFinishDesc* __restrict__ descs, int* __restrict__ bad_flags) {
+    const NgdFinishDesc c = descs[blockIdx.y];
+    const int R = c.R, D = c.D;
+    extern __shared__ float sm[];
+    float* As = sm;                         // [R][R + 1]
+    float* Bs = sm + kMaxR * (kMaxR + 1);   // [R][kW1Cols]
+    int bad = 0;
+    bool loaded = false;
+    for (int c0 = blockIdx.x * kW1Cols; c0 < D; c0 += gridDim.x * kW1Cols) {
+        if (!loaded) {
+            for (int i = threadIdx.x; i < R * R; i += blockDim.x) As[(i / R) * (R + 1) + i % R] = c.A[i];
+            loaded = true;
+        }
+        const int nc = min(kW1Cols, D - c0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < R * kW1Cols; i += blockDim.x) {
+            const int r = i / kW1Cols, cc = i % kW1Cols;
+            Bs[i] = cc < nc ? fmaf(c.wc[r], c.W[(int64_t)r * D + c0 + cc], c.J[(int64_t)r * D + c0 + cc]) : 0.f;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < R * kW1Cols; i += blockDim.x) {
+            const int r = i / kW1Cols, cc = i % kW1Cols;
+            if (cc >= nc) continue;
+            float acc = 0.f;
+            for (int j = 0; j < R; ++j) acc = fmaf(As[r * (R + 1) + j], Bs[j * kW1Cols + cc], acc);
+            c.W1[(int64_t)r * D + c0 + cc] = acc;
+            bad |= !isfinite(acc);
+        }
+    }
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < R; i += blockDim.x) bad |= !isfinite(c.d1[i]);
+        if (threadIdx.x == 0) bad |= !isfinite(c.rho1[0]);
+    }
+    bad = __syncthreads_or(bad);
+    if (bad && threadIdx.x == 0) atomicOr(bad_flags + blockIdx.y, 1);
+}
+__global__ void __launch_bounds__(256)
+ngd_finish_copy_kernel(const NgdFinishDesc* __restrict__ descs, const int* __restrict__ bad_flags) {
+    if (bad_flags[blockIdx.y]) return;
+    const NgdFinishDesc c = descs[blockIdx.y];
+    const int nW = c.R * c.D;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nW; i += gridDim.x * blockDim.x) c.W[i] = c.W1[i];
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < c.R; i += blockDim.x) c.d[i] = c.d1[i];
+        if (threadIdx.x == 0) c.rho[0] = c.rho1[0];
+    }
+}
+
 }  // namespace
+
+// W1 = A (J + wc ∘ W) for `count` factors (80-byte NgdFinishDesc each, device memory), then the guarded hand-over
+// W←W1, d←d1, rho←rho1.  flags: `count` ints of caller scratch; max_D / max_elems size the grids.
+FDT_API int fdt_ngd_finish_multi(const void* descs, int count, int* flags, int max_D, int max_elems, cudaStream_t st) {
+    if (count <= 0) return 0;
+    static bool attr = false;
+    const size_t smem = sizeof(float) * ((size_t)kMaxR * (kMaxR + 1) + (size_t)kMaxR * kW1Cols);
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(ngd_w1_check_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    int cchunks = (max_D + kW1Cols - 1) / kW1Cols;
+    if (cchunks > 32) cchunks = 32;
+    if (cchunks < 1) cchunks = 1;
+    int chunks = (max_elems + 256 * 8 - 1) / (256 * 8);
+    if (chunks < 1) chunks = 1;
+    if (chunks > 64) chunks = 64;
+    cudaMemsetAsync(flags, 0, sizeof(int) * count, st);
+    ngd_w1_check_kernel<<<dim3(cchunks, count), 256, smem, st>>>((const NgdFinishDesc*)descs, flags);
+    ngd_finish_copy_kernel<<<dim3(chunks, count), 256, 0, st>>>((const NgdFinishDesc*)descs, flags);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
 
 // sums: [2n] zero on entry.  X, Xh: [n, M] contiguous fp32.
 FDT_API int fdt_ngd_sumsq2(const float* X, const float* Xh, float* sums, int n, int64_t M, cudaStream_t st) {

@@ -580,6 +580,22 @@ def ngd_norms_rescale(X: torch.Tensor, Xhat: torch.Tensor):
     return sums[:n], Xhat
 
 
+def ngd_small_axis_ok(D: int, R: int) -> bool:
+    return 2 <= D <= 12 and R == (D + 1) // 2
+
+
+def ngd_small_axis(X: torch.Tensor, W: torch.Tensor, A: int, D: int, B: int, J: Optional[torch.Tensor]):
+    """Precondition a short axis of the physical gradient view ``X`` = [n, A, D, B] (csrc/ngd_axis.cu): projection,
+    deflation, norm restoration and (when ``J`` is given) the Fisher statistics J = Σ h xᵀ, without materialising
+    H or a transposed copy.  Returns (p0 [n], out [same shape as X])."""
+    n = X.shape[0]
+    Xhat = torch.empty_like(X)
+    sums = torch.empty(2 * n, dtype=torch.float32, device=X.device)
+    call("fdt_ngd_small_axis", X, W, Xhat, sums, J, n, i64(A), int(D), i64(B), int(W.shape[1]), launches=1)
+    call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(A * D * B))
+    return sums[:n], Xhat
+
+
 _commit_cache = {}
 
 
@@ -603,6 +619,33 @@ def ngd_commit_multi(pending):
         ent = (dev, len(rows), list(pending), flags, max(fb.R * fb.D for fb in pending))
         _commit_cache[key] = ent
     call("fdt_ngd_commit_multi", ent[0], ent[1], ent[3], ent[4], launches=3)
+
+
+_finish_cache = {}
+
+
+def ngd_finish_multi(pending):
+    """W1 = A (J + wc ∘ W) for every factor of every pending batch, then the guarded hand-over W←W1, d←d1,
+    rho←rho1: three launches for the whole model (csrc/ngd_eig.cu::fdt_ngd_finish_multi)."""
+    import struct
+    key = tuple(id(fb) for fb in pending)
+    ent = _finish_cache.get(key)
+    if ent is None:
+        rows = []
+        for fb in pending:
+            R, D = fb.R, fb.D
+            for f in range(fb.n):
+                rows.append(struct.pack(
+                    "<9Q2i", fb.W1.data_ptr() + f * R * D * 4, fb.d1.data_ptr() + f * R * 4, fb.rho1.data_ptr() + f * 4,
+                    fb.W.data_ptr() + f * R * D * 4, fb.d.data_ptr() + f * R * 4, fb.rho.data_ptr() + f * 4,
+                    fb.A.data_ptr() + f * R * R * 4, fb.J.data_ptr() + f * R * D * 4, fb.wc.data_ptr() + f * R * 4, R, D))
+        blob = b"".join(rows)
+        dev = torch.empty(len(blob), dtype=torch.uint8, device=pending[0].W.device)
+        dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
+        flags = torch.zeros(len(rows), dtype=torch.int32, device=dev.device)
+        ent = (dev, len(rows), list(pending), flags, max(fb.D for fb in pending), max(fb.R * fb.D for fb in pending))
+        _finish_cache[key] = ent
+    call("fdt_ngd_finish_multi", ent[0], ent[1], ent[3], ent[4], ent[5], launches=3)
 
 
 # Opt-in: measured on B200 the batched tf32 tcgen05 kernels are numerically fine (7e-4 relative, tf32) but do

@@ -145,21 +145,26 @@ def _split_factor(N: int, target: int = 2048) -> int:
     return S
 
 
+def _alloc_stats(fb: FactorBatch):
+    """Persistent work buffers of a factor batch's Fisher refresh (stable addresses for graph replay)."""
+    n, R, D = fb.n, fb.R, fb.D
+    kw = dict(dtype=fb.W.dtype, device=fb.W.device)
+    fb.J = torch.empty(n, R, D, **kw)
+    fb.K = torch.empty(n, R, R, **kw)
+    fb.L = torch.empty(n, R, R, **kw)
+    fb.A = torch.empty(n, R, R, **kw)
+    fb.W1 = torch.empty(n, R, D, **kw)
+    fb.wc = torch.empty(n, R, **kw)
+    fb.d1 = torch.empty(n, R, **kw)
+    fb.rho1 = torch.empty(n, **kw)
+    fb.tr = torch.empty(n, **kw)
+
+
 def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
     """J = HᵀX, L, K = JJᵀ into the factor batch's persistent work buffers."""
     W = fb.W
     if not hasattr(fb, "J"):
-        n, R, D = fb.n, fb.R, fb.D
-        kw = dict(dtype=W.dtype, device=W.device)
-        fb.J = torch.empty(n, R, D, **kw)
-        fb.K = torch.empty(n, R, R, **kw)
-        fb.L = torch.empty(n, R, R, **kw)
-        fb.A = torch.empty(n, R, R, **kw)
-        fb.W1 = torch.empty(n, R, D, **kw)
-        fb.wc = torch.empty(n, R, **kw)
-        fb.d1 = torch.empty(n, R, **kw)
-        fb.rho1 = torch.empty(n, **kw)
-        fb.tr = torch.empty(n, **kw)
+        _alloc_stats(fb)
     if getattr(fb, "_h_rows", False):
         # H is [n, N, R] for both layouts (tcgen05 path): J on the tensor cores, L / K are R x R
         from .. import ops
@@ -233,9 +238,7 @@ def flush_refreshes(pending: List[FactorBatch]):
         from .. import ops
         cu = ops._cu()
         cu.ngd_eig_update_multi(pending)
-        for fb in pending:                              # W1 = A (J + w_coeff ∘ W)
-            torch.bmm(fb.A, torch.addcmul(fb.J, fb.wc.unsqueeze(2), fb.W), out=fb.W1)
-        cu.ngd_commit_multi(pending)                    # guarded W←W1, d←d1, rho←rho1: one launch for all factors
+        cu.ngd_finish_multi(pending)      # W1 = A (J + w_coeff ∘ W), then the guarded W←W1, d←d1, rho←rho1
     else:
         for fb in pending:
             A, w_coeff, d1, rho1 = fisher_update_torch(fb, fb.J, fb.K, fb.L, fb.tr)
@@ -317,6 +320,46 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
     scale = torch.sqrt(p0 / (p1 + 1.0e-30))
     out = Xhat * scale[:, None, None]
     return torch.where(torch.isnan(p1)[:, None, None], Xm, out)
+
+
+def _small_axis_native(fb: FactorBatch, d_p: torch.Tensor) -> bool:
+    if not (d_p.is_cuda and d_p.dtype == torch.float32):
+        return False
+    from .. import ops
+    return ops.use_native(d_p) and ops._cu().ngd_small_axis_ok(fb.D, fb.R)
+
+
+def precondition_small_axis(fb: FactorBatch, d_p: torch.Tensor, pa: int, pending: Optional[List[FactorBatch]]) -> torch.Tensor:
+    """:func:`precondition` for a short axis (D <= 12) of the stacked physical tensor ``d_p`` = [n, *phys]: the axis
+    at physical position ``pa`` is preconditioned in place of the ``[n, N, D]`` matrix view, so no transposed copy
+    is made and H is never materialised (csrc/ngd_axis.cu).  Same math as ngd_optimizer.py:138-168,195-218; the
+    statistics use L = J Wᵀ (N > D always holds here, ngd_optimizer.py:205-210)."""
+    from .. import ops
+    cu = ops._cu()
+    n = d_p.shape[0]
+    phys = d_p.shape[1:]
+    A = int(math.prod(phys[:pa]))
+    B = int(math.prod(phys[pa + 1:]))
+    X = d_p.contiguous()
+    updating = fb.updating()
+    fb.t += 1
+    if updating and fb.N <= fb.D:      # cannot happen for a sensible tensor; keep the general path's semantics
+        fb.t -= 1
+        Xm = X.movedim(pa + 1, -1)
+        return precondition(fb, Xm.reshape(n, fb.N, fb.D), False, pending).reshape(Xm.shape).movedim(-1, pa + 1)
+    if updating and not hasattr(fb, "J"):
+        _alloc_stats(fb)
+    p0, out = cu.ngd_small_axis(X, fb.W, A, fb.D, B, fb.J if updating else None)
+    if updating:
+        torch.bmm(fb.J, fb.W.transpose(1, 2), out=fb.L)
+        torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+        fb.tr.copy_(p0)
+        if pending is None:
+            A_, w_coeff, d1, rho1 = _fisher_update(fb, fb.J, fb.K, fb.L, fb.tr)
+            _apply_refresh(fb, A_, w_coeff, d1, rho1)
+        else:
+            pending.append(fb)
+    return out
 
 
 class _ShapeGroup:
@@ -481,7 +524,10 @@ class NGD(Optimizer):
             if fb is None:
                 fb = sg.factors[axis] = FactorBatch(n, N, D, group["alpha"], group["rank"], group["update_period"],
                                                     group["eta"], d_p.dtype, d_p.device)
-            if pa == nd - 1:
+            if fb.t > 0 and _small_axis_native(fb, d_p):
+                # short axis (conv kernel axes, class axes): one bandwidth-bound pass over the tensor where it lies
+                d_p = precondition_small_axis(fb, d_p, pa, pending)
+            elif pa == nd - 1:
                 d_p = precondition(fb, d_p.reshape(n, N, D), False, pending).reshape(n, *phys_shape)
             elif pa == 0:
                 d_p = precondition(fb, d_p.reshape(n, D, N), True, pending).reshape(n, *phys_shape)

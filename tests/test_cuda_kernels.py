@@ -285,3 +285,51 @@ def test_ngd_tf32_tcgen05_gemms(n, N, D, R, left):
     J = torch.zeros(n, R, D, device=DEV)
     cu.ngd_stats_j(Href.contiguous(), Xin, J, left)
     _relnorm(J, torch.bmm(Href.transpose(1, 2), X), 3e-3, "J")
+
+
+@pytest.mark.parametrize("n,A,D,B", [(3, 64, 3, 192), (2, 5, 3, 7), (1, 1, 10, 2048), (4, 576, 3, 1), (2, 9, 4, 36), (1, 3, 12, 20)])
+@pytest.mark.parametrize("with_j", [False, True])
+def test_ngd_small_axis(n, A, D, B, with_j):
+    """Short-axis NGD pass on the [n, A, D, B] view vs the two-GEMM formulation on the [n, N, D] matrix."""
+    from fdt.ops import cuda_ops as cu
+    torch.manual_seed(0)
+    R = (D + 1) // 2
+    X = torch.randn(n, A, D, B, device=DEV)
+    W = torch.randn(n, R, D, device=DEV) * 0.3
+    J = torch.full((n, R, D), 7.0, device=DEV) if with_j else None
+    p0, out = cu.ngd_small_axis(X, W, A, D, B, J)
+    Xm = X.double().movedim(2, -1).reshape(n, A * B, D)
+    Wd = W.double()
+    H = Xm @ Wd.transpose(1, 2)
+    Xh = Xm - H @ Wd
+    p0r = (Xm * Xm).sum((1, 2))
+    p1r = (Xh * Xh).sum((1, 2))
+    ref = (Xh * torch.sqrt(p0r / p1r)[:, None, None]).reshape(n, A, B, D).movedim(-1, 2)
+    _close(p0, p0r, 1e-5, 1e-5, "p0")
+    _close(out, ref, 1e-4, 1e-5, "out")
+    if with_j:
+        _close(J, H.transpose(1, 2) @ Xm, 1e-4, 1e-3, "J")
+
+
+def test_ngd_small_axis_matches_general_path():
+    """One NGD trajectory of a conv-shaped tensor with the short-axis kernel on and off."""
+    from fdt import ops
+    from fdt.optim import NGD
+    from fdt.ops import cuda_ops as cu
+    outs = []
+    for enabled in (True, False):
+        torch.manual_seed(0)
+        p = torch.nn.Parameter(torch.randn(16, 8, 3, 3, device=DEV))
+        opt = NGD([p], lr=0.1, momentum=0.9)
+        saved = cu.ngd_small_axis_ok
+        if not enabled:
+            cu.ngd_small_axis_ok = lambda D, R: False
+        try:
+            g = torch.Generator(device=DEV).manual_seed(1)
+            for _ in range(14):
+                p.grad = torch.randn(p.shape, device=DEV, generator=g)
+                opt.step()
+        finally:
+            cu.ngd_small_axis_ok = saved
+        outs.append(p.detach().clone())
+    _relnorm(outs[0], outs[1], 2e-3, "small-axis vs general NGD trajectory")
