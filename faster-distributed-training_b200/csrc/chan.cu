@@ -384,6 +384,19 @@ FDT_API int fdt_bn_act_fwd(const void* y, const void* res, void* out, float* ctx
     return fdt_chan_affine_act(y, nullptr, res, out, coef, P, C, act, st);
 }
 
+// Same unit when the producer of `y` already accumulated the per-channel Σy, Σy² into scratch[0 .. 2C) (the conv
+// GEMM's epilogue does, csrc/gemm_sm100.cu): coefficients → normalise [+ residual] + activation, two launches and
+// one pass over y less than fdt_bn_act_fwd.  Not for form 2 (eval: no batch statistics).
+FDT_API int fdt_bn_act_fwd_presummed(const void* y, const void* res, void* out, float* ctx, float* scratch,
+                                     const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                     int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st) {
+    if (C % 8 || form == 2) return -1;
+    float* coef = scratch + 2 * (size_t)C;
+    int rc = fdt_bn_finalize_fwd(scratch, coef, ctx, gamma, beta, running_mean, running_var, C, (float)P, eps, momentum, form, st);
+    if (rc) return rc;
+    return fdt_chan_affine_act(y, nullptr, res, out, coef, P, C, act, st);
+}
+
 // ---------------------------------------------------------------------------------------------
 // fdt_bn_act_fwd_noalloc — the same fused normalisation forward as fdt_bn_act_fwd, for callers
 // that have no working memory to hand over and are not allowed to go and get some.

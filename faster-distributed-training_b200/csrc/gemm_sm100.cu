@@ -42,6 +42,10 @@ struct GemmParams {
     int H, W, bh, bn, pad, kw, cpb;   // cpb = Cin / 64 (k-blocks per tap)
 };
 
+// Column statistics (Σ, Σ² per output channel — the BatchNorm batch statistics of a conv output) are accumulated per
+// CTA in shared memory over all the tiles it owns and flushed with one global atomic per touched column at the end.
+constexpr int kSumCols = 2048;
+
 template <int BN, int kStages>
 struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
@@ -50,7 +54,8 @@ struct SmemLayout {
     static constexpr int kCOff = kStages * kStageBytes;           // bf16 output staging: BN/64 atoms of 16 KB, per warpgroup
     static constexpr int kCBytes = 2 * (BN / 64) * 16384;
     static constexpr int kBarOff = kCOff + kCBytes;
-    static constexpr int kTotal = kBarOff + (2 * kStages + 4) * 8 + 16 + 1024;   // + alignment slack
+    static constexpr int kSumOff = kBarOff + (((2 * kStages + 4) * 8 + 16 + 15) & ~15);   // per-CTA column statistics
+    static constexpr int kTotal = kSumOff + 2 * kSumCols * 4 + 1024;                     // + alignment slack
 };
 
 // Persistent: gridDim.x CTAs (<= #SMs) walk the tile list (m fastest, so neighbouring CTAs share the weight
@@ -93,6 +98,10 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
+    float* s_sums = reinterpret_cast<float*>(smem + L::kSumOff);
+    const bool smem_sums = p.sums != nullptr && p.N <= kSumCols;
+    if (smem_sums)
+        for (int i = threadIdx.x; i < 2 * p.N; i += kThreads) s_sums[i] = 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -216,8 +225,13 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             s2[j] = (upper ? s2[j + off] : s2[j]) + recv2;
                         }
                     }
-                    atomicAdd(p.sums + col0 + lane, s1[0]);
-                    atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
+                    if (smem_sums) {
+                        atomicAdd(s_sums + col0 + lane, s1[0]);
+                        atomicAdd(s_sums + p.N + col0 + lane, s2[0]);
+                    } else {
+                        atomicAdd(p.sums + col0 + lane, s1[0]);
+                        atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
+                    }
                 }
                 if (p.out) {
                     // bf16 tile → shared memory in the 128B-swizzled layout of the output tensor map
@@ -245,6 +259,13 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         tma_store_2d(&tmC, sC + a * 16384, n_tile * BN + a * 64, m_tile * BM);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
+            }
+        }
+        if (smem_sums) {
+            asm volatile("bar.sync 3, 256;" ::: "memory");          // both epilogue warpgroups are done accumulating
+            for (int i = threadIdx.x - 64; i < 2 * p.N; i += 256) {
+                const float v = s_sums[i];
+                if (v != 0.f) atomicAdd(p.sums + i, v);
             }
         }
         if (p.out && threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");

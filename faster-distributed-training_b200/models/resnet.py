@@ -165,6 +165,13 @@ class ResNet(nn.Module):
         self.conv5_x = self._make_layer(block, 512, num_block[3], 2)
         self.avg_pool = nn.AdaptiveAvgPool2d((1, 1))
         self.fc = nn.Linear(512 * block.expansion, num_classes)
+        # layout of the transposed filter the dX GEMM wants (FlatParameters.refresh_dgrad_shadow makes them all in
+        # one launch per step): 0 = tap-rotated [Cin][kh][kw][Cout] (implicit GEMM), 1 = [K, Cout] (col2im path)
+        for m in self.modules():
+            if isinstance(m, ConvBNStat):
+                m.conv_weight._fdt_dgrad_mode = 0
+            elif isinstance(m, nn.Conv2d):
+                m.weight._fdt_dgrad_mode = 0 if m.stride[0] == 1 and 2 * m.padding[0] == m.kernel_size[0] - 1 else 1
 
     def _make_layer(self, block, out_channels, num_blocks, stride):
         layers = []

@@ -181,6 +181,8 @@ class Transformer(nn.Module):
         for m in self.modules():
             if isinstance(m, nn.Linear) and m.in_features % 64 == 0 and m.out_features % 8 == 0:
                 m.weight._fdt_wgrad_fused = True      # gradient all-reduced inside the wgrad kernel (DDP)
+            if isinstance(m, nn.Linear) and m.in_features % 8 == 0 and m.out_features % 8 == 0:
+                m.weight._fdt_dgrad_mode = 0          # Wᵀ for the dX GEMM is produced once per step for all layers
         self.init_params()
 
     def init_params(self):

@@ -69,6 +69,12 @@ def _w16(p: torch.Tensor) -> torch.Tensor:
     return p.detach().to(BF16)
 
 
+def _wdgrad(p: Optional[torch.Tensor], mode: int) -> Optional[torch.Tensor]:
+    """Pre-transposed data-gradient operand of a flat-buffer parameter (FlatParameters.refresh_dgrad_shadow)."""
+    f = getattr(p, "_fdt_flat", None) if p is not None else None
+    return f[0].dgrad_shadow_of(p, mode) if f is not None else None
+
+
 def cast_bf16_(src: torch.Tensor, dst: torch.Tensor):
     call("fdt_cast_bf16", src, dst, i64(src.numel()))
 
@@ -110,15 +116,22 @@ def _next_seed_off(device) -> torch.Tensor:
 
 
 # ----------------------------------------------------------------------------- conv back ends
-def _conv_fwd(x, w16, stride, padding):
+# BatchNorm batch statistics from the conv GEMM's epilogue (fp32 accumulators, before the bf16 rounding of y) instead
+# of a separate pass over y.  FDT_BN_EPILOGUE_STATS=0 restores the separate reduction.
+_EPI_STATS = os.environ.get("FDT_BN_EPILOGUE_STATS", "1") == "1"
+
+
+def _conv_fwd(x, w16, stride, padding, sums=None):
+    """``sums`` ([2*Cout] fp32, zero on entry): filled with Σy, Σy² per channel by the native paths.  Returns
+    (y, sums_filled)."""
     if _native_gemm():
         from . import gemm_sm100
-        y = gemm_sm100.conv_fwd(x, w16, stride, padding)
+        y = gemm_sm100.conv_fwd(x, w16, stride, padding, sums)
         if y is None:       # stride 2 / stem / odd widths: explicit im2col + the same tcgen05 GEMM
-            y = gemm_sm100.conv_fwd_im2col(x, w16, stride, padding)
+            y = gemm_sm100.conv_fwd_im2col(x, w16, stride, padding, sums)
         if y is not None:
-            return y
-    return F.conv2d(x, w16, stride=stride, padding=padding)
+            return y, sums is not None
+    return F.conv2d(x, w16, stride=stride, padding=padding), False
 
 
 def _grad_slot(weight) -> Optional[torch.Tensor]:
@@ -189,9 +202,9 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
     if _native_gemm():
         from . import gemm_sm100
         if need_dx:
-            dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding)
+            dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding, _wdgrad(weight, 0))
             if dx is None:
-                dx = gemm_sm100.conv_dgrad_im2col(dy, w16, x.shape, stride, padding)
+                dx = gemm_sm100.conv_dgrad_im2col(dy, w16, x.shape, stride, padding, _wdgrad(weight, 1))
         if need_dw:
             if mc is not None:      # tile-by-tile in-switch all-reduce fused into the wgrad epilogue
                 dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, mc[0], mc[1], True)
@@ -226,16 +239,25 @@ class _ConvBNAct(torch.autograd.Function):
         stride, padding, eps, act, form = cfg["stride"], cfg["padding"], cfg["eps"], ACT[cfg["act"]], cfg["form"]
         x = _nhwc(x)
         w16 = _w16(weight)
-        y = _conv_fwd(x, w16, stride, padding)
+        C = weight.shape[0]
+        dev = x.device
+        scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)      # sums[2C] | coef[3C]
+        sums = None
+        if _EPI_STATS and form != 2 and C % 8 == 0:
+            sums = scratch[:2 * C]
+            sums.zero_()
+        y, presummed = _conv_fwd(x, w16, stride, padding, sums)
         Nb, C, Ho, Wo = y.shape
         P = Nb * Ho * Wo
-        dev = y.device
-        scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)      # sums[2C] | coef[3C]
         bnctx = torch.empty(5 * C, dtype=torch.float32, device=dev)
         out = torch.empty_like(y)
         res = _nhwc(residual) if residual is not None else None
-        call("fdt_bn_act_fwd", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
-             i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=4 if form != 2 else 2)
+        if presummed:
+            call("fdt_bn_act_fwd_presummed", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"),
+                 cfg.get("running_var"), i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=2)
+        else:
+            call("fdt_bn_act_fwd", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
+                 i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=4 if form != 2 else 2)
         ctx.save_for_backward(x, weight, w16, y, out, bnctx)
         ctx.cfg = (stride, padding, act, form, residual is not None, gamma is not None)
         return out

@@ -79,11 +79,16 @@ def dgrad_weight(w16: torch.Tensor) -> torch.Tensor:
     return w16.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
 
 
-def conv_dgrad(dy: torch.Tensor, w16: torch.Tensor, x_shape, stride: int, padding: int) -> Optional[torch.Tensor]:
-    """dX of a stride-1 "same" convolution = the same implicit GEMM with the rotated, transposed filter."""
+def conv_dgrad(dy: torch.Tensor, w16: torch.Tensor, x_shape, stride: int, padding: int,
+               wt: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """dX of a stride-1 "same" convolution = the same implicit GEMM with the rotated, transposed filter
+    (``wt``: that filter if the caller already has it — FlatParameters.refresh_dgrad_shadow)."""
     N, Cin, H, W = x_shape
     Cout, _, kh, kw = w16.shape
-    wt = dgrad_weight(w16)
+    if not _conv_ok(dy, w16, stride, padding):      # shape-only and symmetric in (Cin, Cout): same answer as for wt
+        return None
+    if wt is None:
+        wt = dgrad_weight(w16)
     if not _conv_ok(dy, wt, stride, padding):
         return None
     return conv_fwd(dy, wt, stride, padding)
@@ -136,12 +141,13 @@ def conv_fwd_im2col(x, w16, stride, padding, sums=None):
     return y
 
 
-def conv_dgrad_im2col(dy, w16, x_shape, stride, padding):
+def conv_dgrad_im2col(dy, w16, x_shape, stride, padding, wt=None):
     geom = _im2col_geom(x_shape, w16.shape, stride, padding)
     if geom is None:
         return None
     N, C, H, W, O, k, Ho, Wo, K, Kp = geom
-    wt = _weight_2d(w16, K, Kp).t().contiguous()                 # [Kp, O]
+    if wt is None or tuple(wt.shape) != (Kp, O):
+        wt = _weight_2d(w16, K, Kp).t().contiguous()             # [Kp, O]
     dA = torch.empty(N * Ho * Wo, Kp, dtype=BF16, device=dy.device)
     call("fdt_gemm_nt", dy, wt, dA, None, None, None, N * Ho * Wo, Kp, O, 0)
     dx = torch.empty((N, C, H, W), dtype=BF16, device=dy.device, memory_format=torch.channels_last)

@@ -52,7 +52,9 @@ class _Linear(torch.autograd.Function):
         gz = gz.contiguous()
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = g.gemm_nt(gz, w16.t().contiguous(), None, "none")
+            from .cuda_ops import _wdgrad
+            wt = _wdgrad(weight, 0)                  # [in, out], produced once per step for all layers
+            dx = g.gemm_nt(gz, wt if wt is not None else w16.t().contiguous(), None, "none")
             if dx is None:
                 dx = gz @ w16
             dx = dx.view(ctx.shp).to(ctx.xdtype)

@@ -168,6 +168,62 @@ class FlatParameters:
             self.shadow_flat = torch.empty(self.total, dtype=torch.bfloat16, device=self.device)
         from ..ops import cuda_ops
         cuda_ops.cast_bf16_(self.param_flat, self.shadow_flat)
+        self.refresh_dgrad_shadow()
+
+    # -- data-gradient operand layouts (transposed / tap-rotated weights), one launch per step
+    def _build_dgrad_table(self):
+        """Parameters flagged by their model with ``_fdt_dgrad_mode`` (0: implicit-GEMM dgrad / Linear,
+        1: col2im dgrad) get a slot in one bf16 buffer that :meth:`refresh_dgrad_shadow` fills from the shadow."""
+        import struct
+        ents, total = [], 0
+        for idx, p in enumerate(self.params):
+            mode = getattr(p, "_fdt_dgrad_mode", None)
+            if mode is None or p.dim() not in (2, 4):
+                continue
+            O, I = p.shape[0], p.shape[1]
+            T = p.shape[2] * p.shape[3] if p.dim() == 4 else 1
+            if O % 8 or I % 8:
+                continue
+            ents.append((idx, O, T, I, int(mode), total))
+            total += O * T * I
+        self._dgrad_views = {}
+        self._dgrad_table = None
+        if not ents:
+            return
+        self.dgrad_flat = torch.empty(total, dtype=torch.bfloat16, device=self.device)
+        rows = []
+        for idx, O, T, I, mode, off in ents:
+            g, i = self._index[idx]
+            src = self.shadow_flat.data_ptr() + 2 * (g.offset + i * g.numel)
+            dst = self.dgrad_flat[off:off + O * T * I]
+            rows.append(struct.pack("<2Q4i", src, dst.data_ptr(), O, T, I, mode))
+            p = self.params[idx]
+            if p.dim() == 2:
+                view = dst.view(I, O)                                    # = W.t().contiguous()
+            elif mode == 0:
+                view = dst.view(I, p.shape[2], p.shape[3], O).permute(0, 3, 1, 2)   # [Cin, Cout, kh, kw] channels_last
+            else:
+                view = dst.view(T * I, O)                                # the [K, O] matrix of the col2im dgrad
+            self._dgrad_views[idx] = (mode, view)
+        blob = b"".join(rows)
+        dev = torch.empty(len(blob), dtype=torch.uint8, device=self.device)
+        dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
+        self._dgrad_table = (dev, len(rows))
+
+    def refresh_dgrad_shadow(self):
+        if self.device.type != "cuda" or self.shadow_flat is None:
+            return
+        if not hasattr(self, "_dgrad_table"):
+            self._build_dgrad_table()
+        if self._dgrad_table is not None:
+            from ..ops._lib import call
+            call("fdt_dgrad_weights", self._dgrad_table[0], self._dgrad_table[1])
+
+    def dgrad_shadow_of(self, p: torch.nn.Parameter, mode: int) -> Optional[torch.Tensor]:
+        ent = getattr(self, "_dgrad_views", {}).get(p._fdt_flat[1])
+        if ent is None or ent[0] != mode or getattr(self, "_dgrad_table", None) is None:
+            return None
+        return ent[1]
 
     def shadow_of(self, p: torch.nn.Parameter) -> Optional[torch.Tensor]:
         if self.shadow_flat is None:

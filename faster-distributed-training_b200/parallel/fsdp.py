@@ -62,6 +62,7 @@ class FullyShardedEngine(nn.Module):
                 if self.flat.shadow_flat is None:
                     self.flat.shadow_flat = torch.empty(self.flat.total, dtype=torch.bfloat16, device=self.flat.device)
                 symm.all_gather_(self.flat.param_flat, *self.region, shadow=self.flat.shadow_flat)
+                self.flat.refresh_dgrad_shadow()
                 self._gathered, self._stale = True, False
                 return
             self.comm.all_gather_(self.flat.param_flat, self.region)

@@ -40,6 +40,11 @@ int fdt_bn_finalize_bwd(const float* sums, const float* ctx, float* coef, float*
 int fdt_bn_act_fwd(const void* y, const void* res, void* out, float* ctx, float* scratch,
                    const float* gamma, const float* beta, float* running_mean, float* running_var,
                    int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st);
+/* same, when scratch[0 .. 2C) already holds Σy, Σy² per channel (written by the conv GEMM epilogue: `sums` of
+ * fdt_conv_fwd / fdt_gemm_nt) — skips the statistics pass over y; forms 0 and 1 only */
+int fdt_bn_act_fwd_presummed(const void* y, const void* res, void* out, float* ctx, float* scratch,
+                   const float* gamma, const float* beta, float* running_mean, float* running_var,
+                   int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st);
 /* Same operation as fdt_bn_act_fwd for callers that cannot supply working memory and must not
  * allocate any (a host that gave the whole GPU to its own pool, a bare C program, a loop that has to
  * keep clear of cudaMalloc/cudaFree): the 5*C floats live in a fixed array inside the library, so

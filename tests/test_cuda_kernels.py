@@ -333,3 +333,37 @@ def test_ngd_small_axis_matches_general_path():
             cu.ngd_small_axis_ok = saved
         outs.append(p.detach().clone())
     _relnorm(outs[0], outs[1], 2e-3, "small-axis vs general NGD trajectory")
+
+
+def test_dgrad_weight_shadow_layouts():
+    """All data-gradient operand layouts produced by one launch (csrc/weight_prep.cu) vs the torch transposes."""
+    from fdt.ops import cuda_ops as cu
+    from fdt.ops import gemm_sm100 as g
+    from fdt.parallel.flat import FlatParameters
+    torch.manual_seed(0)
+    convs = [torch.nn.Parameter(torch.randn(64, 32, 3, 3)), torch.nn.Parameter(torch.randn(72, 40, 1, 1)),
+             torch.nn.Parameter(torch.randn(128, 64, 3, 3)), torch.nn.Parameter(torch.randn(16, 3, 3, 3))]
+    lins = [torch.nn.Parameter(torch.randn(96, 200)), torch.nn.Parameter(torch.randn(10, 64))]
+    modes = [0, 0, 1, 0, 0, 0]
+    for p, m in zip(convs + lins, modes):
+        p._fdt_dgrad_mode = m
+    flat = FlatParameters(convs + lins, device=torch.device(DEV))
+    flat.refresh_shadow()
+    torch.cuda.synchronize()
+    for p, m in zip(convs + lins, modes):
+        w16 = cu._w16(p)
+        got = cu._wdgrad(p, m)
+        if p.shape[0] % 8 or p.shape[1] % 8:
+            assert got is None
+            continue
+        assert got is not None and cu._wdgrad(p, 1 - m) is None
+        if p.dim() == 2:
+            want = w16.t()
+        elif m == 0:
+            want = g.dgrad_weight(w16)
+            assert got.is_contiguous(memory_format=torch.channels_last)
+        else:
+            O, I, kh, kw = p.shape
+            want = g._weight_2d(w16, kh * kw * I, kh * kw * I).t()
+        assert got.shape == want.shape
+        assert torch.equal(got.float(), want.float())
