@@ -224,7 +224,87 @@ __global__ void mixup_ce_kernel(const float* __restrict__ logits, const int64_t*
     if ((threadIdx.x & 31) == 0) { atomicAdd(out, loss); atomicAdd(out + 1, corr); }
 }
 
+// ---- Linear backward preparation: gz = gout ∘ act'(saved) as the bf16 GEMM operand, and the bias gradient
+// db += Σ_rows gz in the same pass (ref: the autograd of F.linear + activation — an elementwise chain, a cast and
+// a reduction per layer).  `saved` is the pre-activation z for GELU, the output for ReLU / tanh.
+// block = 32 column groups of 8 x 8 row lanes; grid = (column slabs of 256, row chunks).
+template <bool kF32In>
+__global__ void __launch_bounds__(256)
+linear_bwd_prep_kernel(const void* __restrict__ gout, const __nv_bfloat16* __restrict__ saved, __nv_bfloat16* __restrict__ gz,
+                       float* __restrict__ db, int64_t T, int N, int act) {
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int col = (blockIdx.x * 32 + tx) * 8;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    if (col < N) {
+        for (int64_t r = (int64_t)blockIdx.y * 8 + ty; r < T; r += (int64_t)gridDim.y * 8) {
+            const int64_t off = r * N + col;
+            float g[8];
+            if (kF32In) {
+                const float4 a = *reinterpret_cast<const float4*>(static_cast<const float*>(gout) + off);
+                const float4 b = *reinterpret_cast<const float4*>(static_cast<const float*>(gout) + off + 4);
+                g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+            } else {
+                unpack8(ld8(static_cast<const __nv_bfloat16*>(gout) + off), g);
+            }
+            if (act != ACT_NONE) {
+                float sv[8];
+                unpack8(ld8(saved + off), sv);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float d;
+                    if (act == ACT_GELU) {
+                        const float z = sv[j];
+                        d = 0.5f * (1.f + erff(z * 0.70710678118654752f)) + z * 0.39894228040143268f * __expf(-0.5f * z * z);
+                    } else {
+                        d = act_bwd_from_out(sv[j], act);
+                    }
+                    g[j] *= d;
+                }
+            }
+            if (gz) st8(gz + off, pack8(g));
+            if (db) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += gz ? __bfloat162float(__float2bfloat16(g[j])) : g[j];
+            }
+        }
+    }
+    if (db == nullptr) return;
+    __shared__ float red[8][32 * 8 + 1];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[ty][tx * 8 + j] = acc[j];
+    __syncthreads();
+    const int c = threadIdx.x;                // one of the slab's 256 columns
+    const int gc = blockIdx.x * 256 + c;
+    if (gc < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += red[k][c];
+        atomicAdd(db + gc, t);
+    }
+}
+
 }  // namespace
+
+// gout: [T, N] bf16 or fp32; saved: [T, N] bf16 or NULL (act == 0); gz: [T, N] bf16 out or NULL (only the bias
+// gradient is wanted); db: [N] fp32, ACCUMULATED into (+=), or NULL.  N % 8 == 0.
+FDT_API int fdt_linear_bwd_prep(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
+                                int act, cudaStream_t st) {
+    if (N % 8 || (act != ACT_NONE && saved == nullptr)) return -1;
+    const int slabs = (N + 255) / 256;
+    int chunks = (int)((T + 63) / 64);
+    const int cap = (148 * 8 + slabs - 1) / slabs;
+    if (chunks > cap) chunks = cap;
+    if (chunks < 1) chunks = 1;
+    dim3 grid(slabs, chunks);
+    if (gout_is_f32)
+        linear_bwd_prep_kernel<true><<<grid, 256, 0, st>>>(gout, (const __nv_bfloat16*)saved, (__nv_bfloat16*)gz, db, T, N, act);
+    else
+        linear_bwd_prep_kernel<false><<<grid, 256, 0, st>>>(gout, (const __nv_bfloat16*)saved, (__nv_bfloat16*)gz, db, T, N, act);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
 
 FDT_API int fdt_ln_fwd(const float* x, const float* a, const float* b, void* y, float* stats, int M, int D, float eps,
                        cudaStream_t st) {

@@ -143,6 +143,14 @@ def _grad_slot(weight) -> Optional[torch.Tensor]:
     return g if g.is_contiguous() and g.dtype == torch.float32 else None
 
 
+def _flat_grad_slot(p) -> Optional[torch.Tensor]:
+    """A 1-D / 2-D flat-buffer parameter's gradient view, for kernels that accumulate into it directly."""
+    if p is None or getattr(p, "_fdt_flat", None) is None or p.grad is None or p.dim() > 2:
+        return None
+    g = p.grad
+    return g if g.is_contiguous() and g.dtype == torch.float32 else None
+
+
 def _mc_slot(weight):
     """(multicast address, alpha) when this parameter's gradient is all-reduced inside the wgrad
     kernel (DDP engine with an NVLS-mapped gradient buffer), else None."""

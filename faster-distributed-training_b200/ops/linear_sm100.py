@@ -31,28 +31,38 @@ class _Linear(torch.autograd.Function):
         else:
             out = g.gemm_nt(x16, w16, b32, act)
             saved = out
-        ctx.save_for_backward(x16, w16, saved, weight)
+        ctx.save_for_backward(x16, w16, saved, weight, bias)
         ctx.act, ctx.shp, ctx.xdtype = act, shp, x.dtype
         ctx.bshape = None if bias is None else bias.shape
         return out.view(*shp[:-1], w16.shape[0])
 
     @staticmethod
     def backward(ctx, gout):
-        x16, w16, saved, weight = ctx.saved_tensors
+        from .cuda_ops import ACT, _flat_grad_slot, _wdgrad
+        from ._lib import call, i64
+        x16, w16, saved, weight, bias = ctx.saved_tensors
         N = w16.shape[0]
-        gz = gout.to(BF16).reshape(-1, N)
-        if ctx.act == "gelu":
-            zf = saved.float()
-            gz = (gz.float() * (0.5 * (1 + torch.erf(zf * 0.7071067811865476)) +
-                                zf * 0.3989422804014327 * torch.exp(-0.5 * zf * zf))).to(BF16)
-        elif ctx.act == "relu":
-            gz = gz * (saved > 0)
-        elif ctx.act == "tanh":
-            gz = (gz.float() * (1 - saved.float() ** 2)).to(BF16)
-        gz = gz.contiguous()
+        g2 = gout.reshape(-1, N)
+        if g2.dtype not in (BF16, torch.float32):
+            g2 = g2.float()
+        if not g2.is_contiguous():
+            g2 = g2.contiguous()
+        T = g2.shape[0]
         dx = dw = db = None
+        # one pass: gz = gout ∘ act'(saved) in bf16 (the GEMM operand) and db += Σ_rows gz
+        need_db = ctx.bshape is not None and ctx.needs_input_grad[2]
+        db_slot = _flat_grad_slot(bias) if need_db else None
+        if need_db and db_slot is None:
+            db = torch.zeros(N, dtype=torch.float32, device=g2.device)
+        reuse = ctx.act == "none" and g2.dtype == BF16          # the incoming gradient already is the operand
+        gz = g2 if reuse else torch.empty(T, N, dtype=BF16, device=g2.device)
+        if need_db or not reuse:
+            call("fdt_linear_bwd_prep", g2, int(g2.dtype == torch.float32), saved if ctx.act != "none" else None,
+                 None if reuse else gz, (db_slot if db_slot is not None else db) if need_db else None, i64(T), N,
+                 ACT[ctx.act])
+        if db is not None:
+            db = db.view(ctx.bshape)
         if ctx.needs_input_grad[0]:
-            from .cuda_ops import _wdgrad
             wt = _wdgrad(weight, 0)                  # [in, out], produced once per step for all layers
             dx = g.gemm_nt(gz, wt if wt is not None else w16.t().contiguous(), None, "none")
             if dx is None:
@@ -70,11 +80,12 @@ class _Linear(torch.autograd.Function):
                     _mc_accumulate(weight, (gz.t() @ x16).float())
                     dw = None
             else:
-                dw = wgrad_sm100.linear_wgrad(gz, x16)
-                if dw is None:
+                slot = _flat_grad_slot(weight)       # accumulate straight into the flat gradient buffer
+                dw = wgrad_sm100.linear_wgrad(gz, x16, slot) if slot is not None else wgrad_sm100.linear_wgrad(gz, x16)
+                if dw is True:
+                    dw = None
+                elif dw is None:
                     dw = (gz.t() @ x16).float()
-        if ctx.bshape is not None and ctx.needs_input_grad[2]:
-            db = gz.float().sum(0).view(ctx.bshape)
         return dx, dw, db, None
 
 

@@ -60,6 +60,10 @@ int fdt_bn_act_fwd_noalloc(const void* y, const void* res, void* out, float* ctx
 /* ---- row-wise kernels, csrc/rowwise.cu ----------------------------------------------------------
  * ref: LayerNorm (transformer.py:230-242), Embeddings (:132-156), sub-layer dropout+residual (:245-275),
  *      mixup_criterion(_meta) (resnet50_test.py:451-457) */
+/* Linear backward preparation: gz = gout ∘ act'(saved) (bf16 GEMM operand) and db += Σ_rows gz in one pass.
+ * gout [T,N] bf16|fp32; saved [T,N] bf16 (z for GELU, the output for ReLU/tanh) or NULL; gz, db may be NULL. */
+int fdt_linear_bwd_prep(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
+                        int act, cudaStream_t st);
 int fdt_ln_fwd(const float* x, const float* a, const float* b, void* y_bf16, float* stats, int M, int D,
                float eps, cudaStream_t st);
 int fdt_ln_bwd(const float* x, const float* a, const float* stats, const void* g_bf16, float* dx_acc,
