@@ -17,6 +17,7 @@
 // the `grad_out_transpose @ activated` products of MLPScratch / nn.Linear (transformer.py:318-334).
 #include "common.cuh"
 #include "sm100.cuh"
+#include <cstdlib>
 #include <mutex>
 
 using namespace fdt;
@@ -61,7 +62,7 @@ __device__ __forceinline__ void mc_red_add_v4(float* addr, float a, float b, flo
 }
 
 template <int BN, int kStages, bool kConv>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WgradParams p) {
     using L = WSmem<BN, kStages>;
     extern __shared__ uint8_t smem_raw[];
@@ -147,27 +148,38 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ C
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
             const int q = warp & 3;
-            const int co = m_tile * BM + q * 32 + lane;
+            // The partial tile goes TMEM → registers → shared memory (the pipeline stages are free: every MMA, hence
+            // every TMA load, has completed) so that each warp can add whole 512-byte row segments with one
+            // red.global.add.v4 per lane: full-line atomics instead of 32 scattered 16-byte ones per instruction.
+            constexpr int kPitch = BN + 4;                      // floats; +16 B keeps the 128-bit row writes conflict-free
+            float* stg = reinterpret_cast<float*>(smem);
+            fence_proxy_async();
+            const int rloc = q * 32 + lane;
+            const float al = p.multicast ? 1.f : p.alpha;       // multicast: alpha is applied when the finished tile is pushed
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 uint32_t r[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
                 tmem_ld_wait();
-                if (co < p.Cout) {
-                    float* dst = p.dw + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c * 32;
-                    const float al = p.alpha;
-                    if (p.multicast) {
-                        // split-K partials meet in the LOCAL staging buffer; only the finished tile crosses NVLink
-                        float* loc = p.acc + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c * 32;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4)
-                            red_add_v4(loc + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                       __uint_as_float(r[j + 3]));
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4)
-                            red_add_v4(dst + j, al * __uint_as_float(r[j]), al * __uint_as_float(r[j + 1]),
-                                       al * __uint_as_float(r[j + 2]), al * __uint_as_float(r[j + 3]));
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(stg + rloc * kPitch + c * 32 + j) =
+                        make_float4(al * __uint_as_float(r[j]), al * __uint_as_float(r[j + 1]), al * __uint_as_float(r[j + 2]),
+                                    al * __uint_as_float(r[j + 3]));
+            }
+            __syncwarp();
+            {
+                constexpr int kF4 = BN / 4;                     // float4 per tile row: 32 (BN = 128) or 16 (BN = 64)
+                constexpr int kRows = 32 / kF4;                 // rows covered by one warp instruction
+                float* base = p.multicast ? p.acc : p.dw;       // multicast: split-K partials meet in the LOCAL staging buffer
+                const int c4 = lane % kF4;
+#pragma unroll 4
+                for (int rr = 0; rr < 32; rr += kRows) {
+                    const int row = q * 32 + rr + lane / kF4;
+                    const int co = m_tile * BM + row;
+                    if (co < p.Cout) {
+                        const float4 v = *reinterpret_cast<const float4*>(stg + row * kPitch + c4 * 4);
+                        red_add_v4(base + ((size_t)co * p.taps + tap) * p.Cin + n_tile * BN + c4 * 4, v.x, v.y, v.z, v.w);
                     }
                 }
             }
@@ -280,7 +292,8 @@ int get_staging(WgradParams& p, int tiles) {
 
 template <int BN, bool kConv>
 int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream_t st) {
-    constexpr int kStages = 4;
+    constexpr int kStages = BN == 128 ? 3 : 4;             // <= 97 KB of shared memory: two CTAs per SM, so one CTA's prologue /
+                                                           // epilogue overlaps the other's main loop
     using L = WSmem<BN, kStages>;
     auto kern = wgrad_kernel<BN, kStages, kConv>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
@@ -288,7 +301,13 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream
     const int tiles_m = (p.Cout + BM - 1) / BM;
     p.tiles_n = p.Cin / BN;
     const int tiles = tiles_m * p.tiles_n * p.taps;
-    int splits = (148 * 2 + tiles - 1) / tiles;            // ~2 waves worth of CTAs
+    static int target = 0;                                 // CTAs per launch: one resident wave (2 CTAs per SM)
+    if (target == 0) {
+        const char* e = getenv("FDT_WGRAD_CTAS");
+        target = e ? atoi(e) : 296;
+        if (target < 1) target = 296;
+    }
+    int splits = target / tiles;                           // round down: a few CTAs over one wave would cost a whole extra round
     if (splits > p.num_kb) splits = p.num_kb;
     if (splits < 1) splits = 1;
     p.kb_per_split = (p.num_kb + splits - 1) / splits;
