@@ -1,19 +1,27 @@
-// Batched TF32 tcgen05 GEMMs for the NGD preconditioner (fp32 operands in shared memory, kind::tf32,
-// fp32 accumulation in tensor memory), one launch per same-shaped factor batch (blockIdx.z = factor).
+// Batched fp32-accurate tcgen05 GEMMs for the NGD preconditioner ("3xTF32": every fp32 operand is split into a
+// tf32-exact high part and a low remainder in shared memory, and three kind::tf32 MMAs — hi·hi, lo·hi, hi·lo —
+// accumulate in fp32 tensor memory; relative error ~2^-22 per product, the level of an fp32 FMA chain).
+// One launch per same-shaped factor batch (blockIdx.z = factor).
 //
-// Per factor (X: the gradient matrix, N rows x D; W: the R x D inverse-Fisher factor, R <= 80):
+// Per factor (X: the gradient matrix, N rows x D; W: the R x D inverse-Fisher factor, R <= 128):
 //     H  = X Wᵀ                       "project"  (store)
 //     X̂  = X − H W                    "deflate"  (subtract epilogue, + Σx², Σx̂² for the norm restoration)
 //     J  = Hᵀ X                       "stats"    (long reduction over the N rows: split-K + red.add)
-// For a tensor's FIRST axis the gradient is only available transposed (X' = Xᵀ, D x N, N contiguous); the
-// same three products are then issued with MN-major operand descriptors / a transposed epilogue instead of
-// materialising X — all four K-major / MN-major operand combinations are used.
+//
+// Pipeline per CTA (one 128 x BN output tile):  TMA warp → [full] → 4 converter/epilogue warps → [conv] → MMA
+// thread → [empty].  The converter warps do two jobs on each landed stage:
+//   * split:      hi = x rounded to tf32 (exactly representable), lo = x − hi, written to a second tile;
+//   * transpose:  kind::tf32 only takes K-major tiles with the plain 128B swizzle, but half of the operands of the
+//                 three products are stored with the M/N index contiguous (Xᵀ for a tensor's first axis, W in the
+//                 deflation, H and X in the statistics).  Those land un-swizzled as [32 k][128 m] boxes and the
+//                 converter writes them out in the K-major 128B-swizzled layout — no transposed copy in global memory.
 //
 // Parity: the torch.mm chain of OnlineNaturalGradient._precondition_directions3 (ngd_optimizer.py:195-218;
 // one cuBLAS SGEMM launch per product per factor — SURVEY.md K17).
 #include "common.cuh"
 #include "sm100.cuh"
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 using namespace fdt;
@@ -21,20 +29,22 @@ using namespace sm100;
 
 namespace {
 
-constexpr int BM = 128, BKE = 32 /* fp32 elements = 128 B */, kThreads = 192, kStages = 4;
+constexpr int BM = 128, BKE = 32 /* fp32 elements = 128 B */, kThreads = 192;
 enum Epi : int { EPI_STORE = 0, EPI_SUB = 1, EPI_RED = 2 };
 
 struct TfParams {
-    int M, N, K;                // GEMM extents per batch item (D = A·Bᵀ-style: D[M,N] = Σ_k A[m,k] B[n,k])
+    int M, N, K;                // GEMM extents per batch item: D[M,N] = Σ_k A[m,k] B[n,k]
     int BN;                     // N tile (multiple of 16, <= 128)
-    int a_mn, b_mn;             // operand majorness: 0 = K contiguous, 1 = M/N contiguous
+    int a_mn, b_mn;             // operand storage: 0 = K contiguous ([rows][K]), 1 = M/N contiguous ([K][rows])
     int epi;
     int c_trans;                // EPI_SUB/STORE: C/out element (m, n) lives at [n * ldc + m] instead of [m * ldc + n]
+    int terms;                  // 3: fp32-accurate split products; 1: plain tf32
     float* out; const float* cin;
     int64_t ldc, batch_stride_c;
     float* sums;                // EPI_SUB: [2 * batches] Σcin², Σout²
     int batches;
     int num_kb, kb_per_split;
+    int stages, stage_bytes, a_raw_off, b_hi_off, b_lo_off, b_raw_off;   // stage layout (bytes from the stage base)
 };
 
 __device__ __forceinline__ void tma_load_3d(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
@@ -48,22 +58,62 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
-__host__ __device__ constexpr uint32_t make_idesc_tf32(uint32_t M, uint32_t N, uint32_t a_mn, uint32_t b_mn) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | (a_mn << 15) | (b_mn << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc_tf32(uint32_t M, uint32_t N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);      // K-major A and B
 }
 
-constexpr int kABytes = BM * 128;           // 128 rows x 128 B (K-major) or 4 atoms of 32 k-rows x 128 B (MN-major)
-constexpr int kBBytes = 128 * 128;
-constexpr int kStageBytes = kABytes + kBBytes;
-constexpr int kSmemTotal = kStages * kStageBytes + (2 * kStages + 1) * 8 + 16 + 1024;
+constexpr int kATile = BM * 128;            // 128 rows x 128 B
+
+// byte offset of the 16-byte chunk (row r, k-quad q) in a K-major tile with the 128B swizzle
+__device__ __forceinline__ uint32_t sw128(int r, int q) { return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((q ^ (r & 7)) << 4)); }
+
+// hi = x rounded to nearest tf32 (10 explicit mantissa bits), lo = x − hi (exact in fp32, |lo| <= 2^-11 |x|, either
+// sign — so the rounding errors of the low-order products do not accumulate in one direction over a long K)
+__device__ __forceinline__ float tf32_rn(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
+__device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
+    hi.x = tf32_rn(v.x); lo.x = v.x - hi.x;
+    hi.y = tf32_rn(v.y); lo.y = v.y - hi.y;
+    hi.z = tf32_rn(v.z); lo.z = v.z - hi.z;
+    hi.w = tf32_rn(v.w); lo.w = v.w - hi.w;
+}
+
+// converter: `rows` x 32 fp32 tile → hi / lo tiles in the K-major swizzled layout.  t = 0..127.
+//   mn == 0: the tile already is K-major swizzled in `hi` (TMA wrote it there): split in place.
+//   mn != 0: the tile sits un-swizzled in `raw` as [32 k][raw_pitch floats]: transpose while splitting.
+__device__ __forceinline__ void convert_tile(uint8_t* hi, uint8_t* lo, const uint8_t* raw, int rows, int raw_pitch, int mn,
+                                             bool want_lo, int t) {
+    if (!mn) {
+        for (int i = t; i < rows * 8; i += 128) {
+            float4* ph = reinterpret_cast<float4*>(hi + i * 16);
+            float4 h, l;
+            split4(*ph, h, l);
+            if (want_lo) { *ph = h; *reinterpret_cast<float4*>(lo + i * 16) = l; }
+        }
+    } else {
+        const float* src = reinterpret_cast<const float*>(raw);
+        for (int r = t; r < rows; r += 128) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                float4 v, h, l;
+                v.x = src[(4 * q + 0) * raw_pitch + r]; v.y = src[(4 * q + 1) * raw_pitch + r];
+                v.z = src[(4 * q + 2) * raw_pitch + r]; v.w = src[(4 * q + 3) * raw_pitch + r];
+                split4(v, h, l);
+                const uint32_t off = sw128(r, q);
+                *reinterpret_cast<float4*>(hi + off) = want_lo ? h : v;
+                if (want_lo) *reinterpret_cast<float4*>(lo + off) = l;
+            }
+        }
+    }
+}
 
 __global__ void __launch_bounds__(kThreads, 1)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TfParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
-    uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * p.stage_bytes);
+    uint64_t* conv_bar = full_bar + 4;
+    uint64_t* empty_bar = conv_bar + 4;
+    uint64_t* tmem_full_bar = empty_bar + 4;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -72,10 +122,11 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int batch = blockIdx.z;
     const int kb0 = blockIdx.y * p.kb_per_split;
     const int nkb = min(p.num_kb, kb0 + p.kb_per_split) - kb0;
+    const int S = p.stages;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA); prefetch_tmap(&tmB);
-        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&conv_bar[s], 128); mbar_init(&empty_bar[s], 1); }
         mbar_init(tmem_full_bar, 1);
         fence_barrier_init();
     }
@@ -90,51 +141,62 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (warp == 0) {
             if (lane == 0) {
                 for (int i = 0; i < nkb; ++i) {
-                    const int kb = kb0 + i, s = i % kStages;
-                    mbar_wait(&empty_bar[s], ((i / kStages) & 1) ^ 1);
-                    uint8_t* sA = smem + s * kStageBytes;
-                    uint8_t* sB = sA + kABytes;
-                    mbar_arrive_expect_tx(&full_bar[s], kABytes + b_bytes);
-                    if (p.a_mn) {       // [K rows][M contiguous]: 4 atoms of {32 m, 32 k}
-#pragma unroll
-                        for (int a = 0; a < 4; ++a) tma_load_3d(sA + a * 4096, &tmA, &full_bar[s], m_tile * BM + a * 32, kb * BKE, batch);
-                    } else {
-                        tma_load_3d(sA, &tmA, &full_bar[s], kb * BKE, m_tile * BM, batch);
-                    }
-                    if (p.b_mn) {
-                        for (int a = 0; a < p.BN / 32; ++a) tma_load_3d(sB + a * 4096, &tmB, &full_bar[s], n_tile * p.BN + a * 32, kb * BKE, batch);
-                    } else {
-                        tma_load_3d(sB, &tmB, &full_bar[s], kb * BKE, n_tile * p.BN, batch);
-                    }
+                    const int kb = kb0 + i, s = i % S;
+                    mbar_wait(&empty_bar[s], ((i / S) & 1) ^ 1);
+                    uint8_t* st = smem + s * p.stage_bytes;
+                    mbar_arrive_expect_tx(&full_bar[s], kATile + b_bytes);
+                    if (p.a_mn) tma_load_3d(st + p.a_raw_off, &tmA, &full_bar[s], m_tile * BM, kb * BKE, batch);   // [32 k][128 m]
+                    else tma_load_3d(st, &tmA, &full_bar[s], kb * BKE, m_tile * BM, batch);                        // [128 m][32 k] swizzled
+                    if (p.b_mn) tma_load_3d(st + p.b_raw_off, &tmB, &full_bar[s], n_tile * p.BN, kb * BKE, batch);
+                    else tma_load_3d(st + p.b_hi_off, &tmB, &full_bar[s], kb * BKE, n_tile * p.BN, batch);
                 }
             }
         } else if (warp == 1) {
             if (lane == 0) {
-                const uint32_t idesc = make_idesc_tf32(BM, (uint32_t)p.BN, (uint32_t)p.a_mn, (uint32_t)p.b_mn);
+                const uint32_t idesc = make_idesc_tf32(BM, (uint32_t)p.BN);
                 for (int i = 0; i < nkb; ++i) {
-                    const int s = i % kStages;
-                    mbar_wait(&full_bar[s], (i / kStages) & 1);
+                    const int s = i % S;
+                    mbar_wait(&conv_bar[s], (i / S) & 1);
                     tc_fence_after();
-                    const uint32_t a_addr = smem_u32(smem + s * kStageBytes), b_addr = a_addr + kABytes;
-                    // K-major: 8-row groups 1 KB apart, +32 B per K=8 step.  MN-major: 32-wide atoms 4 KB apart (LBO),
-                    // 8-k-row groups 1 KB apart (SBO), +1 KB per K=8 step.
-                    const uint64_t da = p.a_mn ? make_smem_desc(a_addr, 4096, 1024) : make_smem_desc(a_addr, 16, 1024);
-                    const uint64_t db = p.b_mn ? make_smem_desc(b_addr, 4096, 1024) : make_smem_desc(b_addr, 16, 1024);
-                    const uint32_t sa = p.a_mn ? 64 : 2, sb = p.b_mn ? 64 : 2;
+                    const uint32_t base = smem_u32(smem + s * p.stage_bytes);
+                    // K-major, 128B swizzle: 8-row groups 1 KB apart, +32 B per K = 8 step
+                    const uint64_t ah = make_smem_desc(base, 16, 1024), al = make_smem_desc(base + kATile, 16, 1024);
+                    const uint64_t bh = make_smem_desc(base + p.b_hi_off, 16, 1024), bl = make_smem_desc(base + p.b_lo_off, 16, 1024);
 #pragma unroll
-                    for (int k = 0; k < BKE / 8; ++k) umma_tf32(tmem_base, da + sa * k, db + sb * k, idesc, (i | k) != 0);
+                    for (int k = 0; k < BKE / 8; ++k) {
+                        if (p.terms == 3) {
+                            umma_tf32(tmem_base, al + 2 * k, bh + 2 * k, idesc, (i | k) != 0);      // small terms first
+                            umma_tf32(tmem_base, ah + 2 * k, bl + 2 * k, idesc, 1);
+                            umma_tf32(tmem_base, ah + 2 * k, bh + 2 * k, idesc, 1);
+                        } else {
+                            umma_tf32(tmem_base, ah + 2 * k, bh + 2 * k, idesc, (i | k) != 0);
+                        }
+                    }
                     umma_commit(&empty_bar[s]);
                 }
                 umma_commit(tmem_full_bar);
             }
         } else {
+            // ---------------- converter: split (and transpose) every landed stage
+            const int t = threadIdx.x - 64;
+            const bool want_lo = p.terms == 3;
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % S;
+                mbar_wait(&full_bar[s], (i / S) & 1);
+                uint8_t* st = smem + s * p.stage_bytes;
+                if (want_lo || p.a_mn) convert_tile(st, st + kATile, st + p.a_raw_off, BM, BM, p.a_mn, want_lo, t);
+                if (want_lo || p.b_mn) convert_tile(st + p.b_hi_off, st + p.b_lo_off, st + p.b_raw_off, p.BN, p.BN, p.b_mn, want_lo, t);
+                fence_proxy_async();                 // generic-proxy writes → visible to the tensor core's async-proxy reads
+                mbar_arrive(&conv_bar[s]);
+            }
+            // ---------------- epilogue
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
             const int q = warp & 3;
             const int m = m_tile * BM + q * 32 + lane;
             const bool m_ok = m < p.M;
-            float* out = p.out + (size_t)batch * p.batch_stride_c;
-            const float* cin = p.cin ? p.cin + (size_t)batch * p.batch_stride_c : nullptr;
+            float* __restrict__ out = p.out + (size_t)batch * p.batch_stride_c;
+            const float* __restrict__ cin = p.cin ? p.cin + (size_t)batch * p.batch_stride_c : nullptr;
             float sq_in = 0.f, sq_out = 0.f;
 #pragma unroll 1
             for (int c = 0; c < (p.BN + 31) / 32; ++c) {
@@ -145,18 +207,35 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (!m_ok) continue;
                 if (p.c_trans) {
                     // element (m, n) at [n * ldc + m]: lanes (consecutive m) hit consecutive addresses
+                    float x[32];
+                    if (p.epi == EPI_SUB) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int n = n0 + j;
+                            x[j] = (n < p.N && c * 32 + j < p.BN) ? __ldg(cin + (size_t)n * p.ldc + m) : 0.f;
+                        }
+                    }
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const int n = n0 + j;
                         if (n < p.N && c * 32 + j < p.BN) {
                             const size_t idx = (size_t)n * p.ldc + m;
                             float v = __uint_as_float(r[j]);
-                            if (p.epi == EPI_SUB) { const float x = cin[idx]; sq_in += x * x; v = x - v; sq_out += v * v; }
+                            if (p.epi == EPI_SUB) { sq_in += x[j] * x[j]; v = x[j] - v; sq_out += v * v; }
                             if (p.epi == EPI_RED) atomicAdd(out + idx, v); else out[idx] = v;
                         }
                     }
                 } else {
                     const size_t row = (size_t)m * p.ldc;
+                    float4 x[8];
+                    if (p.epi == EPI_SUB) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int n = n0 + 4 * j;
+                            x[j] = (n + 3 < p.N && c * 32 + 4 * j + 3 < p.BN) ? __ldg(reinterpret_cast<const float4*>(cin + row + n))
+                                                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) {
                         const int n = n0 + j;
@@ -164,9 +243,9 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
                                                    __uint_as_float(r[j + 3]));
                             if (p.epi == EPI_SUB) {
-                                const float4 x = *reinterpret_cast<const float4*>(cin + row + n);
-                                sq_in += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
-                                v = make_float4(x.x - v.x, x.y - v.y, x.z - v.z, x.w - v.w);
+                                const float4 xx = x[j >> 2];
+                                sq_in += xx.x * xx.x + xx.y * xx.y + xx.z * xx.z + xx.w * xx.w;
+                                v = make_float4(xx.x - v.x, xx.y - v.y, xx.z - v.z, xx.w - v.w);
                                 sq_out += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
                             }
                             if (p.epi == EPI_RED)
@@ -205,91 +284,119 @@ EncodeTiledFn get_encode() {
     });
     return fn;
 }
-// fp32 matrix batch [batches][outer][inner] (inner contiguous, row stride ld elements); box = 32 inner x box_outer
+// fp32 matrix batch [batches][outer][inner] (inner contiguous, row stride ld elements).
+//   swizzled: box = 32 inner x box_outer, 128B swizzle (a K-major operand tile);
+//   raw:      box = box_inner x 32 outer, no swizzle   (an M/N-major tile the converter warps transpose)
 bool encode3(CUtensorMap* m, const float* ptr, uint64_t inner, uint64_t outer, uint64_t batches, uint64_t ld, uint64_t bstride,
-             uint32_t box_outer) {
+             uint32_t box_inner, uint32_t box_outer, bool swizzled) {
     if (!get_encode()) return false;
     cuuint64_t dims[3] = {inner, outer, batches};
     cuuint64_t strides[2] = {ld * 4, bstride * 4};
-    cuuint32_t box[3] = {32, box_outer, 1};
+    cuuint32_t box[3] = {box_inner, box_outer, 1};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(ptr), dims, strides, box, estr,
-                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, swizzled ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
-        fprintf(stderr, "fdt ngd gemm: tensor-map encode failed (%d): inner=%llu outer=%llu batches=%llu ld=%llu\n", (int)r,
-                (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)batches, (unsigned long long)ld);
+        fprintf(stderr, "fdt ngd gemm: tensor-map encode failed (%d): inner=%llu outer=%llu batches=%llu ld=%llu box=%ux%u\n", (int)r,
+                (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)batches, (unsigned long long)ld,
+                box_inner, box_outer);
     return r == CUDA_SUCCESS;
+}
+// operand with `rows` rows (M or N index) and `K` reduction length, tile of box_rows rows
+bool encode_operand(CUtensorMap* m, const float* ptr, int mn, uint64_t rows, uint64_t K, uint64_t batches, uint32_t box_rows) {
+    if (mn) return encode3(m, ptr, rows, K, batches, rows, rows * K, box_rows, 32, false);     // stored [K][rows]
+    return encode3(m, ptr, K, rows, batches, K, rows * K, 32, box_rows, true);                 // stored [rows][K]
+}
+
+int g_terms = 0;
+int terms() {
+    if (g_terms == 0) {
+        const char* e = getenv("FDT_NGD_TF32_TERMS");          // 3 (default): fp32-accurate split products; 1: plain tf32
+        g_terms = (e && atoi(e) == 1) ? 1 : 3;
+    }
+    return g_terms;
 }
 
 int launch(const CUtensorMap& a, const CUtensorMap& b, TfParams p, int splits, cudaStream_t st) {
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
+    p.terms = terms();
+    const int bt = p.BN * 128;
+    // stage: [A hi][A lo][B hi][B lo][A raw?][B raw?]; the lo tiles only exist for the 3-term product
+    int off = kATile;
+    if (p.terms == 3) off += kATile;
+    p.b_hi_off = off; off += bt;
+    p.b_lo_off = off; if (p.terms == 3) off += bt;
+    p.a_raw_off = off; if (p.a_mn) off += kATile;
+    p.b_raw_off = off; if (p.b_mn) off += bt;
+    p.stage_bytes = (off + 1023) & ~1023;
     p.num_kb = (p.K + BKE - 1) / BKE;
+    int stages = (220 * 1024) / p.stage_bytes;
+    if (stages > 4) stages = 4;
+    if (stages > p.num_kb) stages = p.num_kb < 1 ? 1 : p.num_kb;
+    if (stages < 1) return -7;
+    p.stages = stages;
+    const int smem = stages * p.stage_bytes + 13 * 8 + 16 + 1024;
+    static int attr = 0;
+    if (attr < smem) {
+        cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr = 227 * 1024;
+    }
     if (splits < 1) splits = 1;
     if (splits > p.num_kb) splits = p.num_kb;
     p.kb_per_split = (p.num_kb + splits - 1) / splits;
     splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
     const int tiles = ((p.M + BM - 1) / BM) * ((p.N + p.BN - 1) / p.BN);
-    tf32_gemm_kernel<<<dim3(tiles, splits, p.batches), kThreads, kSmemTotal, st>>>(a, b, p);
+    tf32_gemm_kernel<<<dim3(tiles, splits, p.batches), kThreads, smem, st>>>(a, b, p);
     FDT_CHECK_LAUNCH();
     return 0;
 }
 
-int pick_bn(int N, int granule) { return N >= 128 ? 128 : ((N + granule - 1) / granule) * granule; }   // 16 (K-major B) or 32 (MN-major B: whole atoms)
+int pick_bn(int N) { return N >= 128 ? 128 : ((N + 15) / 16) * 16; }
 
 }  // namespace
 
-// All operands are K-major (the reduction index contiguous): with kind::tf32 the plain 128B swizzle is only
-// usable that way, so the few transposed views that are needed (Wᵀ, Hᵀ, and Xᵀ where the gradient is stored the
-// other way round) are small explicit copies made by the caller — W and H are R-wide, X is weight-sized.
-//
-// Projection + deflation for `n` same-shaped factors:
-//   Xrows [n, N, D]   the gradient matrix with rows = N (for a first-axis factor: the transposed copy of X')
-//   W [n, R, D], Wt [n, D, R] (= Wᵀ)
-//   H out [n, N, R] = Xrows Wᵀ
-//   Xhat out = Cin − H W, where Cin / Xhat are [n, N, D] (c_trans == 0) or stored transposed [n, D, N] (c_trans != 0)
-//   sums [2n] zero on entry → Σ Cin², Σ Xhat² per factor.
-// Requirements: R % 16 == 0, R <= 128, D % 4 == 0, (c_trans ? N % 4 == 0 : true).
-FDT_API int fdt_ngd_project(const float* Xrows, const float* W, const float* Wt, float* H, const float* Cin, float* Xhat,
-                            float* sums, int n, int N, int D, int R, int c_trans, cudaStream_t st) {
-    if (R % 16 || R > 128 || D % 4 || (c_trans && N % 4)) return -1;
+// Projection + deflation for `n` same-shaped factors, straight from the gradient where it lies:
+//   X [n, N, D] (x_trans == 0) or the transposed gradient [n, D, N] (x_trans != 0);  W [n, R, D]
+//   H out [n, N, R] = X Wᵀ;  Xhat out (same layout as X) = X − H W;  sums [2n], zero on entry → Σ X², Σ Xhat².
+// Requirements: R % 4 == 0, R <= 128, D % 4 == 0, (x_trans ? N % 4 == 0 : true).
+FDT_API int fdt_ngd_project(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int R,
+                            int x_trans, cudaStream_t st) {
+    if (R % 4 || R > 128 || D % 4 || (x_trans && N % 4) || n <= 0) return -1;
     CUtensorMap tA, tB;
     TfParams p{};
-    p.batches = n; p.a_mn = 0; p.b_mn = 0;
-    // ---- H[N, R] = Xrows Wᵀ :  M = N, N = R, K = D
-    p.M = N; p.N = R; p.K = D; p.BN = pick_bn(R, 16); p.epi = EPI_STORE; p.c_trans = 0;
+    p.batches = n;
+    // ---- H[N, R] = X Wᵀ :  M = N, N = R, K = D;  A = X (K-major, or [D][N] when transposed), B = W [R][D] K-major
+    p.M = N; p.N = R; p.K = D; p.BN = pick_bn(R); p.epi = EPI_STORE; p.c_trans = 0; p.a_mn = x_trans ? 1 : 0; p.b_mn = 0;
     p.out = H; p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)N * R; p.sums = nullptr;
-    if (!encode3(&tA, Xrows, D, N, n, D, (uint64_t)N * D, BM)) return -4;
-    if (!encode3(&tB, W, D, R, n, D, (uint64_t)R * D, p.BN)) return -4;
+    if (!encode_operand(&tA, X, p.a_mn, N, D, n, BM)) return -4;
+    if (!encode_operand(&tB, W, 0, R, D, n, p.BN)) return -4;
     int rc = launch(tA, tB, p, 1, st);
     if (rc) return rc;
-    // ---- Xhat = Cin − H W :  M = N, N = D, K = R ;  A = H [N, R], B = Wt [D, R]
-    p.M = N; p.N = D; p.K = R; p.BN = pick_bn(D, 16); p.epi = EPI_SUB;
-    p.out = Xhat; p.cin = Cin; p.sums = sums;
-    if (c_trans) { p.c_trans = 1; p.ldc = N; } else { p.c_trans = 0; p.ldc = D; }
+    // ---- Xhat = X − H W :  M = N, N = D, K = R;  A = H [N][R] K-major, B[n = d, k = r] = W[r][d]: stored [K][rows]
+    p.M = N; p.N = D; p.K = R; p.BN = pick_bn(D); p.epi = EPI_SUB; p.a_mn = 0; p.b_mn = 1;
+    p.out = Xhat; p.cin = X; p.sums = sums;
+    if (x_trans) { p.c_trans = 1; p.ldc = N; } else { p.c_trans = 0; p.ldc = D; }
     p.batch_stride_c = (int64_t)N * D;
-    if (!encode3(&tA, H, R, N, n, R, (uint64_t)N * R, BM)) return -4;
-    if (!encode3(&tB, Wt, R, D, n, R, (uint64_t)D * R, p.BN)) return -4;
+    if (!encode_operand(&tA, H, 0, N, R, n, BM)) return -4;
+    if (!encode_operand(&tB, W, 1, D, R, n, p.BN)) return -4;
     return launch(tA, tB, p, 1, st);
 }
 
-// J[n, R, D] = Hᵀ X = Ht · Xtᵀ with Ht [n, R, N] and Xt [n, D, N] (both with the N rows contiguous).
-// J must be zero on entry: split-K partial tiles are red.add-ed.  R % 4 == 0, D % 4 == 0, N % 4 == 0.
-FDT_API int fdt_ngd_stats_j(const float* Ht, const float* Xt, float* J, int n, int N, int D, int R, cudaStream_t st) {
-    if (R % 4 || R > 128 || D % 4 || N % 4) return -1;
+// J[n, R, D] = Hᵀ X with H [n, N, R] and X [n, N, D] (x_trans == 0) or [n, D, N] (x_trans != 0).  J is zeroed here;
+// split-K partial tiles are red.add-ed.  R % 4 == 0, D % 4 == 0, (x_trans ? N % 4 == 0 : true).
+FDT_API int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int N, int D, int R, int x_trans, cudaStream_t st) {
+    if (R % 4 || R > 128 || D % 4 || (x_trans && N % 4) || n <= 0) return -1;
+    cudaMemsetAsync(J, 0, sizeof(float) * (size_t)n * R * D, st);
     CUtensorMap tA, tB;
     TfParams p{};
-    p.batches = n; p.a_mn = 0; p.b_mn = 0;
-    p.M = R; p.N = D; p.K = N; p.BN = pick_bn(D, 16); p.epi = EPI_RED; p.c_trans = 0;
+    p.batches = n;
+    // M = R, N = D, K = N;  A[m = r, k = i] = H[i][r]: stored [K][rows];  B[n = d, k = i] = X[i][d] ([K][rows]) or X'[d][i] (K-major)
+    p.M = R; p.N = D; p.K = N; p.BN = pick_bn(D); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = x_trans ? 0 : 1;
     p.out = J; p.cin = nullptr; p.ldc = D; p.batch_stride_c = (int64_t)R * D; p.sums = nullptr;
-    if (!encode3(&tA, Ht, N, R, n, N, (uint64_t)R * N, BM)) return -4;
-    if (!encode3(&tB, Xt, N, D, n, N, (uint64_t)D * N, p.BN)) return -4;
+    if (!encode_operand(&tA, H, 1, R, N, n, BM)) return -4;
+    if (!encode_operand(&tB, X, p.b_mn, D, N, n, p.BN)) return -4;
     const int tiles = ((D + p.BN - 1) / p.BN) * n;
-    int splits = (148 * 2 + tiles - 1) / tiles;
+    int splits = (148 + tiles - 1) / tiles;
     return launch(tA, tB, p, splits, st);
 }

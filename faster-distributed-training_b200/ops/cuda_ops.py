@@ -678,38 +678,33 @@ def ngd_finish_multi(pending):
     call("fdt_ngd_finish_multi", ent[0], ent[1], ent[3], ent[4], ent[5], launches=3)
 
 
-# Opt-in: measured on B200 the batched tf32 tcgen05 kernels are numerically fine (7e-4 relative, tf32) but do
-# not shorten the step (11.6 vs 11.5 ms/step on ResNet-50: the factor batches are small and the extra operand
-# transposes cost what the tensor cores save), so the fp32 torch.bmm path stays the default.
-NGD_TF32 = os.environ.get("FDT_NGD_TF32", "0") == "1"
+# NGD's per-factor products on the tensor cores (csrc/ngd_gemm_sm100.cu): fp32-accurate 3xTF32 by default.
+# FDT_NGD_TC=0 → batched cuBLAS fp32 (torch.bmm); FDT_NGD_TF32_TERMS=1 → plain tf32 (faster, 1e-3 relative).
+NGD_TC = os.environ.get("FDT_NGD_TC", os.environ.get("FDT_NGD_TF32", "1")) == "1"
+NGD_TF32 = NGD_TC       # old name
 
 
 def ngd_tf32_ok(n, N, D, R, left) -> bool:
-    """Shapes the batched tcgen05 (kind::tf32) NGD kernels cover; the rest stays on torch.bmm."""
-    return NGD_TF32 and R % 16 == 0 and R <= 128 and D % 4 == 0 and N % 4 == 0 and N >= 4
+    """Shapes the batched tcgen05 NGD kernels cover; the rest stays on torch.bmm / the short-axis kernel."""
+    return NGD_TC and R % 4 == 0 and 16 <= R <= 128 and D % 4 == 0 and (not left or N % 4 == 0)
 
 
 def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool):
-    """H = X Wᵀ and X̂ = X − H W for a factor batch on the tensor cores (csrc/ngd_gemm_sm100.cu), then the
-    norm-restoring rescale.  ``X`` is [n, N, D] (left=False) or the transposed gradient [n, D, N] (left=True).
-    Returns (H [n, N, R], out (same layout as X), p0 [n], Xrows [n, N, D])."""
+    """H = X Wᵀ and X̂ = X − H W for a factor batch on the tensor cores, then the norm-restoring rescale.  ``X`` is
+    [n, N, D] (left=False) or the transposed gradient [n, D, N] (left=True), used where it lies.
+    Returns (H [n, N, R], out (same layout as X), p0 [n])."""
     n, R, D = W.shape
     N = X[0].numel() // D
-    Xrows = X.transpose(1, 2).contiguous() if left else X
-    Wt = W.transpose(1, 2).contiguous()
     H = torch.empty(n, N, R, dtype=torch.float32, device=X.device)
     Xhat = torch.empty_like(X)
     sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
-    call("fdt_ngd_project", Xrows, W, Wt, H, X, Xhat, sums, n, N, D, R, int(bool(left)), launches=2)
+    call("fdt_ngd_project", X, W, H, Xhat, sums, n, N, D, R, int(bool(left)), launches=2)
     call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(N * D))
-    return H, Xhat, sums[:n], Xrows
+    return H, Xhat, sums[:n]
 
 
 def ngd_stats_j(H: torch.Tensor, X: torch.Tensor, J: torch.Tensor, left: bool):
     """J = Hᵀ X on the tensor cores.  H [n, N, R]; X [n, N, D] (left=False) or [n, D, N] (left=True)."""
     n, R, D = J.shape
     N = H.shape[1]
-    Ht = H.transpose(1, 2).contiguous()
-    Xt = X if left else X.transpose(1, 2).contiguous()
-    J.zero_()
-    call("fdt_ngd_stats_j", Ht, Xt, J, n, N, D, R)
+    call("fdt_ngd_stats_j", H, X, J, n, N, D, R, int(bool(left)))

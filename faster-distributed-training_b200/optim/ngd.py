@@ -288,7 +288,7 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
         cu = ops._cu()
         if cu.ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, left):
             fb._h_rows = True
-            H, out, p0, _ = cu.ngd_project(Xc, fb.W, left)   # tcgen05 tf32: H, X̂ (+Σx², Σx̂²), rescale
+            H, out, p0 = cu.ngd_project(Xc, fb.W, left)      # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale
             if updating:
                 if pending is None:
                     _refresh(fb, Xc, left, H, p0)

@@ -149,9 +149,12 @@ int fdt_ngd_commit_multi(const void* descs, int count, int* flags, int max_elems
 /* W1 = A (J + wc ∘ W) for every factor (80-byte descriptors: W1,d1,rho1,W,d,rho,A,J,wc pointers + int R, D), fused
  * with the finiteness check, then the guarded hand-over: 3 launches for the whole model */
 int fdt_ngd_finish_multi(const void* descs, int count, int* flags, int max_D, int max_elems, cudaStream_t st);
-int fdt_ngd_project(const float* Xrows, const float* W, const float* Wt, float* H, const float* Cin, float* Xhat,
-                    float* sums, int n, int N, int D, int R, int c_trans, cudaStream_t st);
-int fdt_ngd_stats_j(const float* Ht, const float* Xt, float* J, int n, int N, int D, int R, cudaStream_t st);
+/* fp32-accurate tensor-core products (3xTF32 split in shared memory; M/N-major operands transposed in shared memory):
+ * X [n,N,D] (x_trans=0) or [n,D,N] (x_trans=1); W [n,R,D]; H [n,N,R] = X W^T; Xhat = X - H W (layout of X);
+ * sums [2n] zero on entry -> sum X^2, sum Xhat^2.  J [n,R,D] = H^T X (zeroed inside). */
+int fdt_ngd_project(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int R,
+                    int x_trans, cudaStream_t st);
+int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int N, int D, int R, int x_trans, cudaStream_t st);
 /* short axis (2 <= D <= 12, R == (D+1)/2) of the [n, A, D, B] view of a gradient: x̂ = x − Wᵀ(W x) in place of two
  * inner-dimension-3 SGEMMs and a transpose; sums [2n] = Σx², Σx̂²; J [n, R, D] = Σ h xᵀ or NULL.  csrc/ngd_axis.cu */
 int fdt_ngd_small_axis(const float* X, const float* W, float* Xhat, float* sums, float* J, int n, int64_t A, int D,
