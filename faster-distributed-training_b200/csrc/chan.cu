@@ -25,6 +25,8 @@ __global__ void __launch_bounds__(kThreads)
 chan_reduce2_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
                     const __nv_bfloat16* __restrict__ out_act, __nv_bfloat16* __restrict__ g_store,
                     float* __restrict__ sums /*[2,C]*/, int64_t P, int C, int act, int rows_per_block) {
+    pdl_wait();
+    pdl_launch_dependents();
     constexpr int kLanes = kThreads / kTPR;
     const int cv = threadIdx.x % kTPR, rl = threadIdx.x / kTPR;
     const int c0 = (blockIdx.y * kTPR + cv) * 8;
@@ -115,15 +117,72 @@ chan_reduce2_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __
     }
 }
 
+// Where the affine kernels get their per-channel coefficients from.  mode 0: a ready [3,C] table.  mode 1 / 2: derived
+// on the fly from the batch sums — the work of bn_finalize_fwd / bn_finalize_bwd, redone by every CTA for the few
+// channels it needs (a handful of flops) so that the separate finalize launch disappears; the CTA with
+// blockIdx.x == 0 also writes the side outputs (forward: ctx + running statistics; backward: dgamma / dbeta).
+struct BnDerive {
+    int mode, form;
+    const float* sums;                     // mode 1: Σy, Σy² ; mode 2: Σg, Σg·y
+    float* ctx;                            // mode 1: written [5,C]; mode 2: read
+    const float* gamma; const float* beta;
+    float* running_mean; float* running_var;
+    float* dgamma; float* dbeta;
+    float N, eps, momentum;
+};
+
+// form 0: reference FusedConvBN  (unbiased var, eps added to the std, no affine)      resnet.py:85-100
+// form 1: nn.BatchNorm2d training (biased var, eps inside sqrt, affine, running-stat update)
+__device__ __forceinline__ void bn_coef_fwd(const BnDerive& d, int c, int C, bool writer, float& A, float& B, float& Cc) {
+    const float g = d.gamma ? d.gamma[c] : 1.f, b = d.beta ? d.beta[c] : 0.f;
+    const float s = d.sums[c], ss = d.sums[C + c];
+    const float mean = s / d.N;
+    const float m2 = fmaxf(ss - s * mean, 0.f);
+    float inv, k;
+    if (d.form == 0) {
+        const float sd = sqrtf(m2 / (d.N - 1.f));
+        inv = 1.f / (sd + d.eps);
+        k = (sd + d.eps) / ((d.N - 1.f) * fmaxf(sd, 1e-20f));
+    } else {
+        inv = rsqrtf(m2 / d.N + d.eps);
+        k = 1.f / d.N;
+        if (writer && d.running_mean) {
+            d.running_mean[c] = (1.f - d.momentum) * d.running_mean[c] + d.momentum * mean;
+            d.running_var[c] = (1.f - d.momentum) * d.running_var[c] + d.momentum * (m2 / fmaxf(d.N - 1.f, 1.f));
+        }
+    }
+    const float scale = g * inv;
+    A = scale; B = 0.f; Cc = b - mean * scale;
+    if (writer) { d.ctx[c] = mean; d.ctx[C + c] = inv; d.ctx[2 * C + c] = scale; d.ctx[3 * C + c] = k; d.ctx[4 * C + c] = g; }
+}
+// sums = (Σg, Σg·y) → dy = A·g + B·y + Cc ;  dgamma = Σg·ŷ, dbeta = Σg
+__device__ __forceinline__ void bn_coef_bwd(const BnDerive& d, int c, int C, bool writer, float& A, float& B, float& Cc) {
+    const float mean = d.ctx[c], inv = d.ctx[C + c], scale = d.ctx[2 * C + c], k = d.ctx[3 * C + c];
+    const float sg = d.sums[c], sgy = d.sums[C + c];
+    const float sgyh = inv * (sgy - mean * sg);          // Σ g·ŷ
+    if (writer && d.dgamma) { d.dgamma[c] = sgyh; d.dbeta[c] = sg; }
+    if (d.form == 2) { A = scale; B = 0.f; Cc = 0.f; return; }
+    const float b = sg / d.N, cc = k * sgyh;
+    A = scale; B = -scale * cc * inv; Cc = -scale * b + scale * cc * inv * mean;
+}
+__device__ __forceinline__ void bn_coef(const BnDerive& d, const float* __restrict__ coef, int c, int C, bool writer,
+                                        float& A, float& B, float& Cc) {
+    if (d.mode == 1) bn_coef_fwd(d, c, C, writer, A, B, Cc);
+    else if (d.mode == 2) bn_coef_bwd(d, c, C, writer, A, B, Cc);
+    else { A = coef[c]; B = coef[C + c]; Cc = coef[2 * C + c]; }
+}
+
 // out = act(A[c]·x1 + B[c]·x2 + Cc[c] + res);  x2 / res optional.  Grid-stride over 16-byte vectors,
 // four independent vectors in flight per thread, coefficients staged in shared memory.
 template <bool kX2, bool kRes>
 __global__ void __launch_bounds__(kThreads)
 chan_affine_act_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
                        const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
-                       const float* __restrict__ coef /*[3,C]: A,B,Cc*/, int64_t total_vecs, int C, int act) {
+                       const float* __restrict__ coef /*[3,C]: A,B,Cc*/, int64_t total_vecs, int C, int act, const BnDerive d) {
     extern __shared__ float sc[];
-    for (int i = threadIdx.x; i < 3 * C; i += kThreads) sc[i] = coef[i];
+    pdl_wait();
+    pdl_launch_dependents();
+    for (int i = threadIdx.x; i < C; i += kThreads) bn_coef(d, coef, i, C, blockIdx.x == 0, sc[i], sc[C + i], sc[2 * C + i]);
     __syncthreads();
     const int vecC = C >> 3;
     const int64_t stride = (int64_t)gridDim.x * kThreads * 4;
@@ -174,12 +233,15 @@ template <bool kX2, bool kRes, int kAct>
 __global__ void __launch_bounds__(kThreads)
 chan_affine_act_fast_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
                             const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
-                            const float* __restrict__ coef, int64_t total_vecs, int C) {
+                            const float* __restrict__ coef, int64_t total_vecs, int C, const BnDerive d) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int vecC = C >> 3;
     const int c = (threadIdx.x % vecC) * 8;          // blockIdx.x * 1024 and j * 256 are multiples of vecC
     float A[8], B[8], Cc[8];
+    const bool writer = blockIdx.x == 0 && threadIdx.x < vecC;      // these threads cover every channel exactly once
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { A[i] = coef[c + i]; B[i] = kX2 ? coef[C + c + i] : 0.f; Cc[i] = coef[2 * C + c + i]; }
+    for (int i = 0; i < 8; ++i) bn_coef(d, coef, c + i, C, writer, A[i], B[i], Cc[i]);
     const int64_t stride = (int64_t)gridDim.x * kThreads * 4;
     for (int64_t base = (int64_t)blockIdx.x * kThreads * 4 + threadIdx.x; base < total_vecs; base += stride) {
         bf16x8 v1[4], v2[4], vr[4];
@@ -228,6 +290,8 @@ __global__ void bn_finalize_fwd_kernel(const float* __restrict__ sums, float* __
                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                        float* __restrict__ running_mean, float* __restrict__ running_var,
                                        int C, float N, float eps, float momentum, int form) {
+    pdl_wait();
+    pdl_launch_dependents();
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     float mean, inv, k, g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
@@ -262,6 +326,8 @@ __global__ void bn_finalize_fwd_kernel(const float* __restrict__ sums, float* __
 __global__ void bn_finalize_bwd_kernel(const float* __restrict__ sums, const float* __restrict__ ctx,
                                        float* __restrict__ coef, float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        int C, float N, int form) {
+    pdl_wait();
+    pdl_launch_dependents();
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     float mean = ctx[c], inv = ctx[C + c], scale = ctx[2 * C + c], k = ctx[3 * C + c];
@@ -292,21 +358,21 @@ int launch_reduce2(const void* a, const void* b, const void* out_act, void* g_st
     auto A = (const __nv_bfloat16*)a; auto B = (const __nv_bfloat16*)b; auto O = (const __nv_bfloat16*)out_act;
     auto G = (__nv_bfloat16*)g_store;
     if (out_act && act != ACT_NONE)
-        chan_reduce2_kernel<kTPR, true, false><<<grid, kThreads, 0, st>>>(A, B, O, G, sums, P, C, act, (int)rpb);
+        fdt::launch(chan_reduce2_kernel<kTPR, true, false>, grid, dim3(kThreads), 0, st, A, B, O, G, sums, P, C, act, (int)rpb);
     else if (a == b)
-        chan_reduce2_kernel<kTPR, false, true><<<grid, kThreads, 0, st>>>(A, B, nullptr, nullptr, sums, P, C, act, (int)rpb);
+        fdt::launch(chan_reduce2_kernel<kTPR, false, true>, grid, dim3(kThreads), 0, st, A, B, (const __nv_bfloat16*)nullptr, (__nv_bfloat16*)nullptr, sums, P, C, act, (int)rpb);
     else
-        chan_reduce2_kernel<kTPR, false, false><<<grid, kThreads, 0, st>>>(A, B, nullptr, nullptr, sums, P, C, act, (int)rpb);
+        fdt::launch(chan_reduce2_kernel<kTPR, false, false>, grid, dim3(kThreads), 0, st, A, B, (const __nv_bfloat16*)nullptr, (__nv_bfloat16*)nullptr, sums, P, C, act, (int)rpb);
     return 0;
 }
 
 }  // namespace
 
 // sums[2,C] is cleared by this call (stream-ordered memset) before the reduction.
-FDT_API int fdt_chan_reduce2(const void* a, const void* b, const void* out_act, void* g_store, float* sums,
+static int reduce2_impl(bool zero, const void* a, const void* b, const void* out_act, void* g_store, float* sums,
                              int64_t P, int C, int act, cudaStream_t st) {
     if (C % 8 || C <= 0) return -1;
-    cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
+    if (zero) cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, st);
     const int vecC = C / 8;
     if (vecC % 32 == 0) launch_reduce2<32>(a, b, out_act, g_store, sums, P, C, act, st);
     else if (vecC % 16 == 0) launch_reduce2<16>(a, b, out_act, g_store, sums, P, C, act, st);
@@ -318,8 +384,19 @@ FDT_API int fdt_chan_reduce2(const void* a, const void* b, const void* out_act, 
     return 0;
 }
 
-FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res, void* out, const float* coef,
-                                int64_t P, int C, int act, cudaStream_t st) {
+// sums [2C] = Σ a·act'(out), Σ a·act'(out)·b per channel (act' dropped when out_act is NULL); sums is cleared first.
+FDT_API int fdt_chan_reduce2(const void* a, const void* b, const void* out_act, void* g_store, float* sums,
+                             int64_t P, int C, int act, cudaStream_t st) {
+    return reduce2_impl(true, a, b, out_act, g_store, sums, P, C, act, st);
+}
+// same, accumulating into sums (the caller cleared it — e.g. one memset for a whole model's statistics arena)
+FDT_API int fdt_chan_reduce2_acc(const void* a, const void* b, const void* out_act, void* g_store, float* sums,
+                                 int64_t P, int C, int act, cudaStream_t st) {
+    return reduce2_impl(false, a, b, out_act, g_store, sums, P, C, act, st);
+}
+
+static int affine_launch(const void* x1, const void* x2, const void* res, void* out, const float* coef,
+                         int64_t P, int C, int act, const BnDerive& d, cudaStream_t st) {
     if (C % 8 || C <= 0 || 3 * (size_t)C * sizeof(float) > 48 * 1024) return -1;
     const int64_t total = P * (C / 8);
     int64_t blocks = (total + kThreads * 4 - 1) / (kThreads * 4);
@@ -328,7 +405,7 @@ FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res,
     auto X1 = (const __nv_bfloat16*)x1; auto X2 = (const __nv_bfloat16*)x2; auto R = (const __nv_bfloat16*)res;
     auto O = (__nv_bfloat16*)out;
     if (kThreads % (C / 8) == 0 && (act == ACT_NONE || act == ACT_RELU || act == ACT_CELU)) {
-#define FDT_FAST(X2F, RF, ACTV) chan_affine_act_fast_kernel<X2F, RF, ACTV><<<(int)blocks, kThreads, 0, st>>>(X1, X2, R, O, coef, total, C)
+#define FDT_FAST(X2F, RF, ACTV) fdt::launch(chan_affine_act_fast_kernel<X2F, RF, ACTV>, dim3((int)blocks), dim3(kThreads), 0, st, X1, X2, R, O, coef, total, C, d)
 #define FDT_FAST_ACT(X2F, RF) do { if (act == ACT_RELU) FDT_FAST(X2F, RF, ACT_RELU); else if (act == ACT_CELU) FDT_FAST(X2F, RF, ACT_CELU); else FDT_FAST(X2F, RF, ACT_NONE); } while (0)
         if (x2 && res) FDT_FAST_ACT(true, true);
         else if (x2) FDT_FAST_ACT(true, false);
@@ -339,26 +416,53 @@ FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res,
         FDT_CHECK_LAUNCH();
         return 0;
     }
-    if (x2 && res) chan_affine_act_kernel<true, true><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
-    else if (x2) chan_affine_act_kernel<true, false><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
-    else if (res) chan_affine_act_kernel<false, true><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
-    else chan_affine_act_kernel<false, false><<<(int)blocks, kThreads, smem, st>>>(X1, X2, R, O, coef, total, C, act);
+    if (x2 && res) fdt::launch(chan_affine_act_kernel<true, true>, dim3((int)blocks), dim3(kThreads), smem, st, X1, X2, R, O, coef, total, C, act, d);
+    else if (x2) fdt::launch(chan_affine_act_kernel<true, false>, dim3((int)blocks), dim3(kThreads), smem, st, X1, X2, R, O, coef, total, C, act, d);
+    else if (res) fdt::launch(chan_affine_act_kernel<false, true>, dim3((int)blocks), dim3(kThreads), smem, st, X1, X2, R, O, coef, total, C, act, d);
+    else fdt::launch(chan_affine_act_kernel<false, false>, dim3((int)blocks), dim3(kThreads), smem, st, X1, X2, R, O, coef, total, C, act, d);
     FDT_CHECK_LAUNCH();
     return 0;
+}
+
+FDT_API int fdt_chan_affine_act(const void* x1, const void* x2, const void* res, void* out, const float* coef,
+                                int64_t P, int C, int act, cudaStream_t st) {
+    BnDerive d{};
+    return affine_launch(x1, x2, res, out, coef, P, C, act, d, st);
+}
+
+// Normalise [+ residual] + activation with the coefficients derived in the same kernel from scratch[0 .. 2C) =
+// Σy, Σy² (forms 0 and 1): one launch.  Writes ctx [5,C] (and the running statistics) for the backward pass.
+FDT_API int fdt_bn_act_fwd_fused(const void* y, const void* res, void* out, float* ctx, const float* sums,
+                                 const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                 int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st) {
+    if (form != 0 && form != 1) return -1;
+    BnDerive d{};
+    d.mode = 1; d.form = form; d.sums = sums; d.ctx = ctx; d.gamma = gamma; d.beta = beta;
+    d.running_mean = running_mean; d.running_var = running_var; d.N = (float)P; d.eps = eps; d.momentum = momentum;
+    return affine_launch(y, nullptr, res, out, nullptr, P, C, act, d, st);
+}
+
+// Backward counterpart: dy = A·g + B·y + Cc with the coefficients derived from sums = (Σg, Σg·y) and the forward ctx;
+// dgamma / dbeta (may be NULL) are written by the same launch.
+FDT_API int fdt_bn_bwd_apply(const void* g, const void* y, void* dy, const float* sums, const float* ctx, float* dgamma,
+                             float* dbeta, int64_t P, int C, int form, cudaStream_t st) {
+    BnDerive d{};
+    d.mode = 2; d.form = form; d.sums = sums; d.ctx = const_cast<float*>(ctx); d.dgamma = dgamma; d.dbeta = dbeta; d.N = (float)P;
+    return affine_launch(g, y, nullptr, dy, nullptr, P, C, ACT_NONE, d, st);
 }
 
 FDT_API int fdt_bn_finalize_fwd(const float* sums, float* coef, float* ctx, const float* gamma, const float* beta,
                                 float* running_mean, float* running_var, int C, float N, float eps, float momentum,
                                 int form, cudaStream_t st) {
-    bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(sums, coef, ctx, gamma, beta, running_mean, running_var,
-                                                          C, N, eps, momentum, form);
+    fdt::launch(bn_finalize_fwd_kernel, dim3((C + 127) / 128), dim3(128), 0, st, sums, coef, ctx, gamma, beta, running_mean,
+                running_var, C, N, eps, momentum, form);
     FDT_CHECK_LAUNCH();
     return 0;
 }
 
 FDT_API int fdt_bn_finalize_bwd(const float* sums, const float* ctx, float* coef, float* dgamma, float* dbeta,
                                 int C, float N, int form, cudaStream_t st) {
-    bn_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(sums, ctx, coef, dgamma, dbeta, C, N, form);
+    fdt::launch(bn_finalize_bwd_kernel, dim3((C + 127) / 128), dim3(128), 0, st, sums, ctx, coef, dgamma, dbeta, C, N, form);
     FDT_CHECK_LAUNCH();
     return 0;
 }
@@ -391,10 +495,7 @@ FDT_API int fdt_bn_act_fwd_presummed(const void* y, const void* res, void* out, 
                                      const float* gamma, const float* beta, float* running_mean, float* running_var,
                                      int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st) {
     if (C % 8 || form == 2) return -1;
-    float* coef = scratch + 2 * (size_t)C;
-    int rc = fdt_bn_finalize_fwd(scratch, coef, ctx, gamma, beta, running_mean, running_var, C, (float)P, eps, momentum, form, st);
-    if (rc) return rc;
-    return fdt_chan_affine_act(y, nullptr, res, out, coef, P, C, act, st);
+    return fdt_bn_act_fwd_fused(y, res, out, ctx, scratch, gamma, beta, running_mean, running_var, P, C, eps, momentum, form, act, st);
 }
 
 // ---------------------------------------------------------------------------------------------

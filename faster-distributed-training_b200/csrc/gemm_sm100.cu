@@ -106,6 +106,8 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();                    // everything above overlapped the previous kernel's tail; its outputs are visible from here on
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -336,7 +338,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, 
     static int num_sms = 0;
     if (!num_sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
     const int grid = num_tiles < num_sms ? num_tiles : num_sms;
-    kern<<<grid, kThreads, L::kTotal, st>>>(tmA, tmB, tmC, p);
+    if (fdt::launch(kern, dim3(grid), dim3(kThreads), L::kTotal, st, tmA, tmB, tmC, p) != cudaSuccess) return (int)cudaGetLastError();
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -93,6 +93,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ C
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (nkb > 0) {
         if (warp == 0) {
@@ -317,7 +319,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream
         int rc = get_staging(p, tiles);
         if (rc) return rc;
     }
-    kern<<<dim3(tiles, splits), kThreads, L::kTotal, st>>>(a, b, p);
+    if (fdt::launch(kern, dim3(tiles, splits), dim3(kThreads), L::kTotal, st, a, b, p) != cudaSuccess) return (int)cudaGetLastError();
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -45,7 +45,8 @@ class ConvBNStat(nn.Module):
             self.conv_weight.uniform_(-bound, bound)
 
     def forward(self, x, act="none", residual=None):
-        return ops.conv_bnstat_act(x, self.conv_weight, self.stride, self.padding, self.eps, act, residual)
+        return ops.conv_bnstat_act(x, self.conv_weight, self.stride, self.padding, self.eps, act, residual,
+                                   getattr(self, "_fdt_arena", None))
 
     def extra_repr(self):
         return f"{self.in_channels}, {self.out_channels}, k={self.kernel_size}, pad={self.padding}, eps={self.eps}"
@@ -69,7 +70,8 @@ class Act(nn.Module):
 def _conv_bn(conv: nn.Conv2d, bn: nn.BatchNorm2d, x, act="none", residual=None):
     return ops.conv_bnaffine_act(
         x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked,
-        conv.stride[0], conv.padding[0], bn.eps, bn.momentum, bn.training, act, residual)
+        conv.stride[0], conv.padding[0], bn.eps, bn.momentum, bn.training, act, residual,
+        getattr(bn, "_fdt_arena", None))
 
 
 class _Block(nn.Module):
@@ -167,6 +169,14 @@ class ResNet(nn.Module):
         self.fc = nn.Linear(512 * block.expansion, num_classes)
         # layout of the transposed filter the dX GEMM wants (FlatParameters.refresh_dgrad_shadow makes them all in
         # one launch per step): 0 = tap-rotated [Cin][kh][kw][Cout] (implicit GEMM), 1 = [K, Cout] (col2im path)
+        # batch-statistics slots of all conv+BN units in one arena, cleared by a single fill per forward pass
+        self._bn_total = 0
+        self._bn_arena = None
+        for m in self.modules():
+            C = m.out_channels if isinstance(m, ConvBNStat) else (m.num_features if isinstance(m, nn.BatchNorm2d) else 0)
+            if C:
+                m._fdt_arena_off = self._bn_total
+                self._bn_total += 4 * C
         for m in self.modules():
             if isinstance(m, ConvBNStat):
                 m.conv_weight._fdt_dgrad_mode = 0
@@ -185,6 +195,12 @@ class ResNet(nn.Module):
         are bf16 NHWC end to end; the logits come back in fp32."""
         if ops.use_native(x):
             x = ops._cu().to_nhwc_bf16(x)
+            if self._bn_arena is None:
+                self._bn_arena = ops._cu().BNArena()
+                for m in self.modules():
+                    if hasattr(m, "_fdt_arena_off"):
+                        m._fdt_arena = (self._bn_arena, m._fdt_arena_off)
+            self._bn_arena.begin(self._bn_total, x.device)     # also in eval: the FusedConvBN units always use batch statistics
         o = self.conv1[0](x, act="celu")
         o = self.conv2_x(o)
         o = self.conv3_x(o)

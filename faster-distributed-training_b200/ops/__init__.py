@@ -39,19 +39,20 @@ def launch_counter():
     return _lib.LAUNCHES
 
 
-def conv_bnstat_act(x, weight, stride=1, padding=0, eps=1e-3, act="none", residual=None):
+def conv_bnstat_act(x, weight, stride=1, padding=0, eps=1e-3, act="none", residual=None, arena=None):
+    """``arena``: optional ``(BNArena, offset)`` — a statistics slot cleared once per forward pass by the model."""
     if use_native(x):
-        return _cu().conv_bnstat_act(x, weight, stride, padding, eps, act, residual)
+        return _cu().conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena)
     return ref.conv_bnstat_act(x, weight, stride, padding, eps, act, residual)
 
 
 def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_batches_tracked,
                       stride=1, padding=0, eps=1e-5, momentum=0.1, training=True,
-                      act="none", residual=None):
+                      act="none", residual=None, arena=None):
     if use_native(x):
         return _cu().conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
                                        num_batches_tracked, stride, padding, eps, momentum,
-                                       training, act, residual)
+                                       training, act, residual, arena)
     return ref.conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
                                  num_batches_tracked, stride, padding, eps, momentum,
                                  training, act, residual)

@@ -121,6 +121,27 @@ def _next_seed_off(device) -> torch.Tensor:
 _EPI_STATS = os.environ.get("FDT_BN_EPILOGUE_STATS", "1") == "1"
 
 
+class BNArena:
+    """Per-model scratch for the batch statistics of every conv+BN unit: [Σy, Σy² | Σg, Σg·y] (4·C floats) per unit,
+    cleared by ONE fill at the start of each forward pass instead of one memset per unit and direction.  ``gen`` lets
+    a backward pass check that its slice was cleared for *its* forward (two forwards before one backward fall back
+    to private scratch)."""
+
+    def __init__(self):
+        self.buf: Optional[torch.Tensor] = None
+        self.gen = 0
+
+    def begin(self, total: int, device) -> "BNArena":
+        if self.buf is None or self.buf.numel() < total or self.buf.device != device:
+            self.buf = torch.empty(total, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        self.gen += 1
+        return self
+
+    def slice(self, off: int, n: int) -> torch.Tensor:
+        return self.buf[off:off + n]
+
+
 def _conv_fwd(x, w16, stride, padding, sums=None):
     """``sums`` ([2*Cout] fp32, zero on entry): filled with Σy, Σy² per channel by the native paths.  Returns
     (y, sums_filled)."""
@@ -249,21 +270,30 @@ class _ConvBNAct(torch.autograd.Function):
         w16 = _w16(weight)
         C = weight.shape[0]
         dev = x.device
-        scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)      # sums[2C] | coef[3C]
-        sums = None
+        scratch = sums = None
+        ctx.arena = None
+        arena = cfg.get("arena")            # (BNArena, offset): statistics slots cleared once per forward pass
         if _EPI_STATS and form != 2 and C % 8 == 0:
-            sums = scratch[:2 * C]
-            sums.zero_()
+            if arena is not None and arena[0].buf is not None and arena[0].buf.device == dev:
+                slot = arena[0].slice(arena[1], 4 * C)
+                sums = slot[:2 * C]
+                ctx.arena = (arena[0], arena[0].gen, slot[2 * C:])
+            else:
+                scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)      # sums[2C] | coef[3C]
+                sums = scratch[:2 * C]
+                sums.zero_()
         y, presummed = _conv_fwd(x, w16, stride, padding, sums)
         Nb, C, Ho, Wo = y.shape
         P = Nb * Ho * Wo
         bnctx = torch.empty(5 * C, dtype=torch.float32, device=dev)
         out = torch.empty_like(y)
         res = _nhwc(residual) if residual is not None else None
-        if presummed:
-            call("fdt_bn_act_fwd_presummed", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"),
-                 cfg.get("running_var"), i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=2)
+        if presummed:       # statistics came out of the conv epilogue: normalise + act with inline coefficients, one launch
+            call("fdt_bn_act_fwd_fused", y, res, out, bnctx, sums, gamma, beta, cfg.get("running_mean"),
+                 cfg.get("running_var"), i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act)
         else:
+            if scratch is None:
+                scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)
             call("fdt_bn_act_fwd", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
                  i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=4 if form != 2 else 2)
         ctx.save_for_backward(x, weight, w16, y, out, bnctx)
@@ -278,36 +308,38 @@ class _ConvBNAct(torch.autograd.Function):
         P = Nb * Ho * Wo
         dev = y.device
         gout = _nhwc(gout)
-        sums = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        ar = getattr(ctx, "arena", None)
+        if ar is not None and ar[0].gen == ar[1]:       # slot cleared by this step's forward pass: no memset
+            sums, red, nl = ar[2], "fdt_chan_reduce2_acc", 1
+        else:
+            sums, red, nl = torch.empty(2 * C, dtype=torch.float32, device=dev), "fdt_chan_reduce2", 2
         if act != 0:
             g = torch.empty_like(gout)
-            call("fdt_chan_reduce2", gout, y, out, g, sums, i64(P), C, act, launches=2)
+            call(red, gout, y, out, g, sums, i64(P), C, act, launches=nl)
         else:
             g = gout
-            call("fdt_chan_reduce2", gout, y, None, None, sums, i64(P), C, 0, launches=2)
-        coef = torch.empty(3 * C, dtype=torch.float32, device=dev)
+            call(red, gout, y, None, None, sums, i64(P), C, 0, launches=nl)
         dgamma = dbeta = None
         if affine:
             dgamma = torch.empty(C, dtype=torch.float32, device=dev)
             dbeta = torch.empty(C, dtype=torch.float32, device=dev)
-        call("fdt_bn_finalize_bwd", sums, bnctx, coef, dgamma, dbeta, C, float(P), form)
         dy = torch.empty_like(y)
-        call("fdt_chan_affine_act", g, y, None, dy, coef, i64(P), C, 0)
+        call("fdt_bn_bwd_apply", g, y, dy, sums, bnctx, dgamma, dbeta, i64(P), C, form)
         dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape, weight)
         return dx, dw, dgamma, dbeta, (g if has_res else None), None
 
 
-def conv_bnstat_act(x, weight, stride, padding, eps, act, residual):
-    cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=0)
+def conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena=None):
+    cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=0, arena=arena)
     return _ConvBNAct.apply(x, weight, None, None, residual, cfg)
 
 
 def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_batches_tracked, stride, padding,
-                      eps, momentum, training, act, residual):
+                      eps, momentum, training, act, residual, arena=None):
     if training and num_batches_tracked is not None:
         num_batches_tracked.add_(1)
     cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=1 if training else 2,
-               running_mean=running_mean, running_var=running_var, momentum=momentum)
+               running_mean=running_mean, running_var=running_var, momentum=momentum, arena=arena)
     return _ConvBNAct.apply(x, weight, gamma, beta, residual, cfg)
 
 

@@ -589,6 +589,7 @@ class NGD(Optimizer):
             # joined back into the current stream, which also works inside CUDA-graph capture.
             streams = self._side_streams(sgs)
             used = []
+            spending = {}                                  # per side stream: its factor batches awaiting a Fisher refresh
             if streams:
                 main = torch.cuda.current_stream()
                 fork = torch.cuda.Event()
@@ -602,7 +603,7 @@ class NGD(Optimizer):
                         used.append(st)
                     with torch.cuda.stream(st):
                         G = sg.grads()
-                        d_p = self._precondition_group(sg, group, G, pending)
+                        d_p = self._precondition_group(sg, group, G, spending.setdefault(st, []))
                         if d_p is not G:
                             G.copy_(d_p)
                     continue
@@ -627,13 +628,24 @@ class NGD(Optimizer):
                 else:
                     P.add_(d_p, alpha=-lr)
                 sg.write_back(P)
+            late = []
             if used:
                 for st in used:                            # join only the streams that took work
                     ev = torch.cuda.Event()
                     ev.record(st)
                     torch.cuda.current_stream().wait_event(ev)
+                    if spending.get(st):
+                        # the refresh (eigenproblems + W update) of this stream's factors starts right here, overlapping
+                        # the other streams' projections and the parameter update instead of trailing the whole step
+                        with torch.cuda.stream(st):
+                            flush_refreshes(spending[st])
+                        late.append(st)
             if span is not None:
                 self._fused_update(gi, group, gflat, pflat)
+            for st in late:
+                ev = torch.cuda.Event()
+                ev.record(st)
+                torch.cuda.current_stream().wait_event(ev)
         flush_refreshes(pending)
         return loss
 

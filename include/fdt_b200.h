@@ -40,6 +40,16 @@ int fdt_bn_finalize_bwd(const float* sums, const float* ctx, float* coef, float*
 int fdt_bn_act_fwd(const void* y, const void* res, void* out, float* ctx, float* scratch,
                    const float* gamma, const float* beta, float* running_mean, float* running_var,
                    int64_t P, int C, float eps, float momentum, int form, int act, cudaStream_t st);
+/* one-launch variants with the per-channel coefficients derived inside the normalisation kernel (no separate finalize
+ * launch): forward from sums = (Σy, Σy²) — writes ctx [5,C] and the running statistics; backward from sums = (Σg, Σg·y)
+ * and the forward ctx — writes dgamma / dbeta (may be NULL).  fdt_chan_reduce2_acc: fdt_chan_reduce2 without clearing sums. */
+int fdt_bn_act_fwd_fused(const void* y, const void* res, void* out, float* ctx, const float* sums, const float* gamma,
+                         const float* beta, float* running_mean, float* running_var, int64_t P, int C, float eps,
+                         float momentum, int form, int act, cudaStream_t st);
+int fdt_bn_bwd_apply(const void* g, const void* y, void* dy, const float* sums, const float* ctx, float* dgamma,
+                     float* dbeta, int64_t P, int C, int form, cudaStream_t st);
+int fdt_chan_reduce2_acc(const void* a, const void* b, const void* out_act, void* g_store, float* sums, int64_t P, int C,
+                         int act, cudaStream_t st);
 /* same, when scratch[0 .. 2C) already holds Σy, Σy² per channel (written by the conv GEMM epilogue: `sums` of
  * fdt_conv_fwd / fdt_gemm_nt) — skips the statistics pass over y; forms 0 and 1 only */
 int fdt_bn_act_fwd_presummed(const void* y, const void* res, void* out, float* ctx, float* scratch,
