@@ -18,3 +18,9 @@ cap attn_bwd attn attn_bwd 1
 cap chan_affine chan_affine chan_affine 2
 cap chan_reduce chan_reduce chan_reduce2 2
 cap ngd_eig ngd_eig ngd_eig 2
+cap ngd_axis ngd_axis ngd_small_axis 2
+cap ngd_tc_project ngd_tc tf32_gemm 3
+cap ngd_tc_deflate ngd_tc tf32_gemm 4
+cap ngd_tc_stats ngd_tc tf32_gemm 5
+cap lin_prep lin_prep linear_bwd_prep 2
+cap wprep wprep dgrad_weights 2

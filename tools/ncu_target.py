@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Tiny single-kernel driver for `ncu` captures (one GPU, a handful of launches).
-usage: ncu_target.py {conv1x1|conv3x3|gemm|chan_affine|chan_reduce|ngd_eig}"""
+usage: ncu_target.py {conv1x1|conv3x3|gemm|wgrad|attn|chan_affine|chan_reduce|ngd_eig|ngd_axis|ngd_tc|lin_prep|wprep}"""
 import math
 import os
 import sys
@@ -56,5 +56,34 @@ elif what == "ngd_eig":
     for it in range(6):
         X = torch.randn(148, 576, 512, device="cuda")
         M.precondition(fb, X, left=False)
+elif what == "ngd_axis":
+    from fdt.ops import cuda_ops as cu
+    X = torch.randn(3, 512, 3, 3 * 512, device="cuda")          # [n, O, kh, kw*I] view of three 512x512x3x3 gradients
+    W = torch.randn(3, 2, 3, device="cuda") * 0.3
+    J = torch.empty(3, 2, 3, device="cuda")
+    for _ in range(4):
+        cu.ngd_small_axis(X, W, 512, 3, 3 * 512, J)
+elif what == "ngd_tc":
+    from fdt.ops import cuda_ops as cu
+    X = torch.randn(3, 512, 4608, device="cuda")                 # first-axis factor of three 512x512x3x3 gradients (transposed use)
+    W = torch.randn(3, 80, 512, device="cuda") * 0.05
+    J = torch.empty(3, 80, 512, device="cuda")
+    for _ in range(3):
+        H, out, p0 = cu.ngd_project(X, W, True)
+        cu.ngd_stats_j(H, X, J, True)
+elif what == "lin_prep":
+    g = torch.randn(8192, 1024, device="cuda").bfloat16()
+    z = torch.randn(8192, 1024, device="cuda").bfloat16()
+    gz = torch.empty_like(g)
+    db = torch.zeros(1024, device="cuda")
+    for _ in range(4):
+        call("fdt_linear_bwd_prep", g, 0, z, gz, db, i64(8192), 1024, 3)
+elif what == "wprep":
+    from fdt.models.resnet import resnet50
+    from fdt.parallel.flat import FlatParameters
+    m = resnet50(10)
+    flat = FlatParameters(list(m.parameters()), device=torch.device("cuda"))
+    for _ in range(4):
+        flat.refresh_shadow()
 torch.cuda.synchronize()
 print("ok", what)
