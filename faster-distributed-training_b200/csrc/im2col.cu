@@ -56,6 +56,36 @@ im2col_scalar_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restr
     }
 }
 
+// small-C path (the 3-channel stem): one thread per (pixel, 8 columns of the padded row) → one 16-byte store instead of
+// eight 2-byte ones; whole chunks beyond k·k·C are just zero stores.  Kp % 8 == 0.
+__global__ void __launch_bounds__(256)
+im2col_smallc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ A, const ConvGeom g) {
+    const int K = g.k * g.k * g.C, chunks = g.Kp >> 3;
+    const int64_t total = (int64_t)g.N * g.Ho * g.Wo * chunks;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int ch = (int)(i % chunks);
+        const int64_t p = i / chunks;
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = 0.f;
+        if (ch * 8 < K) {
+            const int wo = (int)(p % g.Wo); const int64_t t = p / g.Wo;
+            const int ho = (int)(t % g.Ho); const int n = (int)(t / g.Ho);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int col = ch * 8 + j;
+                if (col < K) {
+                    const int c = col % g.C, tap = col / g.C;
+                    const int r = tap / g.k, s = tap - r * g.k;
+                    const int h = ho * g.stride + r - g.pad, w = wo * g.stride + s - g.pad;
+                    if (h >= 0 && h < g.H && w >= 0 && w < g.W) f[j] = __bfloat162float(x[(((int64_t)n * g.H + h) * g.W + w) * g.C + c]);
+                }
+            }
+        }
+        st8(A + p * g.Kp + ch * 8, pack8(f));
+    }
+}
+
 // dx[n,h,w,c] = Σ_{(r,s): (h+pad−r) % stride == 0, ...} dA[p(ho,wo), (r·kw+s)·C + c]
 template <bool kVec>
 __global__ void __launch_bounds__(256)
@@ -115,7 +145,10 @@ FDT_API int fdt_im2col(const void* x, void* A, int N, int H, int W, int C, int k
         im2col_vec_kernel<<<blocks_for((int64_t)N * Ho * Wo * k * k * (C / 8)), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)A, g);
     } else {
         if (Kp < k * k * C) return -1;
-        im2col_scalar_kernel<<<blocks_for((int64_t)N * Ho * Wo * Kp), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)A, g);
+        if (Kp % 8 == 0)
+            im2col_smallc_kernel<<<blocks_for((int64_t)N * Ho * Wo * (Kp / 8)), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)A, g);
+        else
+            im2col_scalar_kernel<<<blocks_for((int64_t)N * Ho * Wo * Kp), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)A, g);
     }
     FDT_CHECK_LAUNCH();
     return 0;

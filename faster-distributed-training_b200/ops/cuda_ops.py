@@ -142,14 +142,14 @@ class BNArena:
         return self.buf[off:off + n]
 
 
-def _conv_fwd(x, w16, stride, padding, sums=None):
-    """``sums`` ([2*Cout] fp32, zero on entry): filled with Σy, Σy² per channel by the native paths.  Returns
-    (y, sums_filled)."""
+def _conv_fwd(x, w16, stride, padding, sums=None, keep=None):
+    """``sums`` ([2*Cout] fp32, zero on entry): filled with Σy, Σy² per channel by the native paths.  ``keep``: list that
+    receives the im2col matrix when the explicit path ran (reused by the backward pass).  Returns (y, sums_filled)."""
     if _native_gemm():
         from . import gemm_sm100
         y = gemm_sm100.conv_fwd(x, w16, stride, padding, sums)
         if y is None:       # stride 2 / stem / odd widths: explicit im2col + the same tcgen05 GEMM
-            y = gemm_sm100.conv_fwd_im2col(x, w16, stride, padding, sums)
+            y = gemm_sm100.conv_fwd_im2col(x, w16, stride, padding, sums, keep)
         if y is not None:
             return y, sums is not None
     return F.conv2d(x, w16, stride=stride, padding=padding), False
@@ -212,7 +212,7 @@ def join_side_streams():
     _side["keep"].clear()
 
 
-def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=None):
+def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=None, A=None):
     dx = dw = None
     mc = _mc_slot(weight)
     if (_WGRAD_SIDE and need_dw and mc is None and _native_gemm() and weight is not None
@@ -238,12 +238,12 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
             if mc is not None:      # tile-by-tile in-switch all-reduce fused into the wgrad epilogue
                 dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, mc[0], mc[1], True)
                 if dw is None:
-                    dw = gemm_sm100.conv_wgrad_im2col(dy, x, w_shape, stride, padding, mc[0], mc[1], True)
+                    dw = gemm_sm100.conv_wgrad_im2col(dy, x, w_shape, stride, padding, mc[0], mc[1], True, A)
             else:
                 slot = _grad_slot(weight) if weight is not None else None
                 dw = gemm_sm100.conv_wgrad(dy, x, w_shape, stride, padding, slot)
                 if dw is None:
-                    dw = gemm_sm100.conv_wgrad_im2col(dy, x, w_shape, stride, padding, slot)
+                    dw = gemm_sm100.conv_wgrad_im2col(dy, x, w_shape, stride, padding, slot, A=A)
             if dw is True:          # accumulated straight into the flat gradient buffer(s)
                 need_dw, dw = False, None
     if (need_dx and dx is None) or (need_dw and dw is None):
@@ -282,7 +282,9 @@ class _ConvBNAct(torch.autograd.Function):
                 scratch = torch.empty(5 * C, dtype=torch.float32, device=dev)      # sums[2C] | coef[3C]
                 sums = scratch[:2 * C]
                 sums.zero_()
-        y, presummed = _conv_fwd(x, w16, stride, padding, sums)
+        keep = [] if (torch.is_grad_enabled() and weight.requires_grad) else None
+        y, presummed = _conv_fwd(x, w16, stride, padding, sums, keep)
+        ctx.im2col_A = keep[0] if keep else None
         Nb, C, Ho, Wo = y.shape
         P = Nb * Ho * Wo
         bnctx = torch.empty(5 * C, dtype=torch.float32, device=dev)
@@ -325,7 +327,8 @@ class _ConvBNAct(torch.autograd.Function):
             dbeta = torch.empty(C, dtype=torch.float32, device=dev)
         dy = torch.empty_like(y)
         call("fdt_bn_bwd_apply", g, y, dy, sums, bnctx, dgamma, dbeta, i64(P), C, form)
-        dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape, weight)
+        dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape, weight,
+                           getattr(ctx, "im2col_A", None))
         return dx, dw, dgamma, dbeta, (g if has_res else None), None
 
 

@@ -130,7 +130,9 @@ def im2col(x: torch.Tensor, geom, stride, padding) -> torch.Tensor:
     return A
 
 
-def conv_fwd_im2col(x, w16, stride, padding, sums=None):
+def conv_fwd_im2col(x, w16, stride, padding, sums=None, keep=None):
+    """``keep``: a list that receives the im2col matrix, so the weight-gradient GEMM of the backward pass can reuse
+    it instead of rebuilding it."""
     geom = _im2col_geom(x.shape, w16.shape, stride, padding)
     if geom is None:
         return None
@@ -138,6 +140,8 @@ def conv_fwd_im2col(x, w16, stride, padding, sums=None):
     A = im2col(x, geom, stride, padding)
     y = torch.empty((N, O, Ho, Wo), dtype=BF16, device=x.device, memory_format=torch.channels_last)
     call("fdt_gemm_nt", A, _weight_2d(w16, K, Kp), y, None, None, sums, N * Ho * Wo, O, Kp, 0)
+    if keep is not None:
+        keep.append(A)
     return y
 
 
@@ -155,7 +159,7 @@ def conv_dgrad_im2col(dy, w16, x_shape, stride, padding, wt=None):
     return dx
 
 
-def conv_wgrad_im2col(dy, x, w_shape, stride, padding, accumulate_into=None, alpha=1.0, multicast=False):
+def conv_wgrad_im2col(dy, x, w_shape, stride, padding, accumulate_into=None, alpha=1.0, multicast=False, A=None):
     from . import wgrad_sm100
     geom = _im2col_geom(x.shape, w_shape, stride, padding)
     if geom is None:
@@ -163,7 +167,8 @@ def conv_wgrad_im2col(dy, x, w_shape, stride, padding, accumulate_into=None, alp
     N, C, H, W, O, k, Ho, Wo, K, Kp = geom
     if (N * Ho * Wo) % 64:
         return None
-    A = im2col(x, geom, stride, padding)
+    if A is None or tuple(A.shape) != (N * Ho * Wo, Kp):
+        A = im2col(x, geom, stride, padding)
     dy2 = dy.permute(0, 2, 3, 1).reshape(N * Ho * Wo, O)
     if accumulate_into is not None and Kp == K:
         return wgrad_sm100.linear_wgrad(dy2, A, accumulate_into, alpha, multicast)
