@@ -65,6 +65,19 @@ class FlatParameters:
         for p in params:
             key = tuple(p.shape) + (("fused",) if split_fused and fused_first(p) else ())
             buckets.setdefault(key, []).append(p)
+        if self.sharded:
+            # a shape group larger than one rank's fair share is cut into parts of whole tensors, so that the regions
+            # (all padded to the largest one) stay close to total / world and the optimizer work is balanced
+            target = max(1, sum(p.numel() for p in params) // world_size)
+            cut: "OrderedDict[Tuple, List[torch.nn.Parameter]]" = OrderedDict()
+            for s, ps in buckets.items():
+                per = max(1, target // max(1, ps[0].numel()))
+                if len(ps) <= per:
+                    cut[s] = ps
+                else:
+                    for k in range(0, len(ps), per):
+                        cut[s + (f"part{k // per}",)] = ps[k:k + per]
+            buckets = cut
         # shape groups whose gradients are all-reduced inside the wgrad kernels go first, so that the
         # remaining ("tail") gradients form one contiguous range for the stand-alone all-reduce
         self.fused_end = 0
