@@ -122,3 +122,30 @@ def test_resnet50_odd_batches_train_and_eval(bs):
     for _ in range(2):
         loss, _ = tr.step((imgs, y))
     assert torch.isfinite(loss).item()
+
+
+def _run_cli(script, *flags, timeout=600):
+    import pathlib
+    import subprocess
+    import sys
+    root = pathlib.Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / script), "--device", "cuda", "--synthetic", "--no_plots", *flags],
+                       capture_output=True, text=True, timeout=timeout, cwd=str(root))
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-2500:])
+    return r.stdout
+
+
+def test_cli_resnet_gpu_meta_mixup_graph_and_resume(tmp_path):
+    """The reference's command line on the GPU: NGD + meta-mixup, CUDA-graph step, eval loop, checkpoint, --resume."""
+    common = ["--bs", "64", "--ngd", "--meta_learning", "--steps_per_epoch", "14", "--eval_steps", "2", "--cuda_graph",
+              "--ckpt_dir", str(tmp_path)]
+    out = _run_cli("resnet50_test.py", "--epoch", "1", *common)
+    assert "Loss" in out or "loss" in out
+    assert (tmp_path / "resnet_ckpt.pth").exists()
+    _run_cli("resnet50_test.py", "--epoch", "2", "--resume", *common)
+
+
+def test_cli_transformer_gpu(tmp_path):
+    out = _run_cli("transformer_test.py", "--batch_size", "32", "--ngd", "--epoch", "1", "--steps_per_epoch", "14",
+                   "--eval_steps", "2", "--cuda_graph", "--ckpt_dir", str(tmp_path))
+    assert "Loss" in out or "loss" in out
