@@ -224,6 +224,31 @@ __global__ void mixup_ce_kernel(const float* __restrict__ logits, const int64_t*
     if ((threadIdx.x & 31) == 0) { atomicAdd(out, loss); atomicAdd(out + 1, corr); }
 }
 
+// ---- out = dropout(act(z)) in one pass (bf16 in / out), 8 elements per thread; the mask is the Philox stream of
+// (seed, offset) indexed by element / 4 — the same stream linear_bwd_prep regenerates in the backward pass.
+// ref: the FFN's gelu → nn.Dropout pair (transformer.py:296-306), two elementwise kernels + a stored mask there.
+__device__ __forceinline__ void keep8(const int64_t* __restrict__ seed_off, int64_t elem0, float p, float* m) {
+    Philox rng((uint64_t)seed_off[0]);
+    const uint4 a = rng((uint64_t)(elem0 >> 2), (uint64_t)seed_off[1]);
+    const uint4 b = rng((uint64_t)(elem0 >> 2) + 1, (uint64_t)seed_off[1]);
+    const uint32_t rr[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    const float keep = 1.f / (1.f - p);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = u32_to_unit(rr[j]) >= p ? keep : 0.f;
+}
+__global__ void __launch_bounds__(256)
+act_dropout_fwd_kernel(const __nv_bfloat16* __restrict__ z, __nv_bfloat16* __restrict__ out, int64_t n8, int act, float p,
+                       const int64_t* __restrict__ seed_off) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        float f[8], m[8];
+        unpack8(ld8(z + i * 8), f);
+        if (p > 0.f) keep8(seed_off, i * 8, p, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = act_fwd(f[j], act) * (p > 0.f ? m[j] : 1.f);
+        st8(out + i * 8, pack8(f));
+    }
+}
+
 // ---- Linear backward preparation: gz = gout ∘ act'(saved) as the bf16 GEMM operand, and the bias gradient
 // db += Σ_rows gz in the same pass (ref: the autograd of F.linear + activation — an elementwise chain, a cast and
 // a reduction per layer).  `saved` is the pre-activation z for GELU, the output for ReLU / tanh.
@@ -231,7 +256,7 @@ __global__ void mixup_ce_kernel(const float* __restrict__ logits, const int64_t*
 template <bool kF32In>
 __global__ void __launch_bounds__(256)
 linear_bwd_prep_kernel(const void* __restrict__ gout, const __nv_bfloat16* __restrict__ saved, __nv_bfloat16* __restrict__ gz,
-                       float* __restrict__ db, int64_t T, int N, int act) {
+                       float* __restrict__ db, int64_t T, int N, int act, float p, const int64_t* __restrict__ seed_off) {
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int col = (blockIdx.x * 32 + tx) * 8;
     float acc[8];
@@ -247,6 +272,12 @@ linear_bwd_prep_kernel(const void* __restrict__ gout, const __nv_bfloat16* __res
                 g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
             } else {
                 unpack8(ld8(static_cast<const __nv_bfloat16*>(gout) + off), g);
+            }
+            if (p > 0.f) {              // the forward applied dropout after the activation: same Philox stream
+                float m[8];
+                keep8(seed_off, off, p, m);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) g[j] *= m[j];
             }
             if (act != ACT_NONE) {
                 float sv[8];
@@ -289,9 +320,9 @@ linear_bwd_prep_kernel(const void* __restrict__ gout, const __nv_bfloat16* __res
 
 // gout: [T, N] bf16 or fp32; saved: [T, N] bf16 or NULL (act == 0); gz: [T, N] bf16 out or NULL (only the bias
 // gradient is wanted); db: [N] fp32, ACCUMULATED into (+=), or NULL.  N % 8 == 0.
-FDT_API int fdt_linear_bwd_prep(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
-                                int act, cudaStream_t st) {
-    if (N % 8 || (act != ACT_NONE && saved == nullptr)) return -1;
+static int linear_bwd_prep_impl(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
+                                int act, float p, const int64_t* seed_off, cudaStream_t st) {
+    if (N % 8 || (act != ACT_NONE && saved == nullptr) || (p > 0.f && seed_off == nullptr)) return -1;
     const int slabs = (N + 255) / 256;
     int chunks = (int)((T + 63) / 64);
     const int cap = (148 * 8 + slabs - 1) / slabs;
@@ -299,9 +330,30 @@ FDT_API int fdt_linear_bwd_prep(const void* gout, int gout_is_f32, const void* s
     if (chunks < 1) chunks = 1;
     dim3 grid(slabs, chunks);
     if (gout_is_f32)
-        linear_bwd_prep_kernel<true><<<grid, 256, 0, st>>>(gout, (const __nv_bfloat16*)saved, (__nv_bfloat16*)gz, db, T, N, act);
+        linear_bwd_prep_kernel<true><<<grid, 256, 0, st>>>(gout, (const __nv_bfloat16*)saved, (__nv_bfloat16*)gz, db, T, N, act, p, seed_off);
     else
-        linear_bwd_prep_kernel<false><<<grid, 256, 0, st>>>(gout, (const __nv_bfloat16*)saved, (__nv_bfloat16*)gz, db, T, N, act);
+        linear_bwd_prep_kernel<false><<<grid, 256, 0, st>>>(gout, (const __nv_bfloat16*)saved, (__nv_bfloat16*)gz, db, T, N, act, p, seed_off);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_linear_bwd_prep(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
+                                int act, cudaStream_t st) {
+    return linear_bwd_prep_impl(gout, gout_is_f32, saved, gz, db, T, N, act, 0.f, nullptr, st);
+}
+// same for a layer whose forward was out = dropout(act(z), p): the mask of (seed, offset) is regenerated here
+FDT_API int fdt_linear_bwd_prep_dropout(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T,
+                                        int N, int act, float p, const int64_t* seed_off, cudaStream_t st) {
+    return linear_bwd_prep_impl(gout, gout_is_f32, saved, gz, db, T, N, act, p, seed_off, st);
+}
+// out = dropout(act(z), p), bf16, n % 8 == 0; seed_off = {seed, offset} (device) or NULL when p == 0
+FDT_API int fdt_act_dropout_fwd(const void* z, void* out, int64_t n, int act, float p, const int64_t* seed_off, cudaStream_t st) {
+    if (n % 8 || (p > 0.f && seed_off == nullptr) || p >= 1.f) return -1;
+    const int64_t n8 = n / 8;
+    int64_t blocks = (n8 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    act_dropout_fwd_kernel<<<(int)blocks, 256, 0, st>>>((const __nv_bfloat16*)z, (__nv_bfloat16*)out, n8, act, p, seed_off);
     FDT_CHECK_LAUNCH();
     return 0;
 }

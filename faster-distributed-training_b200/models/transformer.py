@@ -97,9 +97,7 @@ class PositionalWiseFFN(nn.Module):
         self.p = dropout
 
     def forward(self, x):
-        h = ops.linear(x, self.w_1.weight, self.w_1.bias, act="gelu")
-        if self.p > 0 and self.training:
-            h = torch.nn.functional.dropout(h, self.p, True)
+        h = ops.linear(x, self.w_1.weight, self.w_1.bias, act="gelu", dropout_p=self.p, training=self.training)
         return ops.linear(h, self.w_2.weight, self.w_2.bias)
 
 

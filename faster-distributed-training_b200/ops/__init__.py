@@ -80,10 +80,13 @@ def layernorm_ref(x, a_2, b_2, eps=1e-6):
     return ref.layernorm_ref(x, a_2, b_2, eps)
 
 
-def linear(x, weight, bias=None, act="none"):
+def linear(x, weight, bias=None, act="none", dropout_p=0.0, training=False):
+    """act(x Wᵀ + b) [→ dropout(dropout_p) when ``training``]."""
+    p = float(dropout_p) if training else 0.0
     if use_native(x):
-        return _cu().linear(x, weight, bias, act)
-    return ref.linear(x, weight, bias, act)
+        return _cu().linear(x, weight, bias, act, p)
+    out = ref.linear(x, weight, bias, act)
+    return torch.nn.functional.dropout(out, p, True) if p > 0 else out
 
 
 def attention(q, k, v, key_mask=None, dropout_p=0.0, training=True, mask_compat=False):

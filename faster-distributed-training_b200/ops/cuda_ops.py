@@ -498,13 +498,16 @@ class _LinearLib(torch.autograd.Function):
         return dx, dw, db, None
 
 
-def linear(x, weight, bias, act):
+def linear(x, weight, bias, act, drop_p=0.0):
+    """act(x Wᵀ + b), optionally followed by dropout(p) fused into the same elementwise pass (mask regenerated, not
+    stored, in the backward)."""
     if _native_gemm():
         from . import gemm_sm100
-        out = gemm_sm100.linear(x, weight, bias, act)
+        out = gemm_sm100.linear(x, weight, bias, act, drop_p)
         if out is not None:
             return out
-    return _LinearLib.apply(x, weight, bias, act)
+    out = _LinearLib.apply(x, weight, bias, act)
+    return F.dropout(out, drop_p, True) if drop_p > 0 else out
 
 
 def attention(q, k, v, key_mask, dropout_p, training, mask_compat):

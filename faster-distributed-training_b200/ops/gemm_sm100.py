@@ -178,9 +178,9 @@ def conv_wgrad_im2col(dy, x, w_shape, stride, padding, accumulate_into=None, alp
     return dw[:, :K].reshape(O, k, k, C).permute(0, 3, 1, 2)
 
 
-def linear(x, weight, bias, act):
+def linear(x, weight, bias, act, drop_p=0.0):
     from . import linear_sm100
-    return linear_sm100.linear(x, weight, bias, act)
+    return linear_sm100.linear(x, weight, bias, act, drop_p)
 
 
 def attention(q, k, v, key_mask, dropout_p, mask_compat):

@@ -74,6 +74,10 @@ int fdt_bn_act_fwd_noalloc(const void* y, const void* res, void* out, float* ctx
  * gout [T,N] bf16|fp32; saved [T,N] bf16 (z for GELU, the output for ReLU/tanh) or NULL; gz, db may be NULL. */
 int fdt_linear_bwd_prep(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
                         int act, cudaStream_t st);
+int fdt_linear_bwd_prep_dropout(const void* gout, int gout_is_f32, const void* saved, void* gz, float* db, int64_t T, int N,
+                                int act, float p, const int64_t* seed_off, cudaStream_t st);
+/* out = dropout(act(z), p) in one pass (bf16, n % 8 == 0); mask = Philox(seed_off[0], seed_off[1]) indexed by element/4 */
+int fdt_act_dropout_fwd(const void* z, void* out, int64_t n, int act, float p, const int64_t* seed_off, cudaStream_t st);
 int fdt_ln_fwd(const float* x, const float* a, const float* b, void* y_bf16, float* stats, int M, int D,
                float eps, cudaStream_t st);
 int fdt_ln_bwd(const float* x, const float* a, const float* stats, const void* g_bf16, float* dx_acc,

@@ -374,3 +374,34 @@ def test_dgrad_weight_shadow_layouts():
             want = g._weight_2d(w16, kh * kw * I, kh * kw * I).t()
         assert got.shape == want.shape
         assert torch.equal(got.float(), want.float())
+
+
+def test_linear_gelu_dropout_fused():
+    """Linear → GELU → dropout as GEMM + one elementwise pass; the backward regenerates the mask from (seed, offset).
+    Check: keep rate, kept values = gelu(z)/(1-p), and gradients equal to autograd through the recovered mask."""
+    ops = _ops()
+    torch.manual_seed(3)
+    T, K, N, p = 512, 128, 256, 0.25
+    x = torch.randn(T, K, device=DEV).bfloat16().requires_grad_(True)
+    w = torch.nn.Parameter(torch.randn(N, K, device=DEV) * 0.1)
+    b = torch.nn.Parameter(torch.randn(N, device=DEV) * 0.1)
+    out = ops.linear(x, w, b, act="gelu", dropout_p=p, training=True)
+    z = torch.nn.functional.linear(x.float(), w.bfloat16().float(), b)
+    full = torch.nn.functional.gelu(z)
+    mask = (out != 0)
+    keep = mask.float().mean().item()
+    assert abs(keep - (1 - p)) < 0.02, keep
+    _close(out.float()[mask], (full / (1 - p))[mask], 3e-2, 3e-2, "kept values")
+    gout = torch.randn_like(out)
+    out.backward(gout)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().bfloat16().float().requires_grad_(True)
+    br = b.detach().clone().requires_grad_(True)
+    ref = torch.nn.functional.gelu(torch.nn.functional.linear(xr, wr, br)) * mask.float() / (1 - p)
+    ref.backward(gout.float())
+    _relnorm(x.grad, xr.grad, 2e-2, "dx")
+    _relnorm(w.grad, wr.grad, 2e-2, "dw")
+    _relnorm(b.grad, br.grad, 2e-2, "db")
+    # eval / p = 0: plain gelu
+    out0 = ops.linear(x.detach(), w, b, act="gelu", dropout_p=p, training=False)
+    _close(out0, full, 3e-2, 3e-2, "eval")
