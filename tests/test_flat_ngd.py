@@ -51,3 +51,39 @@ def test_sharded_layout_regions():
         for g in flat.groups:
             if g.owner == r:
                 assert lo <= g.offset and g.offset + g.size <= hi
+
+
+def test_sharded_layout_cuts_oversized_shape_groups():
+    """FSDP layout: a shape group larger than a rank's fair share is cut into whole-tensor parts, every parameter has
+    exactly one owner, and the padded regions stay close to total / world."""
+    import torch
+    from fdt.models.resnet import resnet50
+    from fdt.parallel.flat import FlatParameters
+    params = list(resnet50(10).parameters())
+    real = sum(p.numel() for p in params)
+    ref = [p.detach().clone() for p in params]
+    flat = FlatParameters(params, device="cpu", world_size=8, shard=True)
+    assert flat.total / real < 1.25, flat.total / real                  # was 2.4x with whole shape groups
+    owned = [flat.owned_params(r) for r in range(8)]
+    ids = [id(p) for ps in owned for p in ps]
+    assert len(ids) == len(set(ids)) == len(params)
+    for r, (lo, hi) in enumerate(flat.region):
+        assert hi - lo == flat.total // 8
+    loads = [sum(p.numel() for p in ps) for ps in owned]
+    assert max(loads) < 1.25 * real / 8 + max(p.numel() for p in params)
+    for p, q in zip(params, ref):                                          # values survived the move into the flat buffer
+        assert torch.equal(p.detach(), q)
+
+
+def test_linear_dropout_dispatch_cpu():
+    import torch
+    from fdt import ops
+    torch.manual_seed(0)
+    x = torch.randn(64, 32)
+    w, b = torch.randn(48, 32), torch.randn(48)
+    full = torch.nn.functional.gelu(torch.nn.functional.linear(x, w, b))
+    assert torch.allclose(ops.linear(x, w, b, act="gelu", dropout_p=0.5, training=False), full)
+    out = ops.linear(x, w, b, act="gelu", dropout_p=0.5, training=True)
+    kept = out != 0
+    assert 0.35 < kept.float().mean().item() < 0.65
+    assert torch.allclose(out[kept], 2.0 * full[kept], atol=1e-6)
