@@ -24,6 +24,7 @@
 // to block b of the peers, so grids must be identical on all ranks and small enough to be
 // co-resident (they are: <= 64 blocks).
 #include "common.cuh"
+#include <cstdlib>
 using namespace fdt;
 
 namespace {
@@ -187,6 +188,46 @@ all_gather_cast_kernel(const CommCtx c, int64_t region, __nv_bfloat16* __restric
     }
 }
 
+// Pull variant (the default): block b reads sub-slice b of every PEER's region straight out of the peer's memory
+// (P2P loads, 8 x 16 B in flight per thread), writes it into the local fp32 buffer and emits the bf16 shadow in the
+// same pass — one remote read, no second sweep over the gathered buffer.  Measured against the push kernel above
+// (multimem.st sustains ~200 GB/s per GPU): see profiles/r1_collective_sweep_*.
+__global__ void __launch_bounds__(kBlock)
+all_gather_pull_cast_kernel(const CommCtx c, int64_t region, __nv_bfloat16* __restrict__ shadow) {
+    const int nb = gridDim.x;
+    block_barrier(c, blockIdx.x * c.world);               // every rank's region is final (its optimizer step is done)
+    const int64_t per = ((region / 4 + nb - 1) / nb) * 4;
+    const int64_t s0 = min(region, per * blockIdx.x), s1 = min(region, s0 + per);
+    float* mine = c.buf[c.rank];
+    constexpr int U = 8;
+    for (int k = 0; k < c.world; ++k) {
+        const int r = (c.rank + k) % c.world;             // own region first, then the peers in a rotated order
+        const float* src = c.buf[r];
+        const int64_t rb = region * r;
+        for (int64_t i = s0 + threadIdx.x * 4; i < s1; i += (int64_t)kBlock * 4 * U) {
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t e = i + (int64_t)u * kBlock * 4;
+                if (e < s1) v[u] = ld_cg(src + rb + e);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t e = i + (int64_t)u * kBlock * 4;
+                if (e < s1) {
+                    if (r != c.rank) st_cg(mine + rb + e, v[u]);
+                    if (shadow) {
+                        __nv_bfloat162 h0 = __floats2bfloat162_rn(v[u].x, v[u].y), h1 = __floats2bfloat162_rn(v[u].z, v[u].w);
+                        *reinterpret_cast<uint2*>(shadow + rb + e) =
+                            make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+                    }
+                }
+            }
+        }
+    }
+    block_barrier(c, (nb + blockIdx.x) * c.world);        // nobody still reads my region when I go on to overwrite it
+}
+
 // The Σg² slot is complete only when the whole collective kernel has finished on this rank (every
 // local block has passed its end barrier).  This 1-thread kernel, stream-ordered right after it, moves
 // the value to ordinary memory and re-arms the slot for the next call.
@@ -247,6 +288,15 @@ FDT_API int fdt_comm_reduce_scatter_mean(const void* ctx, int64_t lo, int64_t hi
 FDT_API int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16, int use_multicast, cudaStream_t st) {
     CommCtx c = *static_cast<const CommCtx*>(ctx);
     if (c.world < 2 || c.world > kMaxWorld || region % 4) return -1;
+    static int mode = -1;                                  // FDT_AG_PUSH=1 restores the push (multimem.st / P2P store) kernel
+    if (mode < 0) { const char* e = getenv("FDT_AG_PUSH"); mode = (e && e[0] == '1') ? 1 : 0; }
+    if (mode == 0) {
+        int64_t b = (region / 4 + kBlock * 2 - 1) / (kBlock * 2);
+        const int blocks = (int)(b < 1 ? 1 : (b > 128 ? 128 : b));      // 2 * blocks * world signal slots <= 2048
+        all_gather_pull_cast_kernel<<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
+        FDT_CHECK_LAUNCH();
+        return 0;
+    }
     const int blocks = pick_blocks(region * 2);
     if (use_multicast && c.mc) all_gather_cast_kernel<true><<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
     else all_gather_cast_kernel<false><<<blocks, kBlock, 0, st>>>(c, region, (__nv_bfloat16*)shadow_bf16);
