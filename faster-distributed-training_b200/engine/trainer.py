@@ -20,6 +20,8 @@ from __future__ import annotations
 
 from typing import Any, Callable, Dict, Optional, Tuple
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -32,6 +34,25 @@ def as_engine(model: nn.Module) -> nn.Module:
     if hasattr(model, "reduce_gradients"):
         return model
     return DataParallelEngine(model, Communicator())
+
+
+
+class _nvtx:
+    """NVTX range around a phase of the step when FDT_NVTX=1 (for nsys / ncu --nvtx timelines; SURVEY.md §5.1);
+    a no-op otherwise and on CPU."""
+    on = os.environ.get("FDT_NVTX", "0") == "1"
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if _nvtx.on and torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *exc):
+        if _nvtx.on and torch.cuda.is_available():
+            torch.cuda.nvtx.range_pop()
+        return False
 
 
 class Trainer:
@@ -77,26 +98,31 @@ class Trainer:
 
     def _eager_step(self, batch) -> Tuple[torch.Tensor, Any]:
         eng = self.engine
-        eng.zero_grad()
-        eng.pre_forward()
-        loss, aux = self.forward_loss(eng, batch)
-        if self.scaler is not None:
-            self.scaler.scale(loss).backward()
-        else:
-            loss.backward()
-        if self.device.type == "cuda":
-            from ..ops import cuda_ops
-            cuda_ops.join_side_streams()              # side-stream weight gradients have landed
-        eng.reduce_gradients()
-        if self.scaler is not None:
-            self.scaler.unscale_(self._local_grad())
-            skipped_before = self.skipped.clone()
-        self._clip()
-        if self.scaler is not None:
-            self.scaler.update(self.skipped - skipped_before)     # device-side found-inf → scale back-off / growth
-        self.optimizer.step()
-        if hasattr(eng, "post_step"):
-            eng.post_step()
+        with _nvtx("fdt/gather+zero"):
+            eng.zero_grad()
+            eng.pre_forward()
+        with _nvtx("fdt/forward"):
+            loss, aux = self.forward_loss(eng, batch)
+        with _nvtx("fdt/backward"):
+            if self.scaler is not None:
+                self.scaler.scale(loss).backward()
+            else:
+                loss.backward()
+            if self.device.type == "cuda":
+                from ..ops import cuda_ops
+                cuda_ops.join_side_streams()              # side-stream weight gradients have landed
+        with _nvtx("fdt/reduce+clip"):
+            eng.reduce_gradients()
+            if self.scaler is not None:
+                self.scaler.unscale_(self._local_grad())
+                skipped_before = self.skipped.clone()
+            self._clip()
+            if self.scaler is not None:
+                self.scaler.update(self.skipped - skipped_before)     # device-side found-inf → scale back-off / growth
+        with _nvtx("fdt/optimizer"):
+            self.optimizer.step()
+            if hasattr(eng, "post_step"):
+                eng.post_step()
         return loss.detach(), aux
 
     # ------------------------------------------------------------------ graph capture

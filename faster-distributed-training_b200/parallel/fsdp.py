@@ -25,12 +25,17 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 import torch.nn as nn
 
 from .comm import Communicator
 from .flat import FlatParameters
 
+
+
+_POISON = os.environ.get("FDT_DEBUG_POISON", "0") == "1"
 
 class FullyShardedEngine(nn.Module):
     def __init__(self, module: nn.Module, comm: Optional[Communicator] = None, allocator=None):
@@ -83,6 +88,17 @@ class FullyShardedEngine(nn.Module):
         """Call after the optimizer updated the owned region: remote regions are now stale."""
         self._gathered = self.comm.world == 1
         self._stale = True
+        if _POISON and self.comm.world > 1:
+            # debug mode (SURVEY.md §5.2): everything this rank does not own, and the whole operand shadow, become NaN,
+            # so a gather that misses a byte — or a kernel that reads a stale copy — poisons the next loss visibly
+            lo, hi = self.region
+            nan = float("nan")
+            self.flat.param_flat[:lo].fill_(nan)
+            self.flat.param_flat[hi:].fill_(nan)
+            if self.flat.shadow_flat is not None:
+                self.flat.shadow_flat.fill_(nan)
+            if getattr(self.flat, "dgrad_flat", None) is not None:
+                self.flat.dgrad_flat.fill_(nan)
 
     def local_grad(self) -> torch.Tensor:
         lo, hi = self.region

@@ -111,7 +111,9 @@ def test_trainer_learns_and_madgrad_steps():
 def _run_dist(script, world=2, port=29631):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)]
-    env = dict(os.environ, OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="")
+    # FDT_DEBUG_POISON: FSDP turns every non-owned parameter into NaN after each step — the run only matches the
+    # single-process one if the all-gather really rewrites all of them
+    env = dict(os.environ, OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="", FDT_DEBUG_POISON="1")
     return subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT), env=env)
 
 
