@@ -291,8 +291,8 @@ ngd_sumsq2_kernel(const float* __restrict__ X, const float* __restrict__ Xh, flo
 }
 // out_f = isnan(p1) ? X_f : X̂_f · sqrt(p0 / (p1 + 1e-30))
 __global__ void __launch_bounds__(256)
-ngd_rescale_kernel(const float* __restrict__ X, const float* __restrict__ Xh, const float* __restrict__ sums,
-                   float* __restrict__ out, int n, int64_t M) {
+ngd_rescale_kernel(const float* __restrict__ X, const float* Xh, const float* __restrict__ sums,
+                   float* out, int n, int64_t M) {          // out may alias Xh (in-place rescale): no __restrict__ on the pair
     const int f = blockIdx.y;
     const float p0 = sums[f], p1 = sums[n + f];
     const bool bad = isnan(p1);

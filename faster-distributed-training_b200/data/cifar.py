@@ -73,7 +73,16 @@ def get_dataset(root: str = "./data", synthetic: bool = False, n_train: int = 50
     """(train, test) datasets; synthetic stand-ins when requested or when CIFAR-10 is unavailable."""
     if not synthetic:
         try:
-            return CIFAR10(root, True, download=True), CIFAR10(root, False, download=True)
+            import torch.distributed as dist
+            multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+            if multi and dist.get_rank() != 0:
+                dist.barrier()          # rank 0 downloads / extracts first (the reference lets every rank race, resnet50_test.py:311)
+            try:
+                out = CIFAR10(root, True, download=True), CIFAR10(root, False, download=True)
+            finally:
+                if multi and dist.get_rank() == 0:
+                    dist.barrier()
+            return out
         except Exception as e:  # no files and no network
             print(f"==> CIFAR-10 unavailable ({type(e).__name__}); using synthetic CIFAR-shape data")
     return SyntheticCIFAR(n_train, seed=0), SyntheticCIFAR(n_test, seed=1)
