@@ -400,3 +400,27 @@ FDT_API int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int
     int splits = (148 + tiles - 1) / tiles;
     return launch(tA, tB, p, splits, st);
 }
+
+// The R x R Fisher statistics of a refresh:  K[n, R, R] = J Jᵀ and (optionally) L[n, R, R] = J Wᵀ, with J, W [n, R, D]
+// (ngd_optimizer.py:205-214: two torch.mm per factor).  Both operands are K-major as stored; the long reduction over D is
+// split over CTAs and red.add-ed.  K and L are zeroed here.  R % 4 == 0, 16 <= R <= 128, D % 4 == 0.
+FDT_API int fdt_ngd_stats_kl(const float* J, const float* W, float* K, float* L, int n, int D, int R, cudaStream_t st) {
+    if (R % 4 || R < 16 || R > 128 || D % 4 || n <= 0) return -1;
+    cudaMemsetAsync(K, 0, sizeof(float) * (size_t)n * R * R, st);
+    if (L) cudaMemsetAsync(L, 0, sizeof(float) * (size_t)n * R * R, st);
+    CUtensorMap tA, tB;
+    TfParams p{};
+    p.batches = n;
+    p.M = R; p.N = R; p.K = D; p.BN = pick_bn(R); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 0; p.b_mn = 0;
+    p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)R * R; p.sums = nullptr;
+    if (!encode_operand(&tA, J, 0, R, D, n, BM)) return -4;
+    if (!encode_operand(&tB, J, 0, R, D, n, p.BN)) return -4;
+    const int splits = (148 + n - 1) / n;
+    p.out = K;
+    int rc = launch(tA, tB, p, splits, st);
+    if (rc || !L) return rc;
+    if (!encode_operand(&tB, W, 0, R, D, n, p.BN)) return -4;
+    p.out = L;
+    return launch(tA, tB, p, splits, st);
+}
+

@@ -746,3 +746,10 @@ def ngd_stats_j(H: torch.Tensor, X: torch.Tensor, J: torch.Tensor, left: bool):
     n, R, D = J.shape
     N = H.shape[1]
     call("fdt_ngd_stats_j", H, X, J, n, N, D, R, int(bool(left)))
+
+
+def ngd_stats_kl(J: torch.Tensor, W: torch.Tensor, K: torch.Tensor, L: Optional[torch.Tensor]):
+    """K = J Jᵀ and (if ``L`` is given) L = J Wᵀ on the tensor cores; J, W [n, R, D]; K, L [n, R, R]."""
+    n, R, D = J.shape
+    call("fdt_ngd_stats_kl", J, W, K, L, n, D, R, launches=2 if L is not None else 1)
+

@@ -168,12 +168,13 @@ def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
     if getattr(fb, "_h_rows", False):
         # H is [n, N, R] for both layouts (tcgen05 path): J on the tensor cores, L / K are R x R
         from .. import ops
-        ops._cu().ngd_stats_j(H, Xm, fb.J, left)
+        cu = ops._cu()
+        cu.ngd_stats_j(H, Xm, fb.J, left)
         if fb.N > fb.D:
-            torch.bmm(fb.J, W.transpose(1, 2), out=fb.L)
+            cu.ngd_stats_kl(fb.J, W, fb.K, fb.L)          # K = J Jᵀ, L = J Wᵀ
         else:
             torch.bmm(H.transpose(1, 2), H, out=fb.L)
-        torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+            cu.ngd_stats_kl(fb.J, W, fb.K, None)
         return
     S = _split_factor(fb.N)
     if left:   # Xm: [n, D, N], H: [n, R, N];  J = H Xᵀ reduces over N

@@ -169,6 +169,8 @@ int fdt_ngd_finish_multi(const void* descs, int count, int* flags, int max_D, in
 int fdt_ngd_project(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int R,
                     int x_trans, cudaStream_t st);
 int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int N, int D, int R, int x_trans, cudaStream_t st);
+/* K [n,R,R] = J J^T and (L != NULL) L [n,R,R] = J W^T on the tensor cores (zeroed inside; 16 <= R <= 128, R % 4 == 0, D % 4 == 0) */
+int fdt_ngd_stats_kl(const float* J, const float* W, float* K, float* L, int n, int D, int R, cudaStream_t st);
 /* short axis (2 <= D <= 12, R == (D+1)/2) of the [n, A, D, B] view of a gradient: x̂ = x − Wᵀ(W x) in place of two
  * inner-dimension-3 SGEMMs and a transpose; sums [2n] = Σx², Σx̂²; J [n, R, D] = Σ h xᵀ or NULL.  csrc/ngd_axis.cu */
 int fdt_ngd_small_axis(const float* X, const float* W, float* Xhat, float* sums, float* J, int n, int64_t A, int D,

@@ -292,6 +292,13 @@ def test_ngd_tcgen05_gemms(n, N, D, R, left):
     Hf = Href.float().contiguous()
     cu.ngd_stats_j(Hf, Xin, J, left)
     _relnorm(J.double(), torch.bmm(Hf.double().transpose(1, 2), Xd), 3e-5, "J")
+    if R >= 16:
+        K = torch.full((n, R, R), 5.0, device=DEV)
+        L = torch.full((n, R, R), 5.0, device=DEV)
+        Jf = J.clone()
+        cu.ngd_stats_kl(Jf, W, K, L)
+        _relnorm(K.double(), torch.bmm(Jf.double(), Jf.double().transpose(1, 2)), 3e-5, "K")
+        _relnorm(L.double(), torch.bmm(Jf.double(), Wd.transpose(1, 2)), 3e-5, "L")
 
 
 @pytest.mark.parametrize("n,A,D,B", [(3, 64, 3, 192), (2, 5, 3, 7), (1, 1, 10, 2048), (4, 576, 3, 1), (2, 9, 4, 36), (1, 3, 12, 20)])
