@@ -158,6 +158,9 @@ class Trainer:
             if self._steps == self.graph_warmup:
                 self._prime_constants(batch)
             return out
+        if self._static_in is not None and any(
+                torch.is_tensor(s_) and torch.is_tensor(b_) and s_.shape != b_.shape for s_, b_ in zip(self._static_in, batch)):
+            return self._eager_step(batch)       # odd-sized batch (e.g. a ragged last one): graphs are shape-specific
         static = self._copy_in(batch)
         from ..ops import _lib
         if kind not in self._graphs:
