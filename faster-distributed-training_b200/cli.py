@@ -212,7 +212,8 @@ def run_resnet(args, tuning=False):
             params = list(params) + [meta.lam]          # λ is really learned (Q3)
     optimizer, scheduler = get_optimizer(params, args, world, tuning)
     if args.resume:
-        ckpt.load_optimizer_sidecar("resnet", optimizer, scheduler, args.ckpt_dir)
+        ckpt.load_optimizer_sidecar("resnet", optimizer, scheduler, args.ckpt_dir, rank,
+                                    bool(getattr(engine, "optimizer_state_sharded", False)))
     trainer = Trainer(engine, optimizer, ResNetStep(args.alpha, meta), clip_norm=10.0, use_cuda_graph=args.cuda_graph)
 
     n_epochs = args.epoch
@@ -353,6 +354,9 @@ def run_transformer(args, tuning=False):
         scheduler = build_scheduler("onecycle", optimizer, max_lr=lr * 5, epochs=max(epochs_total - start_epoch, 1),
                                     steps_per_epoch=max(steps_per_epoch, 1),
                                     cycle_momentum="momentum" in optimizer.defaults and optimizer.defaults["momentum"] > 0)
+    if args.resume:
+        ckpt.load_optimizer_sidecar("transformer", optimizer, scheduler, args.ckpt_dir, rank,
+                                    bool(getattr(engine, "optimizer_state_sharded", False)))
     trainer = Trainer(engine, optimizer, TransformerStep(), clip_norm=10.0, use_cuda_graph=args.cuda_graph)
 
     training_accuracy, testing_accuracy = [], []

@@ -86,6 +86,90 @@ __global__ void madgrad_kernel(float* __restrict__ p, const float* __restrict__ 
     }
 }
 
+// Device-hyper-parameter variants: lr / momentum / dampening (SGD) and lr / step count / momentum (MADGRAD) are read
+// from device memory, so a captured CUDA graph follows LR and momentum schedules without re-capture.
+// hyper = {lr, momentum, dampening}
+__global__ void sgd_momentum_dev_kernel(float* __restrict__ p, const float* __restrict__ d, float* __restrict__ buf,
+                                        int64_t n, const float* __restrict__ hyper, int nesterov, int first) {
+    const float lr = hyper[0], momentum = hyper[1], dampening = hyper[2];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+        if (i + 3 < n) {
+            const float4 dv = *reinterpret_cast<const float4*>(d + i);
+            float4 pv = *reinterpret_cast<float4*>(p + i);
+            float4 st = dv;
+            if (buf) {
+                float4 b = first ? dv : *reinterpret_cast<const float4*>(buf + i);
+                if (!first) {
+                    b.x = momentum * b.x + (1.f - dampening) * dv.x; b.y = momentum * b.y + (1.f - dampening) * dv.y;
+                    b.z = momentum * b.z + (1.f - dampening) * dv.z; b.w = momentum * b.w + (1.f - dampening) * dv.w;
+                }
+                *reinterpret_cast<float4*>(buf + i) = b;
+                if (nesterov) { st.x = dv.x + momentum * b.x; st.y = dv.y + momentum * b.y; st.z = dv.z + momentum * b.z; st.w = dv.w + momentum * b.w; }
+                else st = b;
+            }
+            pv.x -= lr * st.x; pv.y -= lr * st.y; pv.z -= lr * st.z; pv.w -= lr * st.w;
+            *reinterpret_cast<float4*>(p + i) = pv;
+        } else {
+            for (int64_t j = i; j < n; ++j) {
+                const float dj = d[j];
+                float st = dj;
+                if (buf) {
+                    const float b = first ? dj : momentum * buf[j] + (1.f - dampening) * dj;
+                    buf[j] = b;
+                    st = nesterov ? dj + momentum * b : b;
+                }
+                p[j] -= lr * st;
+            }
+        }
+    }
+}
+
+// g = finite(sq) ? g * min(1, max_norm / (sqrt(sq) + 1e-6)) + wd * p : 0      (clip + weight decay in ONE pass;
+// the reference does clip_grad_norm_ and then `d_p.add_(p, alpha=wd)` per tensor: resnet50_test.py:546, ngd_optimizer.py:478)
+__global__ void clip_wd_kernel(float* __restrict__ g, const float* __restrict__ p, int64_t n, const float* __restrict__ sq,
+                               float max_norm, float wd, float* __restrict__ skipped) {
+    const float s = *sq;
+    const bool finite = isfinite(s);
+    const float coef = finite ? (max_norm > 0.f ? fminf(1.f, max_norm / (sqrtf(s) + 1e-6f)) : 1.f) : 0.f;
+    const float w = finite ? wd : 0.f;
+    if (skipped && !finite && blockIdx.x == 0 && threadIdx.x == 0) *skipped += 1.f;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+        if (i + 3 < n) {
+            float4 v = *reinterpret_cast<float4*>(g + i);
+            float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (w != 0.f) q = *reinterpret_cast<const float4*>(p + i);
+            v.x = finite ? v.x * coef + w * q.x : 0.f; v.y = finite ? v.y * coef + w * q.y : 0.f;
+            v.z = finite ? v.z * coef + w * q.z : 0.f; v.w = finite ? v.w * coef + w * q.w : 0.f;
+            *reinterpret_cast<float4*>(g + i) = v;
+        } else {
+            for (int64_t j = i; j < n; ++j) g[j] = finite ? g[j] * coef + (w != 0.f ? w * p[j] : 0.f) : 0.f;
+        }
+    }
+}
+
+// MADGRAD / MirrorMADGRAD with device-resident hyper-parameters: hyper = {lr (+eps already added), k, momentum}.
+// lamb = lr * sqrt(k + 1).  madgrad_tick_kernel advances k afterwards (stream-ordered), so graph replays keep counting.
+__global__ void madgrad_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ v,
+                                   float* __restrict__ s, float* __restrict__ x0, int64_t n, const float* __restrict__ hyper,
+                                   float decay, float eps, int mirror) {
+    const float lamb = hyper[0] * sqrtf(hyper[1] + 1.f);
+    const float ck = 1.f - hyper[2];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float gi = g[i] + decay * p[i];
+        const float vi = v[i] + lamb * gi * gi;
+        v[i] = vi;
+        const float rms = cbrtf(vi) + eps;
+        float z;
+        if (mirror) { z = x0[i] - lamb * gi / rms; x0[i] = z; }
+        else { const float si = s[i] + lamb * gi; s[i] = si; z = x0[i] - si / rms; }
+        p[i] = (1.f - ck) * p[i] + ck * z;
+    }
+}
+__global__ void madgrad_tick_kernel(float* hyper) { hyper[1] += 1.f; }
+
 __global__ void cast_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
     for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
@@ -132,6 +216,30 @@ FDT_API int fdt_madgrad(float* p, const float* g, float* v, float* s, float* x0,
                         float decay, float eps, int mirror, cudaStream_t st) {
     madgrad_kernel<<<grid_for(n, 1), 256, 0, st>>>(p, g, v, s, x0, n, lamb, ck, decay, eps, mirror);
     FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_sgd_momentum_dev(float* p, const float* d, float* buf, int64_t n, const float* hyper, int nesterov, int first,
+                                 cudaStream_t st) {
+    if (!hyper) return -1;
+    sgd_momentum_dev_kernel<<<grid_for(n, 4), 256, 0, st>>>(p, d, buf, n, hyper, nesterov, first);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_clip_wd(float* g, const float* p, int64_t n, const float* sq, float max_norm, float wd, float* skipped,
+                        cudaStream_t st) {
+    clip_wd_kernel<<<grid_for(n, 4), 256, 0, st>>>(g, p, n, sq, max_norm, wd, skipped);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_madgrad_dev(float* p, const float* g, float* v, float* s, float* x0, int64_t n, float* hyper, float decay,
+                            float eps, int mirror, int tick, cudaStream_t st) {
+    if (!hyper) return -1;
+    madgrad_dev_kernel<<<grid_for(n, 1), 256, 0, st>>>(p, g, v, s, x0, n, hyper, decay, eps, mirror);
+    FDT_CHECK_LAUNCH();
+    if (tick) { madgrad_tick_kernel<<<1, 1, 0, st>>>(hyper); FDT_CHECK_LAUNCH(); }
     return 0;
 }
 

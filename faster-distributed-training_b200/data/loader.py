@@ -9,7 +9,7 @@ The reference wraps ``DataLoader`` in ``prefetch_generator.BackgroundGenerator``
 * :class:`TensorBatchLoader` — for datasets that fit in host memory as tensors (CIFAR-10 is
   150 MB of uint8): a batch is one ``index_select`` into a **pinned** staging buffer, so no worker
   processes, no per-sample Python, and the H2D copy is a single async DMA.  Augmentation and
-  normalisation happen on the GPU (``csrc/mixup_loss.cu``), so the loader ships uint8.
+  normalisation happen on the GPU (``csrc/input_head.cu``), so the loader ships uint8.
 * :class:`DevicePrefetcher` — double-buffers the H2D copies on a side stream so step N+1's inputs
   land while step N computes.
 """
@@ -55,6 +55,22 @@ class BackgroundLoader:
         t.join()
 
 
+class _StagedBatch(tuple):
+    """A batch living in a pinned staging slot; :meth:`mark_copied` (called by whoever enqueued the asynchronous
+    host→device copy) lets the loader know when the slot may be refilled."""
+
+    def __new__(cls, tensors, loader, slot):
+        self = super().__new__(cls, tensors)
+        self._loader, self._slot = loader, slot
+        return self
+
+    def mark_copied(self, stream=None):
+        if torch.cuda.is_available():
+            ev = torch.cuda.Event()
+            ev.record(stream if stream is not None else torch.cuda.current_stream())
+            self._loader._slot_events[self._slot] = ev
+
+
 class TensorBatchLoader:
     def __init__(self, tensors: Sequence[torch.Tensor], batch_size: int, sampler: Optional[ShardedSampler] = None,
                  shuffle: bool = True, drop_last: bool = True, pin: Optional[bool] = None, ring: int = 8, seed: int = 0):
@@ -67,7 +83,10 @@ class TensorBatchLoader:
         # DevicePrefetcher (1 ahead + 1 current) keep at most 5 batches alive, so 8 is safe
         self.ring = max(ring, 8)
         self._stage: List[List[torch.Tensor]] = []
-        for _ in range(ring):
+        # one CUDA event per staging slot: DevicePrefetcher records it after the slot's host→device copy was enqueued,
+        # and the slot is not refilled before that copy has finished (ordering, not timing)
+        self._slot_events: List[Optional["torch.cuda.Event"]] = [None] * self.ring
+        for _ in range(self.ring):
             bufs = []
             for t in self.tensors:
                 b = torch.empty((batch_size,) + tuple(t.shape[1:]), dtype=t.dtype)
@@ -86,7 +105,12 @@ class TensorBatchLoader:
         nb = len(self)
         for b in range(nb):
             sel = idx[b * self.batch_size:(b + 1) * self.batch_size]
-            bufs = self._stage[b % self.ring]
+            slot = b % self.ring
+            bufs = self._stage[slot]
+            ev = self._slot_events[slot]
+            if ev is not None:
+                ev.synchronize()              # the previous H2D copy out of this pinned slot is complete
+                self._slot_events[slot] = None
             out = []
             for t, buf in zip(self.tensors, bufs):
                 if sel.numel() == self.batch_size:
@@ -94,7 +118,7 @@ class TensorBatchLoader:
                     out.append(buf)
                 else:
                     out.append(t.index_select(0, sel))
-            yield tuple(out)
+            yield _StagedBatch(out, self, slot) if self.pin else tuple(out)
 
     def bytes_per_batch(self) -> int:
         return sum(b.numel() * b.element_size() for b in self._stage[0])
@@ -116,6 +140,8 @@ class DevicePrefetcher:
             return self.transform(out) if self.transform else out
         with torch.cuda.stream(self.stream):
             out = tuple(b.to(self.device, non_blocking=True) for b in batch)
+            if hasattr(batch, "mark_copied"):
+                batch.mark_copied(self.stream)
             if self.transform:
                 out = self.transform(out)
         return out

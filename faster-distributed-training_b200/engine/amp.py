@@ -26,12 +26,13 @@ class DynamicLossScaler:
 
     def update(self, found_inf: torch.Tensor):
         """``found_inf``: 0-d device tensor (1.0 when the step's gradients were non-finite)."""
+        # in place (copy_) so that a captured CUDA graph keeps reading / writing the same two scalars
         bad = found_inf > 0
-        self._good = torch.where(bad, torch.zeros_like(self._good), self._good + 1)
-        grow = self._good >= self.growth_interval
-        self._scale = torch.where(bad, self._scale * self.backoff_factor,
-                                  torch.where(grow, self._scale * self.growth_factor, self._scale))
-        self._good = torch.where(grow, torch.zeros_like(self._good), self._good)
+        good = torch.where(bad, torch.zeros_like(self._good), self._good + 1)
+        grow = good >= self.growth_interval
+        self._scale.copy_(torch.where(bad, self._scale * self.backoff_factor,
+                                      torch.where(grow, self._scale * self.growth_factor, self._scale)))
+        self._good.copy_(torch.where(grow, torch.zeros_like(good), good))
 
     def get_scale(self) -> float:
         return float(self._scale)

@@ -10,7 +10,10 @@ Read: ``--resume`` restores ``net``, ``best_acc`` and ``start_epoch``
 direction (the reference's distributed resume is broken by this mismatch, Q10).
 
 Beyond the reference: an optional sidecar ``<name>_opt.pth`` keeps optimizer / scheduler / RNG
-state (the NGD factors are plain tensors here, so they can be saved).
+state (the NGD factors are plain tensors here, so they can be saved).  When the engine shards the
+optimizer state (FSDP, or DDP with the sharded optimizer step) every rank writes its own
+``<name>_opt_rank<r>.pth`` — a rank only holds the factors / momentum of the tensors it owns — and
+reads its own file back on ``--resume``.
 """
 from __future__ import annotations
 
@@ -40,17 +43,23 @@ def save_checkpoint(name: str, model: torch.nn.Module, acc: float, epoch: int, r
     """All ranks must call this (an FSDP model gathers collectively); rank 0 writes."""
     sd_fn = getattr(model, "full_state_dict", model.state_dict)
     sd = {k: v.detach().to("cpu").clone() for k, v in sd_fn().items()}
+    sharded = bool(getattr(model, "optimizer_state_sharded", False))
+    if optimizer is not None and (rank == 0 or sharded):
+        os.makedirs(directory, exist_ok=True)
+        side = {"optimizer": optimizer.state_dict(),
+                "scheduler": None if scheduler is None else scheduler.state_dict(),
+                "rng": torch.get_rng_state(), "rank": int(rank), "sharded": sharded}
+        torch.save(side, sidecar_path(name, directory, rank if sharded else None))
     if rank != 0:
         return None
     os.makedirs(directory, exist_ok=True)
     path = ckpt_path(name, directory)
     torch.save({"net": sd, "acc": float(acc), "epoch": int(epoch)}, path)
-    if optimizer is not None:
-        side = {"optimizer": optimizer.state_dict(),
-                "scheduler": None if scheduler is None else scheduler.state_dict(),
-                "rng": torch.get_rng_state()}
-        torch.save(side, os.path.join(directory, f"{name}_opt.pth"))
     return path
+
+
+def sidecar_path(name: str, directory: str = CKPT_DIR, rank: Optional[int] = None) -> str:
+    return os.path.join(directory, f"{name}_opt.pth" if rank is None else f"{name}_opt_rank{rank}.pth")
 
 
 def load_best_performance(name: str, num_class: int, resume: bool, directory: str = CKPT_DIR) -> Tuple[float, int]:
@@ -81,11 +90,19 @@ def load_weights(name: str, model: torch.nn.Module, directory: str = CKPT_DIR, s
     return ck
 
 
-def load_optimizer_sidecar(name: str, optimizer, scheduler=None, directory: str = CKPT_DIR) -> bool:
-    path = os.path.join(directory, f"{name}_opt.pth")
-    if not os.path.isfile(path):
+def load_optimizer_sidecar(name: str, optimizer, scheduler=None, directory: str = CKPT_DIR, rank: int = 0,
+                           sharded: bool = False) -> bool:
+    """``sharded``: the engine shards optimizer state — only this rank's own ``_opt_rank<r>.pth`` is acceptable (another
+    rank's shard would have the wrong tensors; the replicated ``_opt.pth`` of an unsharded run is tried second and is
+    rejected by the optimizer's own validation if it does not fit)."""
+    cands = [sidecar_path(name, directory, rank), sidecar_path(name, directory)] if sharded else [sidecar_path(name, directory)]
+    path = next((c for c in cands if os.path.isfile(c)), None)
+    if path is None:
         return False
     side = torch.load(path, map_location="cpu", weights_only=False)
+    if bool(side.get("sharded", False)) and int(side.get("rank", rank)) != int(rank):
+        print(f"==> optimizer sidecar {path} belongs to rank {side.get('rank')}; starting with fresh optimizer state")
+        return False
     try:
         optimizer.load_state_dict(side["optimizer"])
     except (KeyError, ValueError, AssertionError) as e:

@@ -71,8 +71,16 @@ class Trainer:
         self._static_out = None
         self._steps = 0
         self.skipped = torch.zeros((), device=self.device)   # steps whose gradients were non-finite
-        if self.use_graph and hasattr(optimizer, "set_capturable"):
-            optimizer.set_capturable(True)
+        if self.use_graph:
+            # Only optimizers that keep their schedule-dependent scalars (lr, momentum, step count) on the device can
+            # be replayed: a captured graph bakes every Python float into its kernels' arguments.
+            if hasattr(optimizer, "set_capturable"):
+                optimizer.set_capturable(True)
+            else:
+                import warnings
+                warnings.warn(f"{type(optimizer).__name__} is not CUDA-graph capturable (its lr / momentum / step count "
+                              f"are host scalars that a graph replay would freeze); running the step eagerly")
+                self.use_graph = False
 
     # ------------------------------------------------------------------ one eager step
     def _local_grad(self) -> torch.Tensor:
@@ -81,6 +89,9 @@ class Trainer:
     def _clip(self):
         g = self._local_grad()
         sq = self.engine.grad_sq_norm()
+        fused = getattr(self.optimizer, "fused_clip_wd", None)
+        if fused is not None and g.is_cuda and fused(sq, self.clip_norm, self.skipped):
+            return                          # clip + non-finite guard + weight decay ran as one pass over the gradients
         if g.is_cuda:
             from .. import ops
             if ops.use_native(g):       # one fused kernel: clip coefficient, non-finite guard, scaling
@@ -161,6 +172,13 @@ class Trainer:
         if self._static_in is not None and any(
                 torch.is_tensor(s_) and torch.is_tensor(b_) and s_.shape != b_.shape for s_, b_ in zip(self._static_in, batch)):
             return self._eager_step(batch)       # odd-sized batch (e.g. a ragged last one): graphs are shape-specific
+        safe = getattr(self.optimizer, "graph_safe", None)
+        if safe is not None and not self._graphs and not safe():
+            import warnings
+            warnings.warn(f"{type(self.optimizer).__name__} is not on its graph-capturable path for these parameters; "
+                          f"running the step eagerly")
+            self.use_graph = False
+            return self._eager_step(batch)
         static = self._copy_in(batch)
         from ..ops import _lib
         if kind not in self._graphs:
@@ -169,7 +187,11 @@ class Trainer:
             n0 = _lib.LAUNCHES.count
             with torch.cuda.graph(g):
                 out = self._eager_step(static)
-            self._graphs[kind] = (g, out, _lib.LAUNCHES.count - n0)     # native launches recorded in this graph
+            n_native = _lib.LAUNCHES.count - n0                         # native launches recorded in this graph
+            self._graphs[kind] = (g, out, n_native)
+            # capture only records: run the step that was just captured, so this batch is not dropped and `out` holds
+            # real values (the optimizer's Python-side counters already advanced while capturing)
+            g.replay()
             return out
         g, out, n_native = self._graphs[kind]
         g.replay()

@@ -3,9 +3,14 @@
 Every model and optimizer in the framework calls the functions below.  On CPU tensors they
 run the pure-PyTorch oracle in :mod:`fdt.ops.reference`; on CUDA tensors they run the
 hand-written sm_100a kernels from ``csrc/`` (loaded by :mod:`fdt.ops._lib`) through the
-autograd wrappers in :mod:`fdt.ops.cuda_ops`.  There is no silent fallback on a GPU: if the
-native library is missing the call raises, unless ``FDT_FORCE_TORCH=1`` explicitly selects
-the oracle (used by the numerics tests to produce reference values on the same device).
+autograd wrappers in :mod:`fdt.ops.cuda_ops`.  If the native library is missing the call raises
+(``FDT_FORCE_TORCH=1`` explicitly selects the oracle; the numerics tests use it to produce
+reference values on the same device).  A shape the native kernels do not cover runs on the
+library path (cuDNN / cuBLAS / ATen) for that call only — never silently: every such call is
+counted per op in ``fdt.ops._lib.FALLBACKS``, the totals are printed at exit, and
+``FDT_STRICT=1`` turns the first one into a ``NativeCoverageError``.  The default training
+configurations of both models (ResNet-50 at 32x32, the 6-layer transformer up to L=512) take
+no fallback; ``tests/test_strict_native.py`` asserts that under ``FDT_STRICT=1``.
 """
 from __future__ import annotations
 

@@ -96,6 +96,20 @@ def sgd_momentum_(p, d, buf, lr, momentum, dampening, nesterov, first):
          int(bool(nesterov)), int(bool(first)))
 
 
+def sgd_momentum_dev_(p, d, buf, hyper, nesterov, first):
+    """hyper: device fp32 {lr, momentum, dampening} (graph-replay safe)."""
+    call("fdt_sgd_momentum_dev", p, d, buf, i64(p.numel()), hyper, int(bool(nesterov)), int(bool(first)))
+
+
+def clip_wd_(g, p, sq, max_norm, wd, skipped):
+    call("fdt_clip_wd", g, p, i64(g.numel()), sq, float(max_norm if max_norm is not None else 0.0), float(wd), skipped)
+
+
+def madgrad_dev_(p, g, v, s, x0, hyper, decay, eps, mirror, tick=True):
+    call("fdt_madgrad_dev", p, g, v, s, x0, i64(p.numel()), hyper, float(decay), float(eps), int(bool(mirror)), int(bool(tick)),
+         launches=2 if tick else 1)
+
+
 def madgrad_(p, g, v, s, x0, lamb, ck, decay, eps, mirror):
     call("fdt_madgrad", p, g, v, s, x0, i64(p.numel()), float(lamb), float(ck), float(decay), float(eps), int(mirror))
 
@@ -152,6 +166,7 @@ def _conv_fwd(x, w16, stride, padding, sums=None, keep=None):
             y = gemm_sm100.conv_fwd_im2col(x, w16, stride, padding, sums, keep)
         if y is not None:
             return y, sums is not None
+    _lib.note_fallback("conv_fwd", f"cuDNN F.conv2d for x{tuple(x.shape)} w{tuple(w16.shape)} stride {stride}")
     return F.conv2d(x, w16, stride=stride, padding=padding), False
 
 
@@ -248,6 +263,7 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
                 need_dw, dw = False, None
     if (need_dx and dx is None) or (need_dw and dw is None):
         mask = [need_dx and dx is None, need_dw and dw is None, False]
+        _lib.note_fallback("conv_bwd", f"cuDNN convolution_backward (dx={mask[0]}, dw={mask[1]}) for x{tuple(x.shape)} w{tuple(w_shape)}")
         rdx, rdw, _ = torch.ops.aten.convolution_backward(dy, x, w16, None, [stride, stride], [padding, padding],
                                                           [1, 1], False, [0, 0], 1, mask)
         dx = rdx if dx is None else dx
@@ -377,6 +393,7 @@ class _PoolFC(torch.autograd.Function):
 def pool_fc(x, weight, bias):
     """[N, C, H, W] bf16 NHWC → fp32 logits: global average pool + Linear in one kernel each way."""
     if weight.shape[0] > 32 or weight.shape[1] * 4 > 48 * 1024:
+        _lib.note_fallback("pool_fc", f"ATen mean + cuBLAS linear for {tuple(weight.shape)} (native: <= 32 classes, <= 12288 channels)")
         return F.linear(x.float().mean(dim=(2, 3)), weight, bias)
     return _PoolFC.apply(x, weight, bias)
 
@@ -428,6 +445,7 @@ def mixup_cross_entropy(logits, y_a, y_b, lam):
     if not torch.is_tensor(lam):
         lam = torch.tensor([float(lam)], device=logits.device)
     if lam.requires_grad or logits.shape[1] > 32:
+        _lib.note_fallback("mixup_cross_entropy", "ATen log_softmax path (learnable lambda or > 32 classes)")
         return ref.mixup_cross_entropy(logits, y_a, y_b, lam)       # learnable λ: differentiable path
     return _MixupCE.apply(logits, y_a, y_b, lam)
 
@@ -461,6 +479,7 @@ class _LayerNorm(torch.autograd.Function):
 
 def layernorm_ref(x, a_2, b_2, eps):
     if x.shape[-1] not in (128, 256, 512, 1024):
+        _lib.note_fallback("layernorm", f"ATen ops for D={x.shape[-1]} (native: 128/256/512/1024)")
         return ref.layernorm_ref(x, a_2, b_2, eps)
     return _LayerNorm.apply(x, a_2, b_2, eps)
 
@@ -506,6 +525,7 @@ def linear(x, weight, bias, act, drop_p=0.0):
         out = gemm_sm100.linear(x, weight, bias, act, drop_p)
         if out is not None:
             return out
+    _lib.note_fallback("linear", f"cuBLAS for x[..., {x.shape[-1]}] -> {weight.shape[0]} (native: K, N multiples of 64)")
     out = _LinearLib.apply(x, weight, bias, act)
     return F.dropout(out, drop_p, True) if drop_p > 0 else out
 
@@ -516,6 +536,7 @@ def attention(q, k, v, key_mask, dropout_p, training, mask_compat):
         out = gemm_sm100.attention(q, k, v, key_mask, dropout_p if training else 0.0, mask_compat)
         if out is not None:
             return out
+    _lib.note_fallback("attention", f"SDPA / ATen for q{tuple(q.shape)} (native: d_head 64, L <= 512)")
     if mask_compat:
         return ref.attention(q, k, v, key_mask, dropout_p, training, True)
     m = None if key_mask is None else (key_mask != 0)[:, None, None, :]

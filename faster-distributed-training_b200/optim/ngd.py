@@ -445,6 +445,8 @@ class NGD(Optimizer):
         super().__init__(params, defaults)
         self._groups: Dict[int, List[_ShapeGroup]] = {}
         self._lr_tensors: Dict[int, torch.Tensor] = {}
+        self._hyper_host: Dict[int, Tuple[float, float, float]] = {}
+        self._wd_done = False
         self.capturable = False
 
     # ------------------------------------------------------------------ grouping
@@ -490,24 +492,67 @@ class NGD(Optimizer):
             fb.t += 1
 
     def set_capturable(self, flag: bool = True):
-        """Keep the learning rate in a device scalar so a captured CUDA graph sees LR changes."""
+        """Keep lr / momentum / dampening in device scalars so a captured CUDA graph follows their schedules
+        (MultiStepLR, OneCycleLR with ``cycle_momentum``) without re-capture."""
         self.capturable = flag
+
+    @staticmethod
+    def _hyper_values(group) -> Tuple[float, float, float]:
+        return (float(group["lr"]), float(group["momentum"]), float(group["dampening"]))
+
+    def _hyper(self, gi: int, group, device) -> torch.Tensor:
+        """Device triple {lr, momentum, dampening} of a param group, created WITH the current values (a zero-initialised
+        scalar would turn the first step after construction / ``load_state_dict`` into a no-op)."""
+        t = self._lr_tensors.get(gi)
+        if t is None or t.device != device:
+            vals = self._hyper_values(group)
+            t = torch.tensor(vals, dtype=torch.float32, device=device)
+            self._lr_tensors[gi] = t
+            self._hyper_host[gi] = vals
+        return t
 
     def _lr(self, gi: int, group, device):
         if not self.capturable:
             return group["lr"]
-        t = self._lr_tensors.get(gi)
-        if t is None or t.device != device:
-            t = torch.zeros((), dtype=torch.float32, device=device)
-            self._lr_tensors[gi] = t
-        return t
+        return self._hyper(gi, group, device)[0]
 
     def sync_lr(self):
-        """Copy each group's python ``lr`` into its device scalar (call outside graph replay)."""
+        """Copy each group's python ``lr`` / ``momentum`` / ``dampening`` into its device triple when they changed
+        (call outside graph replay; a no-op while a stream is capturing)."""
         for gi, group in enumerate(self.param_groups):
             t = self._lr_tensors.get(gi)
-            if torch.is_tensor(t):
-                t.fill_(float(group["lr"]))
+            if not torch.is_tensor(t):
+                continue
+            vals = self._hyper_values(group)
+            if self._hyper_host.get(gi) != vals:
+                if t.is_cuda and torch.cuda.is_current_stream_capturing():
+                    continue
+                t.copy_(torch.tensor(vals, dtype=torch.float32))
+                self._hyper_host[gi] = vals
+
+    def fused_clip_wd(self, sq: torch.Tensor, max_norm: Optional[float], skipped: Optional[torch.Tensor]) -> bool:
+        """Global-norm clip + non-finite guard + weight decay over the flat gradient range in ONE kernel,
+        called by the Trainer between the gradient reduction and :meth:`step`.  Returns False (nothing done) when the
+        parameters are not flat-backed or not on the native path; the caller then clips separately."""
+        spans = []
+        for gi, group in enumerate(self.param_groups):
+            sgs = self._shape_groups(gi, group)
+            span = self._flat_span(gi, sgs)
+            if span is None:
+                if any(sg.flat_owner is not None for sg in sgs):
+                    return False
+                continue
+            spans.append((span, float(group["weight_decay"])))
+        if not spans or not spans[0][0][0].grad_flat.is_cuda:
+            return False
+        from .. import ops
+        if not ops.use_native(spans[0][0][0].grad_flat):
+            return False
+        for (flat, lo, hi), wd in spans:
+            ops._cu().clip_wd_(flat.grad_flat[lo:hi], flat.param_flat[lo:hi], sq, max_norm, wd, skipped)
+            skipped = None                      # count a skipped step once
+        self._wd_done = True
+        return True
 
     # ------------------------------------------------------------------ step
     def _precondition_group(self, sg: _ShapeGroup, group, d_p: torch.Tensor, pending=None) -> torch.Tensor:
@@ -575,6 +620,8 @@ class NGD(Optimizer):
             with torch.enable_grad():
                 loss = closure()
         pending: List[FactorBatch] = []
+        self.sync_lr()
+        wd_done, self._wd_done = self._wd_done, False
         for gi, group in enumerate(self.param_groups):
             wd, mom, damp = group["weight_decay"], group["momentum"], group["dampening"]
             sgs = self._shape_groups(gi, group)
@@ -583,7 +630,7 @@ class NGD(Optimizer):
             if span is not None:
                 flat, lo, hi = span
                 gflat, pflat = flat.grad_flat[lo:hi], flat.param_flat[lo:hi]
-                if wd != 0:
+                if wd != 0 and not wd_done:
                     gflat.add_(pflat, alpha=wd)
             # Shape groups are independent of each other (each is a chain of small batched kernels that
             # cannot fill 148 SMs), so on CUDA they are spread over a few side streams: forked from and
@@ -658,12 +705,13 @@ class NGD(Optimizer):
         first = buf is None
         if first and mom != 0:
             buf = self._lr_tensors[key] = torch.zeros_like(gflat)
-        lr = self._lr(gi, group, pflat.device)
         if pflat.is_cuda:
             from .. import ops
             if ops.use_native(pflat):
-                ops._cu().sgd_momentum_(pflat, gflat, buf, lr, mom, damp, nesterov, first)
+                # lr, momentum and dampening are read from device memory: graph replays follow their schedules
+                ops._cu().sgd_momentum_dev_(pflat, gflat, buf, self._hyper(gi, group, pflat.device), nesterov, first)
                 return
+        lr = self._lr(gi, group, pflat.device)
         d_p = gflat
         if mom != 0:
             if first:
@@ -697,30 +745,51 @@ class NGD(Optimizer):
         return {"format": "fdt-ngd-v1", "groups": groups}
 
     def load_state_dict(self, state):
+        """Validate the whole state against this optimizer's parameters first, then install it — a mismatching state
+        (another optimizer, another rank's FSDP shard) raises ``ValueError`` and leaves the optimizer untouched."""
         if state.get("format") != "fdt-ngd-v1":
             raise ValueError("not an fdt NGD state dict")
+        if len(state["groups"]) != len(self.param_groups):
+            raise ValueError("parameter groups changed")
+        plan = []
         for gi, (group, entry) in enumerate(zip(self.param_groups, state["groups"])):
+            sgs = None
+            if entry["shape_groups"]:
+                # shape groups need gradients to exist to be discovered; build them from params
+                for p in group["params"]:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+                sgs = self._shape_groups(gi, group)
+                if len(sgs) != len(entry["shape_groups"]):
+                    raise ValueError("parameter set changed")
+                for sg, s in zip(sgs, entry["shape_groups"]):
+                    if tuple(s["shape"]) != sg.shape or s["n"] != len(sg.params):
+                        raise ValueError(f"shape group mismatch: saved {tuple(s['shape'])} x{s['n']}, have {sg.shape} x{len(sg.params)}")
+                    for axis, f in s["factors"].items():
+                        D = sg.shape[int(axis)]
+                        if f["W"].shape[0] != len(sg.params) or f["W"].shape[2] != D:
+                            raise ValueError("factor shape mismatch")
+            fm = entry.get("flat_momentum")
+            if fm is not None:
+                span = self._flat_span(gi, sgs) if sgs is not None else None
+                if span is not None and fm.numel() != span[2] - span[1]:
+                    raise ValueError(f"flat momentum has {fm.numel()} elements, this rank's span has {span[2] - span[1]}")
+            plan.append((gi, group, entry, sgs))
+        for gi, group, entry, sgs in plan:
             for k, v in entry.items():
                 if k not in ("shape_groups", "flat_momentum"):
                     group[k] = v
             if entry.get("flat_momentum") is not None:
                 dev = group["params"][0].device
                 self._lr_tensors[("mom", gi)] = entry["flat_momentum"].to(dev)
-            if not entry["shape_groups"]:
+            if sgs is None:
                 continue                       # saved before the first step: nothing to restore
-            # shape groups need gradients to exist to be discovered; build them from params
-            for p in group["params"]:
-                if p.grad is None:
-                    p.grad = torch.zeros_like(p)
-            sgs = self._shape_groups(gi, group)
-            assert len(sgs) == len(entry["shape_groups"]), "parameter set changed"
             for sg, s in zip(sgs, entry["shape_groups"]):
-                assert tuple(s["shape"]) == sg.shape and s["n"] == len(sg.params)
                 dev, dt = sg.params[0].device, sg.params[0].dtype
                 sg.momentum = None if s["momentum"] is None else s["momentum"].to(dev, dt)
                 sg.factors = {}
                 for axis, f in s["factors"].items():
-                    D = sg.shape[axis]
+                    D = sg.shape[int(axis)]
                     N = sg.params[0].numel() // D
                     fb = FactorBatch(len(sg.params), N, D, group["alpha"], group["rank"],
                                      group["update_period"], group["eta"], dt, dev)

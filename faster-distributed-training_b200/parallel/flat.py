@@ -261,6 +261,22 @@ class FlatParameters:
         hi = max(self._index[i][0].offset + (self._index[i][1] + 1) * self._index[i][0].numel for i in idxs)
         return lo, hi
 
+    @staticmethod
+    def common_span(params) -> Optional[Tuple["FlatParameters", int, int]]:
+        """(flat, lo, hi) when ``params`` all live in ONE FlatParameters buffer and no foreign parameter sits inside
+        [lo, hi) — the range a flat optimizer kernel may sweep; None otherwise."""
+        flats = {id(getattr(p, "_fdt_flat", (None,))[0]) for p in params}
+        if len(flats) != 1 or not params or getattr(params[0], "_fdt_flat", None) is None:
+            return None
+        flat = params[0]._fdt_flat[0]
+        idxs = [p._fdt_flat[1] for p in params]
+        lo, hi = flat.span_of(idxs)
+        mine = set(idxs)
+        for i in range(len(flat.params)):
+            if i not in mine and lo <= flat.span_of([i])[0] < hi:
+                return None
+        return flat, lo, hi
+
     def rebind_grads(self):
         """Re-point ``p.grad`` at the flat buffer (after someone set grads to ``None``)."""
         for idx, p in enumerate(self.params):

@@ -52,6 +52,11 @@ class FullyShardedEngine(nn.Module):
         self._gathered = True
         self._stale = True
 
+    @property
+    def optimizer_state_sharded(self) -> bool:
+        """Each rank's optimizer holds only the tensors it owns (checkpoint sidecars are per rank)."""
+        return self.comm.world > 1
+
     def forward(self, *a, **kw):
         self.pre_forward()
         return self.module(*a, **kw)

@@ -112,6 +112,17 @@ int fdt_sgd_momentum(float* p, const float* d, float* buf, int64_t n, const floa
 int fdt_madgrad(float* p, const float* g, float* v, float* s, float* x0, int64_t n, float lamb, float ck,
                 float decay, float eps, int mirror, cudaStream_t st);
 int fdt_cast_bf16(const float* x, void* y_bf16, int64_t n, cudaStream_t st);
+/* CUDA-graph-safe variants: the schedule-dependent hyper-parameters live in device memory.
+ * fdt_sgd_momentum_dev: hyper = {lr, momentum, dampening}; buf may be NULL (no momentum).
+ * fdt_clip_wd: g = finite(sq) ? g*min(1, max_norm/(sqrt(sq)+1e-6)) + wd*p : 0  (clip_grad_norm_ + the NGD/SGD weight-decay
+ *   add of ngd_optimizer.py:478-479 in one pass; a non-finite norm zeroes the step and bumps *skipped).
+ * fdt_madgrad_dev: hyper = {lr + eps, k, momentum}; lamb = hyper[0]*sqrt(hyper[1]+1); tick != 0 advances k afterwards. */
+int fdt_sgd_momentum_dev(float* p, const float* d, float* buf, int64_t n, const float* hyper, int nesterov, int first,
+                         cudaStream_t st);
+int fdt_clip_wd(float* g, const float* p, int64_t n, const float* sq, float max_norm, float wd, float* skipped,
+                cudaStream_t st);
+int fdt_madgrad_dev(float* p, const float* g, float* v, float* s, float* x0, int64_t n, float* hyper, float decay,
+                    float eps, int mirror, int tick, cudaStream_t st);
 
 /* ---- tcgen05 / TMEM / TMA GEMM and convolution, csrc/gemm_sm100.cu, wgrad_sm100.cu, im2col.cu ------------
  * ref: F.conv2d / F.linear / convolution_backward call sites (resnet.py:21-34,83,108,204,221; transformer.py:168-176,213-226) */
@@ -130,6 +141,9 @@ int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int 
 /* dw[N][K] (fp32) += alpha * dY[M,N]^T · X[M,K] */
 int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, float alpha, int multicast,
                      cudaStream_t st);
+/* per-step operand layouts of the data-gradient GEMMs (transposed / tap-rotated bf16 weights) for every layer in one launch.
+ * descs: `count` 32-byte device records {const bf16* src; bf16* dst; int O, T, I, mode}.  csrc/weight_prep.cu */
+int fdt_dgrad_weights(const void* descs, int count, cudaStream_t st);
 /* explicit im2col / col2im (strided convs, the 3-channel stem): A[N*Ho*Wo, Kp] <-> x[N,H,W,C] */
 int fdt_im2col(const void* x, void* A, int N, int H, int W, int C, int k, int stride, int pad, int Ho, int Wo, int Kp,
                cudaStream_t st);
