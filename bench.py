@@ -140,6 +140,24 @@ def timed_steps(step_fn, steps, warmup, world, flush=True):
 
 
 # ----------------------------------------------------------------------------- our arm
+_HEAP = {}
+
+
+def _heap(device, world, rank):
+    """One NVLink symmetric heap per process, shared by every engine this run builds."""
+    if world == 1:
+        return None
+    if "heap" not in _HEAP:
+        try:
+            from fdt.parallel.symm import SymmetricHeap
+            _HEAP["heap"] = SymmetricHeap.create(device)
+        except Exception as e:
+            _HEAP["heap"] = None
+            if rank == 0:
+                print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {e}); NCCL collectives", file=sys.stderr)
+    return _HEAP["heap"]
+
+
 def build_fdt(model_name, bs, device, world, use_graph, mode):
     from fdt.cli import ResNetStep, TransformerStep
     from fdt.engine.trainer import Trainer
@@ -151,15 +169,10 @@ def build_fdt(model_name, bs, device, world, use_graph, mode):
     from fdt.parallel.fsdp import FullyShardedEngine
     comm = Communicator()
     allocator = None
-    if world > 1:
-        try:
-            from fdt.parallel.symm import SymmetricHeap
-            heap = SymmetricHeap.create(device)
-            comm.symm = heap
-            allocator = heap.alloc_f32
-        except Exception as e:
-            if comm.rank == 0:
-                print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {e}); NCCL collectives", file=sys.stderr)
+    heap = _heap(device, world, comm.rank)
+    if heap is not None:
+        comm.symm = heap
+        allocator = heap.alloc_f32
     torch.manual_seed(123456)
     if model_name == "resnet50":
         model = resnet50(10).to(device)
@@ -187,12 +200,13 @@ def make_host_batches(model_name, bs, n, seq_len, seed):
     return TensorBatchLoader(ds.tensors(), bs, shuffle=True, drop_last=True, pin=True, ring=max(n, 4), seed=seed)
 
 
-def run_fdt(args, rank, local, world):
+def measure_fdt(args, rank, local, world, model, mode, bs, steps, sample_clocks):
+    """Device-timed steps + the end-to-end loop for one (model, parallel mode).  Returns a dict."""
     from fdt import ops
     device = torch.device("cuda", local)
-    trainer, comm = build_fdt(args.model, args.bs, device, world, args.cuda_graph, args.mode)
-    loader = make_host_batches(args.model, args.bs, 8, args.seq_len, seed=rank)
-    host_batches = list(iter(loader))
+    trainer, comm = build_fdt(model, bs, device, world, args.cuda_graph, mode)
+    loader = make_host_batches(model, bs, 8, args.seq_len, seed=rank)
+    host_batches = [tuple(b) for b in iter(loader)]
     dev_batches = [tuple(t.to(device) for t in b) for b in host_batches]
     launches = ops.launch_counter()
 
@@ -205,11 +219,11 @@ def run_fdt(args, rank, local, world):
     for i in range(pre):
         step_dev(i)
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and sample_clocks:
         sampler.start()
     l0 = launches.count
-    ms, per = timed_steps(step_dev, args.steps, warm, world)
-    n_launch = launches.count - l0
+    ms, per = timed_steps(step_dev, steps, warm, world)
+    n_launch = (launches.count - l0) * steps // (steps + warm)       # launches of the timed steps only
     # ---- end to end through the public API: pinned H2D every step, loss D2H every step
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
     h2d_bytes = sum(t.numel() * t.element_size() for t in host_batches[0])
@@ -226,26 +240,81 @@ def run_fdt(args, rank, local, world):
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     s.record()
-    for i in range(args.steps):
+    for i in range(steps):
         step_e2e(i)
     e.record()
     torch.cuda.synchronize()
     _ = float(loss_host[0])
-    wall_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    wall_ms = (time.perf_counter() - t0) * 1e3 / steps
     barrier_sync(world)
-    e2e_ms = max_over_ranks(max(s.elapsed_time(e) / args.steps, wall_ms), world)
-    clocks = sampler.stop() if rank == 0 else {}
-    return ms, per, e2e_ms, h2d_bytes, 4, n_launch, clocks, float(loss_host[0])
+    e2e_ms = max_over_ranks(max(s.elapsed_time(e) / steps, wall_ms), world)
+    clocks = sampler.stop() if (rank == 0 and sample_clocks) else {}
+    out = {"ms": ms, "per": per, "e2e_ms": e2e_ms, "h2d": h2d_bytes, "d2h": 4, "launches": n_launch, "clocks": clocks,
+           "last_loss": float(loss_host[0]), "graph": bool(trainer.use_graph), "steps": steps,
+           "sharded_step": bool(getattr(trainer.engine, "sharded", mode == "fsdp" and world > 1))}
+    del trainer, dev_batches
+    torch.cuda.empty_cache()
+    return out
+
+
+def _series(m, bs, world, unit):
+    gb = bs * world
+    return {"value": round(gb / (m["ms"] / 1e3), 2), "unit": unit, "ms_per_step": round(m["ms"], 4), "global_batch": gb,
+            "steps": m["steps"],
+            "e2e": {"value": round(gb / (m["e2e_ms"] / 1e3), 2), "unit": unit, "ms_per_step": round(m["e2e_ms"], 4),
+                    "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"]}}
+
+
+def fdt_extras(args, rank, local, world):
+    """The other series BASELINE.json names (transformer samples/s; FSDP), measured in the same process right after
+    the headline so they land in the driver's record: same timing rules, fewer steps."""
+    steps = max(3, min(args.steps, 10))
+    plan = [("transformer_ddp", "transformer", "ddp", 64)]
+    if world > 1:
+        plan += [("transformer_fsdp", "transformer", "fsdp", 64), ("resnet50_fsdp", "resnet50", "fsdp", 128)]
+    out = {}
+    for key, model, mode, bs in plan:
+        try:
+            m = measure_fdt(args, rank, local, world, model, mode, bs, steps, False)
+            out[key] = _series(m, bs, world, "img/s" if model == "resnet50" else "samples/s")
+            out[key]["parallelism"] = f"{mode}{world}"
+        except Exception as e:                      # an auxiliary series must never take the headline down
+            out[key] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    return out
 
 
 # ----------------------------------------------------------------------------- reference arm
-def run_reference(args, rank, local, world):
+def run_reference(args, rank, local, world, fair=False):
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.isfile(os.path.join(ref_dir, "ngd_optimizer.py")):
         return None, "baseline/_ref missing (run python baseline/install_ref.py where /root/reference is mounted)"
     sys.path.insert(0, os.path.join(ROOT, "baseline"))
     import run_ref
-    return run_ref.bench(args, rank, local, world, timed_steps, barrier_sync, max_over_ranks, ClockSampler), None
+    return run_ref.bench(args, rank, local, world, timed_steps, barrier_sync, max_over_ranks, ClockSampler, fair=fair), None
+
+
+def reference_extras(args, rank, local, world):
+    """Transformer on the reference arm, single GPU only (its multi-GPU path is FSDP with CPU offload and NGD on a
+    host-resident shard — minutes per step): ``ref_as_is`` and ``ref_fair`` (only the per-element Python loop of
+    MLPScratch.backward vectorised, see baseline/run_ref.py)."""
+    if world != 1:
+        return {}
+    import copy
+    out = {}
+    a = copy.copy(args)
+    a.model, a.bs, a.steps, a.warmup, a.no_clocks = "transformer", 64, 3, 3, True
+    for key, fair in (("transformer_ref_as_is", False), ("transformer_ref_fair", True)):
+        try:
+            res, why = run_reference(a, rank, local, world, fair=fair)
+            if res is None:
+                out[key] = {"unavailable": why}
+                continue
+            ms, per, e2e_ms = res[0], res[1], res[2]
+            out[key] = {"value": round(64 / (ms / 1e3), 2), "unit": "samples/s", "ms_per_step": round(ms, 3), "steps": 3,
+                        "e2e": {"value": round(64 / (e2e_ms / 1e3), 2), "unit": "samples/s", "ms_per_step": round(e2e_ms, 3)}}
+        except Exception as e:
+            out[key] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    return out
 
 
 def main():
@@ -260,6 +329,7 @@ def main():
     ap.add_argument("--mode", default="ddp", choices=["ddp", "fsdp"])
     ap.add_argument("--cuda_graph", type=int, default=int(os.environ.get("FDT_BENCH_GRAPH", "1")))
     ap.add_argument("--no_settle", action="store_true")
+    ap.add_argument("--no_extra", action="store_true", help="skip the auxiliary series (transformer, FSDP) in `extra`")
     args = ap.parse_args()
     if args.bs is None:
         args.bs = 128 if args.model == "resnet50" else 64
@@ -281,9 +351,16 @@ def main():
                 print(json.dumps({"impl": "reference", "unavailable": why}))
             return 0
         ms, per, e2e_ms, h2d, d2h, n_launch, clocks, last_loss, dtype = res
+        impl_detail = {"cuda_graph": False, "loop": "reference recipe (autocast fp16 + GradScaler + clip + NGD), stock DDP/FSDP"}
+        extra = {} if (args.no_extra or args.model != "resnet50") else reference_extras(args, rank, local, world)
     else:
-        ms, per, e2e_ms, h2d, d2h, n_launch, clocks, last_loss = run_fdt(args, rank, local, world)
+        m = measure_fdt(args, rank, local, world, args.model, args.mode, args.bs, args.steps, True)
+        ms, per, e2e_ms, h2d, d2h, n_launch, clocks, last_loss = (m["ms"], m["per"], m["e2e_ms"], m["h2d"], m["d2h"],
+                                                                   m["launches"], m["clocks"], m["last_loss"])
         dtype = "bf16"
+        impl_detail = {"cuda_graph": m["graph"], "sharded_optimizer_step": m["sharded_step"],
+                       "collectives": "in-kernel NVLS/P2P over symmetric memory" if _HEAP.get("heap") is not None else "none (1 GPU)" if world == 1 else "NCCL"}
+        extra = {} if (args.no_extra or args.model != "resnet50" or args.mode != "ddp") else fdt_extras(args, rank, local, world)
     gb = args.bs * world
     value = gb / (ms / 1e3)
     rec = {
@@ -295,12 +372,13 @@ def main():
         "config": {"model": "resnet50-cifar (FusedConvBN variant)" if args.model == "resnet50" else "transformer-6L-d512-h8 classifier",
                    "global_batch": gb, "per_gpu_batch": args.bs, "seq_len": args.seq_len if args.model == "transformer" else None,
                    "parallelism": f"{args.mode}{world}", "optimizer": "NGD(momentum 0.9) + mixup + clip 10",
-                   "cuda_graph": bool(args.cuda_graph) if args.impl == "fdt" else False,
                    "l2": "256 MB flush write between timed steps; per-step working set >> 126 MB L2"},
+        "impl_detail": impl_detail,
         "e2e": {"value": round(gb / (e2e_ms / 1e3), 2), "unit": "img/s" if args.model == "resnet50" else "samples/s",
                 "ms_per_step": round(e2e_ms, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": n_launch, "clocks": clocks, "last_loss": last_loss,
         "step_ms_min_max": [round(min(per), 4), round(max(per), 4)],
+        "extra": extra,
     }
     if rank == 0:
         print(json.dumps(rec))

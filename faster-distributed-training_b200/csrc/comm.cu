@@ -38,16 +38,17 @@ struct CommCtx {
     float* scratch[kMaxWorld];    // peer views of a small fp32 scratch (Σg² slots)
     float* mc;                    // multicast view of the data buffer (NVLS) or null
     int rank, world;
-    int pad0, pad1;
+    int sig_off, pad1;            // sig_off: first slot of this context's signal channel (collectives that may be in flight
+                                  // at the same time — e.g. on two streams — use disjoint channels)
 };
 
 __device__ __forceinline__ void block_barrier(const CommCtx& c, int base) {
     __syncthreads();
     if (threadIdx.x < c.world) {
         __threadfence_system();
-        uint32_t* remote = c.sig[threadIdx.x] + base + c.rank;
+        uint32_t* remote = c.sig[threadIdx.x] + c.sig_off + base + c.rank;
         while (atomicCAS_system(remote, 0u, 1u) != 0u) {}
-        uint32_t* local = c.sig[c.rank] + base + threadIdx.x;
+        uint32_t* local = c.sig[c.rank] + c.sig_off + base + threadIdx.x;
         while (atomicCAS_system(local, 1u, 0u) != 1u) {}
         __threadfence_system();
     }
@@ -281,6 +282,70 @@ FDT_API int fdt_comm_reduce_scatter_mean(const void* ctx, int64_t lo, int64_t hi
     const float scale = 1.f / c.world;
     if (use_multicast && c.mc) reduce_kernel<1, true><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
     else reduce_kernel<1, false><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// Bucketed form of the reduce-scatter for overlap with the backward pass: this rank reduces [lo, hi) — its own slice of
+// the bucket, which may be EMPTY and differs in length between ranks — with a grid of `blocks` CTAs that must be the same
+// on every rank (block b pairs with block b of the peers).  Σg² accumulates in the scratch slot across calls; read it once
+// with fdt_comm_take_scalar after the last bucket.
+FDT_API int fdt_comm_reduce_scatter_range(const void* ctx, int64_t lo, int64_t hi, int blocks, int use_multicast, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld || (lo % 4) || (hi % 4) || hi < lo || blocks < 1 || blocks > 64) return -1;
+    const float scale = 1.f / c.world;
+    if (use_multicast && c.mc) reduce_kernel<1, true><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    else reduce_kernel<1, false><<<blocks, kBlock, 0, st>>>(c, lo, hi, scale);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// Range form of the all-gather (+ bf16 shadow): every rank pulls [lo_r, hi_r) — absolute element offsets in the flat
+// buffer, owned by rank r, the same table on every rank — from each owner.  Regions need not have equal length (ranks own
+// whole tensors), and a table can describe the parameters of ONE model stage, so that the next stage's gather overlaps this
+// stage's forward pass.
+__global__ void __launch_bounds__(kBlock)
+all_gather_range_kernel(const CommCtx c, const int64_t* __restrict__ sub, __nv_bfloat16* __restrict__ shadow) {
+    const int nb = gridDim.x;
+    block_barrier(c, blockIdx.x * c.world);
+    float* mine = c.buf[c.rank];
+    constexpr int U = 8;
+    for (int k = 0; k < c.world; ++k) {
+        const int r = (c.rank + k) % c.world;
+        const int64_t lo = sub[2 * r], hi = sub[2 * r + 1];
+        const int64_t len = hi - lo;
+        const int64_t per = ((len / 4 + nb - 1) / nb) * 4;
+        const int64_t s0 = lo + min(len, per * blockIdx.x), s1 = lo + min(len, per * blockIdx.x + per);
+        const float* src = c.buf[r];
+        for (int64_t i = s0 + threadIdx.x * 4; i < s1; i += (int64_t)kBlock * 4 * U) {
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t e = i + (int64_t)u * kBlock * 4;
+                if (e < s1) v[u] = ld_cg(src + e);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t e = i + (int64_t)u * kBlock * 4;
+                if (e < s1) {
+                    if (r != c.rank) st_cg(mine + e, v[u]);
+                    if (shadow) {
+                        __nv_bfloat162 h0 = __floats2bfloat162_rn(v[u].x, v[u].y), h1 = __floats2bfloat162_rn(v[u].z, v[u].w);
+                        *reinterpret_cast<uint2*>(shadow + e) =
+                            make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+                    }
+                }
+            }
+        }
+    }
+    block_barrier(c, (nb + blockIdx.x) * c.world);
+}
+
+// sub: DEVICE pointer to 2*world int64 {lo_r, hi_r} (multiples of 4, absolute element offsets; hi_r == lo_r allowed).
+FDT_API int fdt_comm_all_gather_range(const void* ctx, const int64_t* sub, void* shadow_bf16, int blocks, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld || !sub || blocks < 1 || blocks > 128) return -1;
+    all_gather_range_kernel<<<blocks, kBlock, 0, st>>>(c, sub, (__nv_bfloat16*)shadow_bf16);
     FDT_CHECK_LAUNCH();
     return 0;
 }

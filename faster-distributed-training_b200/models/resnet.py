@@ -201,12 +201,39 @@ class ResNet(nn.Module):
                     if hasattr(m, "_fdt_arena_off"):
                         m._fdt_arena = (self._bn_arena, m._fdt_arena_off)
             self._bn_arena.begin(self._bn_total, x.device)     # also in eval: the FusedConvBN units always use batch statistics
+        # Stage boundaries for the parallel engines: forward "stage s" = the s-th entry of STAGES (its parameters may still
+        # be arriving — all-gather overlapped with the previous stage's compute); gradient "bucket k" = the stage whose
+        # gradients are final once backward crosses the boundary in front of it (reduce-scatter overlapped with the rest
+        # of backward).  Both calls are no-ops without an engine that asks for them.
+        ops.stage_begin(self, 0)
         o = self.conv1[0](x, act="celu")
         o = self.conv2_x(o)
+        ops.stage_begin(self, 1)
+        o = ops.bucket_boundary(o, self, 2)
         o = self.conv3_x(o)
+        ops.stage_begin(self, 2)
+        o = ops.bucket_boundary(o, self, 1)
         o = self.conv4_x(o)
+        ops.stage_begin(self, 3)
+        o = ops.bucket_boundary(o, self, 0)
         o = self.conv5_x(o)
         return ops.pool_fc(o, self.fc.weight, self.fc.bias)
+
+    # forward stages, in order; backward finishes them in reverse (gradient bucket k = stage NUM_STAGES-1-k)
+    STAGES = (("conv1", "conv2_x"), ("conv3_x",), ("conv4_x",), ("conv5_x", "fc"))
+
+    def stage_of(self, p) -> int:
+        """Index of the forward stage that owns parameter ``p``."""
+        if not hasattr(self, "_stage_index"):
+            self._stage_index = {}
+            for si, names in enumerate(self.STAGES):
+                for n in names:
+                    for q in getattr(self, n).parameters():
+                        self._stage_index[id(q)] = si
+        return self._stage_index[id(p)]
+
+    def grad_bucket_of(self, p) -> int:
+        return len(self.STAGES) - 1 - self.stage_of(p)
 
 
 def resnet18(num_classes=10):

@@ -188,12 +188,44 @@ class Transformer(nn.Module):
             if p.dim() > 1:
                 nn.init.xavier_uniform_(p)
 
+    # Forward stages for the parallel engines (see fdt.ops.stage_begin / bucket_boundary): embeddings | first half of the
+    # encoder | second half + pooler + classifier.  Backward finishes them in reverse; the (large) embedding gradient is
+    # final only at the very end of backward.
+    NUM_STAGES = 3
+
+    def stage_of(self, p) -> int:
+        if not hasattr(self, "_stage_index"):
+            half = self.n_layers // 2
+            idx = {}
+            for q in self.input_embeddings.parameters():
+                idx[id(q)] = 0
+            for li in range(self.n_layers):
+                for m in (self.sublayer_attention[li], self.sublayer_ffn[li]):
+                    for q in m.parameters():
+                        idx[id(q)] = 1 if li < half else 2
+            for m in (self.pooler, self.classifier):
+                for q in m.parameters():
+                    idx[id(q)] = 2
+            self._stage_index = idx
+        return self._stage_index[id(p)]
+
+    def grad_bucket_of(self, p) -> int:
+        return self.NUM_STAGES - 1 - self.stage_of(p)
+
     def encode(self, tokens, token_types, key_mask=None):
+        ops.stage_begin(self, 0)
         emb = self.input_embeddings(tokens, token_types)
         pe = self.input_encodings.table(emb, emb.size(1))
         # Q12: embeddings are counted twice, x = emb + dropout(emb + pe)
         x = ops.dropout_add(emb + pe, emb, self.input_encodings.p, self.training)
-        for att, ffn in zip(self.sublayer_attention, self.sublayer_ffn):
+        half = self.n_layers // 2
+        for li, (att, ffn) in enumerate(zip(self.sublayer_attention, self.sublayer_ffn)):
+            if li == 0:
+                ops.stage_begin(self, 1)
+                x = ops.bucket_boundary(x, self, 1)
+            if li == half:
+                ops.stage_begin(self, 2)
+                x = ops.bucket_boundary(x, self, 0)
             x = ffn(att(x, key_mask))
         x = self.pooler(x)
         if self.training:

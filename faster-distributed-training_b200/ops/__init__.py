@@ -116,3 +116,36 @@ def dropout_add(x, residual, p, training):
     if use_native(x):
         return _cu().dropout_add(x, residual, p, training)
     return ref.dropout_add(x, residual, p, training)
+
+
+class _BucketBoundary(torch.autograd.Function):
+    """Identity whose backward tells the parallel engine that a phase of the backward pass is over."""
+
+    @staticmethod
+    def forward(ctx, x, cb, k):
+        ctx.cb, ctx.k = cb, k
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.cb(ctx.k)
+        return g, None, None
+
+
+def bucket_boundary(x, owner, k: int):
+    """Mark the point of a model's forward pass after which only parameters of gradient buckets < ``k``... are used:
+    when backward crosses it, every kernel producing gradients of bucket ``k`` has been enqueued, and the engine
+    wrapping ``owner`` (it installs ``owner._fdt_bucket_cb``) may start that bucket's reduce-scatter on its
+    communication stream while the rest of backward runs.  A no-op without an engine (or without grad)."""
+    cb = getattr(owner, "_fdt_bucket_cb", None)
+    if cb is None or not torch.is_grad_enabled() or not x.requires_grad:
+        return x
+    return _BucketBoundary.apply(x, cb, k)
+
+
+def stage_begin(owner, k: int):
+    """Forward-pass counterpart: parameters of stage ``k`` are about to be used (the engine may still be gathering them on
+    its communication stream; ``owner._fdt_stage_cb`` makes the compute stream wait for that gather)."""
+    cb = getattr(owner, "_fdt_stage_cb", None)
+    if cb is not None:
+        cb(k)

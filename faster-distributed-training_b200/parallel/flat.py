@@ -52,7 +52,9 @@ class FlatParameters:
                  allocator: Optional[Callable[[int], torch.Tensor]] = None,
                  world_size: int = 1, shard: bool = False,
                  param_allocator: Optional[Callable[[int], torch.Tensor]] = None,
-                 fused_first: Optional[Callable[[torch.nn.Parameter], bool]] = None):
+                 fused_first: Optional[Callable[[torch.nn.Parameter], bool]] = None,
+                 bucket_of: Optional[Callable[[torch.nn.Parameter], int]] = None,
+                 equal_regions: bool = True):
         params = [p for p in params if p.requires_grad]
         assert params, "no trainable parameters"
         device = device or params[0].device
@@ -97,6 +99,14 @@ class FlatParameters:
                 owners[s] = r
                 load[r] += _round_up(len(ps) * ps[0].numel(), ALIGN)
 
+        # Gradient buckets (sharded layout only): ``bucket_of(p)`` = index of the backward phase in which p's gradient
+        # becomes final (0 = first to finish).  A shape group is ready with its LAST member; inside every rank's region the
+        # groups are laid out bucket by bucket, so "bucket k" is one contiguous sub-range per rank —
+        # ``bucket_ranges[k][r]`` — that a reduce-scatter can take as soon as phase k of the backward pass is over.
+        gbucket: Dict[Tuple, int] = {s: (max(int(bucket_of(p)) for p in ps) if bucket_of is not None else 0)
+                                     for s, ps in buckets.items()}
+        self.num_buckets = (max(gbucket.values()) + 1) if gbucket else 1
+        self.bucket_ranges: List[List[Tuple[int, int]]] = []
         self.groups: List[ShapeGroupLayout] = []
         self.region: List[Tuple[int, int]] = []   # per rank (start, end) element range
         off = 0
@@ -105,17 +115,29 @@ class FlatParameters:
             for r in range(world_size):
                 sz = sum(_round_up(len(ps) * ps[0].numel(), ALIGN) for s, ps in buckets.items() if owners[s] == r)
                 sizes.append(sz)
+            # equal_regions: every region padded to the largest one (what all_gather_into_tensor / reduce_scatter_tensor
+            # and the single-launch native kernels need).  Otherwise regions are as long as what their rank owns — the
+            # range collectives take per-rank bounds — so one very large tensor (a 30522 x 512 embedding) does not inflate
+            # the buffers by world x its size.
             region_size = _round_up(max(sizes), ALIGN)
+            self.bucket_ranges = [[(0, 0)] * world_size for _ in range(self.num_buckets)]
+            starts = [r * region_size for r in range(world_size)]
+            if not equal_regions:
+                starts = [sum(sizes[:r]) for r in range(world_size)]
             for r in range(world_size):
-                off = r * region_size
-                self.region.append((off, off + region_size))
-                for s, ps in buckets.items():
-                    if owners[s] != r:
-                        continue
-                    g = ShapeGroupLayout(s, ps, off, r)
-                    self.groups.append(g)
-                    off += _round_up(g.size, ALIGN)
-            total = world_size * region_size
+                off = starts[r]
+                self.region.append((off, off + (region_size if equal_regions else sizes[r])))
+                for k in range(self.num_buckets):
+                    lo = off
+                    for s, ps in buckets.items():
+                        if owners[s] != r or gbucket[s] != k:
+                            continue
+                        g = ShapeGroupLayout(s, ps, off, r)
+                        g.bucket = k
+                        self.groups.append(g)
+                        off += _round_up(g.size, ALIGN)
+                    self.bucket_ranges[k][r] = (lo, off)
+            total = world_size * region_size if equal_regions else _round_up(sum(sizes), ALIGN)
         else:
             for gi, (s, ps) in enumerate(buckets.items()):
                 g = ShapeGroupLayout(s, ps, off, 0)

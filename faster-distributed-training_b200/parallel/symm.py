@@ -27,12 +27,15 @@ import torch.distributed as dist
 from ..ops import _lib
 
 MAX_WORLD = 8
+SIG_SLOTS = 2 * 128 * MAX_WORLD      # one channel: start + end barrier slots of up to 128 blocks x 8 ranks
+SIG_CHANNELS = 4                     # 0: stand-alone collectives on the main stream; 1: bucketed collectives on the
+                                     # communication stream (overlapping forward / backward); 2-3: free
 
 
 class _CommCtx(ctypes.Structure):
     _fields_ = [("buf", ctypes.c_void_p * MAX_WORLD), ("sig", ctypes.c_void_p * MAX_WORLD),
                 ("scratch", ctypes.c_void_p * MAX_WORLD), ("mc", ctypes.c_void_p),
-                ("rank", ctypes.c_int), ("world", ctypes.c_int), ("pad0", ctypes.c_int), ("pad1", ctypes.c_int)]
+                ("rank", ctypes.c_int), ("world", ctypes.c_int), ("sig_off", ctypes.c_int), ("pad1", ctypes.c_int)]
 
 
 class SymmetricHeap:
@@ -48,7 +51,7 @@ class SymmetricHeap:
             symm_mem.enable_symm_mem_for_group(self.group.group_name)
         except Exception:
             pass
-        self.sig = symm_mem.empty(2 * 64 * MAX_WORLD * 2, dtype=torch.int32, device=self.device)
+        self.sig = symm_mem.empty(SIG_SLOTS * SIG_CHANNELS, dtype=torch.int32, device=self.device)
         self.sig.zero_()
         self.scratch = symm_mem.empty(64, dtype=torch.float32, device=self.device)
         self.scratch.zero_()
@@ -70,6 +73,12 @@ class SymmetricHeap:
 
     # ------------------------------------------------------------------ allocation
     def alloc_f32(self, numel: int) -> torch.Tensor:
+        """A zero-filled fp32 buffer of ``numel`` elements that every rank can address on every peer.  The allocation is
+        rounded up to a multiple of 4 x world elements (the kernels move 16-byte vectors and cut the buffer into one
+        chunk per rank); the returned tensor is the first ``numel`` elements, and the collectives run over the padded
+        length — the padding stays zero — so callers may use any length."""
+        want = numel
+        numel = (numel + 4 * self.world - 1) // (4 * self.world) * (4 * self.world)
         t = self.symm_mem.empty(numel, dtype=torch.float32, device=self.device)
         t.zero_()
         torch.cuda.synchronize(self.device)
@@ -87,7 +96,14 @@ class SymmetricHeap:
         ctx.mc = mc
         ctx.rank, ctx.world = self.rank, self.world
         self.bufs[t.data_ptr()] = (t, hdl, ctx)
-        return t
+        return t if want == numel else t[:want]
+
+    def free(self, t: torch.Tensor):
+        """Drop the heap's reference to a buffer from :meth:`alloc_f32` (the memory goes back once the caller's
+        references are gone too).  Collective in spirit: every rank should free the same buffers."""
+        self.bufs.pop(t.data_ptr(), None)
+        for key in [k for k in getattr(self, "_chan", {}) if k[0] == t.data_ptr()]:
+            self._chan.pop(key)
 
     def sub_ctx(self, t: torch.Tensor, offset: int) -> _CommCtx:
         """Context whose data pointers start ``offset`` elements into buffer ``t`` (a tail range)."""
@@ -100,6 +116,37 @@ class SymmetricHeap:
         c.mc = (base.mc + 4 * offset) if base.mc else 0
         c.rank, c.world = self.rank, self.world
         return c
+
+    def channel_ctx(self, t: torch.Tensor, channel: int) -> _CommCtx:
+        """The buffer's context on another signal channel: collectives on different channels may be in flight at the
+        same time (different streams) without touching each other's barrier flags."""
+        assert 0 <= channel < SIG_CHANNELS
+        key = (t.data_ptr(), channel)
+        c = self._chan.get(key) if hasattr(self, "_chan") else None
+        if c is None:
+            if not hasattr(self, "_chan"):
+                self._chan = {}
+            base = self._ctx(t)
+            c = _CommCtx()
+            ctypes.memmove(ctypes.byref(c), ctypes.byref(base), ctypes.sizeof(_CommCtx))
+            c.sig_off = channel * SIG_SLOTS
+            self._chan[key] = c
+        return c
+
+    def reduce_scatter_range_(self, flat: torch.Tensor, lo: int, hi: int, blocks: int, channel: int = 1):
+        """This rank's slice [lo, hi) of one gradient bucket (possibly empty); ``blocks`` is common to all ranks.
+        Σg² keeps accumulating until :meth:`take_sq`."""
+        _lib.call("fdt_comm_reduce_scatter_range", ctypes.byref(self.channel_ctx(flat, channel)), _lib.i64(lo), _lib.i64(hi),
+                  int(blocks), int(self.use_multicast))
+
+    def take_sq(self) -> torch.Tensor:
+        return self._take_sq()
+
+    def all_gather_range_(self, flat: torch.Tensor, sub_dev: torch.Tensor, shadow: Optional[torch.Tensor],
+                          blocks: int, channel: int = 1):
+        """Pull ``[sub_dev[2r], sub_dev[2r+1])`` (absolute element offsets, owned by rank r) from every owner, emitting
+        the bf16 shadow of the same elements.  ``sub_dev``: int64 device tensor, identical on all ranks."""
+        _lib.call("fdt_comm_all_gather_range", ctypes.byref(self.channel_ctx(flat, channel)), sub_dev, shadow, int(blocks))
 
     def multicast_addr(self, t: torch.Tensor) -> int:
         return int(self._ctx(t).mc or 0)
@@ -127,7 +174,8 @@ class SymmetricHeap:
     # ------------------------------------------------------------------ collectives
     def all_reduce_mean_(self, flat: torch.Tensor) -> torch.Tensor:
         ctx = self._ctx(flat)
-        _lib.call("fdt_comm_all_reduce_mean", ctypes.byref(ctx), _lib.i64(flat.numel()), int(self.use_multicast))
+        n = self.bufs[flat.data_ptr()][0].numel()       # padded allocation length (>= flat.numel(), padding is zero)
+        _lib.call("fdt_comm_all_reduce_mean", ctypes.byref(ctx), _lib.i64(n), int(self.use_multicast))
         self._take_sq()
         return flat
 

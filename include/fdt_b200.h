@@ -192,10 +192,15 @@ int fdt_ngd_small_axis(const float* X, const float* W, float* Xhat, float* sums,
 
 /* ---- in-kernel NVLink collectives over a symmetric heap, csrc/comm.cu -------------------------------------------
  * ref: DDP bucket all-reduce (resnet50_test.py:716), FSDP all-gather / reduce-scatter (transformer_test.py:387-392).
- * ctx: host pointer to {float* buf[8]; uint32_t* sig[8]; float* scratch[8]; float* mc; int rank, world, pad0, pad1;} */
+ * ctx: host pointer to {float* buf[8]; uint32_t* sig[8]; float* scratch[8]; float* mc; int rank, world, sig_off, pad1;} */
 int fdt_comm_all_reduce_mean(const void* ctx, int64_t n, int use_multicast, cudaStream_t st);
 int fdt_comm_reduce_scatter_mean(const void* ctx, int64_t lo, int64_t hi, int use_multicast, cudaStream_t st);
 int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16, int use_multicast, cudaStream_t st);
+/* bucketed forms for overlap with backward / forward: per-rank [lo, hi) (may be empty) with a grid size common to all ranks;
+ * per-owner range table `sub` (device, 2*world int64 {lo_r, hi_r}, absolute element offsets; regions may differ in length).  Σg² accumulates across
+ * fdt_comm_reduce_scatter_range calls until fdt_comm_take_scalar. */
+int fdt_comm_reduce_scatter_range(const void* ctx, int64_t lo, int64_t hi, int blocks, int use_multicast, cudaStream_t st);
+int fdt_comm_all_gather_range(const void* ctx, const int64_t* sub, void* shadow_bf16, int blocks, cudaStream_t st);
 int fdt_comm_barrier(const void* ctx, cudaStream_t st);
 int fdt_comm_take_scalar(float* slot, float* out, cudaStream_t st);
 int fdt_comm_mc_red_add(float* dst_mc, const float* src, int64_t n, float alpha, cudaStream_t st);
