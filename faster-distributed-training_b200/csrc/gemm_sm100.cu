@@ -38,8 +38,17 @@ struct GemmParams {
     const float* bias;       // [N] or null
     float* sums;             // [2N] Σ, Σ² per column (atomics) or null
     int act;
-    // conv geometry (conv mode only)
-    int H, W, bh, bn, pad, kw, cpb;   // cpb = Cin / 64 (k-blocks per tap)
+    const __nv_bfloat16* addend;      // optional bf16 tensor added to the result before it is stored (same indexing as `out`):
+                                      // the other branch's gradient at a residual fork, so the sum needs no pass of its own
+    // conv geometry (conv mode only).  H, W, bh, bn describe the grid of OUTPUT pixels a tile row maps to
+    // (row -> (n, oh, ow)); the A tensor is addressed at (in_mul * oh + tap_dh, tap_dw + [0, W) * in_mul).
+    int H, W, bh, bn, cpb;            // cpb = channels-per-tap / 64 (k-blocks per tap)
+    int in_mul;                       // 1, or the convolution stride (the tensor map then carries element strides)
+    int ntaps;
+    int tap_dh[9], tap_dw[9], tap_k[9];   // per tap: A-coordinate offsets and first column of the tap in B's K dimension
+    // output mapping: omode 0 = row-major [M, N] (TMA store); 1 = "parity class" of a stride-2 data gradient: tile row
+    // (n, i, j) is pixel (n, 2i + oph, 2j + opw) of an [*, OH, OW, N] tensor (direct stores)
+    int omode, OH, OW, oph, opw;
 };
 
 // Column statistics (Σ, Σ² per output channel — the BatchNorm batch statistics of a conv output) are accumulated per
@@ -71,6 +80,8 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
     m_tile = b * kBand + r % rows;
     n_tile = r / rows;
 }
+
+__device__ __forceinline__ bool tma_out_any(const GemmParams& p) { return p.out != nullptr && p.omode == 0; }
 
 template <int BN, int kStages, bool kConv>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -129,12 +140,12 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
                     if (kConv) {
                         const int tap = kb / p.cpb, cb = kb - tap * p.cpb;
-                        const int r = tap / p.kw, sx = tap - r * p.kw;
-                        tma_load_4d(sA, &tmA, &full_bar[s], cb * BK, sx - p.pad, h0 + r - p.pad, n0);
+                        tma_load_4d(sA, &tmA, &full_bar[s], cb * BK, p.tap_dw[tap], p.in_mul * h0 + p.tap_dh[tap], n0);
+                        tma_load_2d(sB, &tmB, &full_bar[s], p.tap_k[tap] + cb * BK, n_tile * BN);
                     } else {
                         tma_load_2d(sA, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+                        tma_load_2d(sB, &tmB, &full_bar[s], kb * BK, n_tile * BN);
                     }
-                    tma_load_2d(sB, &tmB, &full_bar[s], kb * BK, n_tile * BN);
                 }
             }
         }
@@ -182,7 +193,15 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t tm = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
             const int row = m_tile * BM + q * 32 + lane;
             const bool row_ok = row < p.M;
-            if (p.out && t > 1) {
+            const bool tma_out = p.out && p.omode == 0;
+            size_t orow = (size_t)row;                              // row of `out` / `addend` this thread's row maps to
+            if (kConv && p.omode == 1 && row_ok) {
+                const int hw = p.H * p.W;
+                const int n = row / hw, rem = row - n * hw;
+                const int i = rem / p.W, j = rem - i * p.W;
+                orow = ((size_t)n * p.OH + 2 * i + p.oph) * p.OW + 2 * j + p.opw;
+            }
+            if (tma_out && t > 1) {
                 // this warpgroup's staging tile is still being read by its previous TMA store
                 if (threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
@@ -207,6 +226,16 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (p.act != ACT_NONE) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
+                }
+                if (p.addend && row_ok) {
+                    const __nv_bfloat16* ad = p.addend + orow * p.N + col0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        float f[8];
+                        unpack8(ld8(ad + j), f);
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) v[j + u] += f[u];
+                    }
                 }
                 if (p.sums) {
                     // per-column Σ and Σ² over the 32 rows of this warp: butterfly transpose-reduce —
@@ -235,7 +264,13 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
                     }
                 }
-                if (p.out) {
+                if (p.out && p.omode == 1) {
+                    if (row_ok) {
+                        __nv_bfloat16* o = p.out + orow * p.N + col0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) st8(o + j, pack8(v + j));
+                    }
+                } else if (p.out) {
                     // bf16 tile → shared memory in the 128B-swizzled layout of the output tensor map
                     uint8_t* atom = sC + (c >> 1) * 16384;
                     const int r_in = q * 32 + lane;
@@ -252,7 +287,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 }
             }
-            if (p.out) {
+            if (tma_out) {
                 fence_proxy_async();
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");          // the 4 warps of this warpgroup
                 if (threadIdx.x == leader) {
@@ -270,7 +305,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (v != 0.f) atomicAdd(p.sums + i, v);
             }
         }
-        if (p.out && threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (tma_out_any(p) && threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -313,11 +348,13 @@ bool encode_2d(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, 
                                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
-bool encode_nhwc(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, int bw, int bh, int bn) {
+// [Nb, H, W, C] bf16; the box covers bw x bh x bn PIXELS taken every `es`-th column / row (traversal stride: a strided
+// convolution reads every es-th input pixel; the box extent in tensor elements is then es x as large)
+bool encode_nhwc(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, int bw, int bh, int bn, int es = 1) {
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Nb};
     cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
+    cuuint32_t box[4] = {64, (cuuint32_t)(bw * es), (cuuint32_t)(bh * es), (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1, (cuuint32_t)es, (cuuint32_t)es, 1};
     CUresult r = cuTensorMapEncodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
                                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -353,35 +390,124 @@ int pick_bn(int M, int N) {
 
 }  // namespace
 
-// out[M,N] (bf16 and/or fp32) = act(A[M,K] · B[N,K]ᵀ + bias).  K % 64 == 0, N % 64 == 0, 16-byte aligned rows.
+// out[M,N] (bf16 and/or fp32) = act(A[M,K] · B[N,K]ᵀ + bias) [+ addend].  K % 64 == 0, N % 64 == 0, 16-byte aligned rows.
 // sums (optional, [2N], zeroed by the caller): per-column Σ and Σ² of the stored values.
-FDT_API int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out_f32, const float* bias, float* sums,
-                        int M, int N, int K, int act, cudaStream_t st) {
+// addend (optional, bf16 [M,N], may alias out_bf16): added before the store.
+FDT_API int fdt_gemm_nt_ex(const void* A, const void* B, void* out_bf16, float* out_f32, const float* bias, float* sums,
+                           const void* addend, int M, int N, int K, int act, cudaStream_t st) {
     if (M <= 0 || N % 64 || K % 64 || K <= 0) return -1;
     CUtensorMap tmA, tmB;
     const int BN = pick_bn(M, N);
     if (!encode_2d(&tmA, A, K, M, BK, BM) || !encode_2d(&tmB, B, K, N, BK, BN)) return -4;
     GemmParams p{};
     p.M = M; p.N = N; p.num_kb = K / BK; p.out = (__nv_bfloat16*)out_bf16; p.out_f32 = out_f32; p.bias = bias;
-    p.sums = sums; p.act = act;
+    p.sums = sums; p.act = act; p.addend = (const __nv_bfloat16*)addend;
     return BN == 128 ? launch<128, false>(tmA, tmB, p, st) : launch<64, false>(tmA, tmB, p, st);
 }
 
-// y[Nb,H,W,Cout] = conv(x[Nb,H,W,Cin], w[Cout,kh,kw,Cin]), stride 1, "same" padding (pad = kh/2), NHWC bf16.
-// Cin % 64 == 0, Cout % 64 == 0, W a power of two <= 128, H·W a multiple of the 128-pixel tile or a divisor of it.
-FDT_API int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int Nb, int H, int W, int Cin, int Cout,
-                         int ksize, int pad, cudaStream_t st) {
-    if (Cin % 64 || Cout % 64 || W > 128 || (W & (W - 1)) || (128 % W)) return -1;
-    int bh = 128 / W, bn = 1;
-    if (bh > H) { if (bh % H) return -1; bn = bh / H; bh = H; }
-    else if (H % bh) return -1;
-    const int M = Nb * H * W;
+FDT_API int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out_f32, const float* bias, float* sums,
+                        int M, int N, int K, int act, cudaStream_t st) {
+    return fdt_gemm_nt_ex(A, B, out_bf16, out_f32, bias, sums, nullptr, M, N, K, act, st);
+}
+
+namespace {
+// tile geometry of a conv-mode launch over an OH x OW grid of output pixels: 128 pixels = bh rows x OW (x bn images)
+bool tile_geom(int OH, int OW, int& bh, int& bn) {
+    if (OW > 128 || OW < 1 || (OW & (OW - 1)) || (128 % OW)) return false;
+    bh = 128 / OW; bn = 1;
+    if (bh > OH) { if (bh % OH) return false; bn = bh / OH; bh = OH; }
+    else if (OH % bh) return false;
+    return true;
+}
+}  // namespace
+
+// y[Nb,OH,OW,Cout] = conv(x[Nb,H,W,Cin], w[Cout,k,k,Cin]) [+ addend], stride 1 or 2, NHWC bf16, OH = (H + 2 pad - k)/stride + 1.
+// Implicit GEMM: per tap one 4-D TMA box of the input shifted by (s - pad, r - pad) — for stride 2 the tensor map walks
+// every second row / column (element strides), so neither an im2col matrix nor a strided copy is ever materialised.
+// Cin % 64 == 0, Cout % 64 == 0, OW a power of two <= 128, OH*OW a multiple or a divisor of the 128-pixel tile.
+FDT_API int fdt_conv_ex(const void* x, const void* w, void* y, float* sums, const void* addend, int Nb, int H, int W, int Cin,
+                        int Cout, int ksize, int pad, int stride, cudaStream_t st) {
+    if (Cin % 64 || Cout % 64 || ksize < 1 || ksize > 3 || (stride != 1 && stride != 2)) return -1;
+    const int OH = (H + 2 * pad - ksize) / stride + 1, OW = (W + 2 * pad - ksize) / stride + 1;
+    int bh, bn;
+    if (!tile_geom(OH, OW, bh, bn)) return -1;
+    if (stride == 2 && ((H & 1) || (W & 1))) return -1;
+    const int M = Nb * OH * OW;
     CUtensorMap tmA, tmB;
     const int BN = pick_bn(M, Cout);
     const int K = ksize * ksize * Cin;
-    if (!encode_nhwc(&tmA, x, Nb, H, W, Cin, W, bh, bn) || !encode_2d(&tmB, w, K, Cout, BK, BN)) return -4;
+    if (!encode_nhwc(&tmA, x, Nb, H, W, Cin, OW, bh, bn, stride) || !encode_2d(&tmB, w, K, Cout, BK, BN)) return -4;
     GemmParams p{};
-    p.M = M; p.N = Cout; p.num_kb = K / BK; p.out = (__nv_bfloat16*)y; p.sums = sums; p.act = ACT_NONE;
-    p.H = H; p.W = W; p.bh = bh; p.bn = bn; p.pad = pad; p.kw = ksize; p.cpb = Cin / BK;
+    p.M = M; p.N = Cout; p.out = (__nv_bfloat16*)y; p.sums = sums; p.act = ACT_NONE; p.addend = (const __nv_bfloat16*)addend;
+    p.H = OH; p.W = OW; p.bh = bh; p.bn = bn; p.cpb = Cin / BK; p.in_mul = stride;
+    p.ntaps = ksize * ksize;
+    for (int r = 0; r < ksize; ++r)
+        for (int sx = 0; sx < ksize; ++sx) {
+            const int t = r * ksize + sx;
+            p.tap_dh[t] = r - pad; p.tap_dw[t] = sx - pad; p.tap_k[t] = t * Cin;
+        }
+    p.num_kb = p.ntaps * p.cpb;
     return BN == 128 ? launch<128, true>(tmA, tmB, p, st) : launch<64, true>(tmA, tmB, p, st);
+}
+
+FDT_API int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int Nb, int H, int W, int Cin, int Cout,
+                         int ksize, int pad, cudaStream_t st) {
+    return fdt_conv_ex(x, w, y, sums, nullptr, Nb, H, W, Cin, Cout, ksize, pad, 1, st);
+}
+
+// Data gradient of a stride-2 convolution, without col2im: dx[Nb,H,W,Cin] (+)= Σ_taps dy[Nb,H/2,W/2,Cout] · w.
+// The input pixels fall into four parity classes (h % 2, w % 2); each class receives contributions from a fixed subset of
+// the taps (3x3, pad 1: 1, 2, 2 and 4 taps; 1x1: only the even/even class), and within a class the gather from dy is a
+// dense stride-1 pattern — so every class is one implicit-GEMM launch over the dy grid whose epilogue stores straight to
+// the class's pixels.  wt: the tap-rotated transposed filter [Cin][k][k][Cout] (the layout the stride-1 dgrad uses).
+// accumulate != 0: dx already holds the other branch's gradient and the result is ADDED to it in the epilogue (classes
+// without taps are then left alone); accumulate == 0: dx is overwritten (classes without taps are zero-filled).
+FDT_API int fdt_conv_dgrad_s2(const void* dy, const void* wt, void* dx, int accumulate, int Nb, int H, int W, int Cin, int Cout,
+                              int ksize, int pad, cudaStream_t st) {
+    if (Cin % 64 || Cout % 64 || (H & 1) || (W & 1) || ksize < 1 || ksize > 3) return -1;
+    const int OH = (H + 2 * pad - ksize) / 2 + 1, OW = (W + 2 * pad - ksize) / 2 + 1;
+    if (OH != H / 2 || OW != W / 2) return -1;
+    int bh, bn;
+    if (!tile_geom(OH, OW, bh, bn)) return -1;
+    const int M = Nb * OH * OW;
+    const int BN = pick_bn(M, Cin);
+    const int K = ksize * ksize * Cout;
+    CUtensorMap tmA, tmB;
+    if (!encode_nhwc(&tmA, dy, Nb, OH, OW, Cout, OW, bh, bn, 1) || !encode_2d(&tmB, wt, K, Cin, BK, BN)) return -4;
+    bool need_clear = false;
+    for (int cls = 0; cls < 4 && !accumulate; ++cls) {
+        const int ph = cls >> 1, pw = cls & 1;
+        int nh = 0, nw = 0;
+        for (int r = 0; r < ksize; ++r) nh += ((ph + pad - r) % 2 == 0);
+        for (int s = 0; s < ksize; ++s) nw += ((pw + pad - s) % 2 == 0);
+        if (nh * nw == 0) need_clear = true;
+    }
+    if (need_clear) {
+        cudaError_t e = cudaMemsetAsync(dx, 0, (size_t)Nb * H * W * Cin * 2, st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    for (int cls = 0; cls < 4; ++cls) {
+        const int ph = cls >> 1, pw = cls & 1;
+        GemmParams p{};
+        p.M = M; p.N = Cin; p.out = (__nv_bfloat16*)dx; p.act = ACT_NONE;
+        p.addend = accumulate ? (const __nv_bfloat16*)dx : nullptr;
+        p.H = OH; p.W = OW; p.bh = bh; p.bn = bn; p.cpb = Cout / BK; p.in_mul = 1;
+        p.omode = 1; p.OH = H; p.OW = W; p.oph = ph; p.opw = pw;
+        int nt = 0;
+        for (int r = 0; r < ksize; ++r) {
+            if ((ph + pad - r) % 2) continue;
+            for (int s = 0; s < ksize; ++s) {
+                if ((pw + pad - s) % 2) continue;
+                // x row h = 2i + ph receives dy row (h + pad - r) / 2 = i + (ph + pad - r) / 2 through tap r
+                p.tap_dh[nt] = (ph + pad - r) / 2; p.tap_dw[nt] = (pw + pad - s) / 2;
+                p.tap_k[nt] = ((ksize - 1 - r) * ksize + (ksize - 1 - s)) * Cout;      // position in the ROTATED filter
+                ++nt;
+            }
+        }
+        if (nt == 0) continue;
+        p.ntaps = nt; p.num_kb = nt * p.cpb;
+        const int rc = BN == 128 ? launch<128, true>(tmA, tmB, p, st) : launch<64, true>(tmA, tmB, p, st);
+        if (rc) return rc;
+    }
+    return 0;
 }

@@ -37,7 +37,8 @@ struct WgradParams {
     float* acc;            // multicast + split-K: local fp32 staging ([Cout][taps][Cin], all zero between launches)
     int* counters;         // multicast + split-K: per-tile arrival counters (all zero between launches)
     int splits;
-    int H, W, bh, bn;      // conv geometry of the 64-pixel box
+    int H, W, bh, bn;      // conv geometry of the 64-pixel box, on the grid of OUTPUT pixels (= dY's pixels)
+    int in_mul;            // convolution stride: output row oh reads input row in_mul * oh + r - pad (element strides in tmX)
     int tiles_n;           // Cin tiles
 };
 
@@ -118,7 +119,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ C
                         else { n0 = kb * p.bn; h0 = 0; }
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
-                            tma_load_4d(sB + j * 8192, &tmX, &full_bar[s], n_tile * BN + j * 64, sx - p.pad, h0 + r - p.pad, n0);
+                            tma_load_4d(sB + j * 8192, &tmX, &full_bar[s], n_tile * BN + j * 64, sx - p.pad, p.in_mul * h0 + r - p.pad, n0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
@@ -251,12 +252,12 @@ bool encode_pc(CUtensorMap* m, const void* ptr, uint64_t C, uint64_t P) {   // [
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
-bool encode_nhwc64(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, int bw, int bh, int bn) {
+bool encode_nhwc64(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, int bw, int bh, int bn, int es = 1) {
     if (!get_encode()) return false;
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Nb};
     cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
+    cuuint32_t box[4] = {64, (cuuint32_t)(bw * es), (cuuint32_t)(bh * es), (cuuint32_t)bn};   // every es-th pixel: bw x bh pixels
+    cuuint32_t estr[4] = {1, (cuuint32_t)es, (cuuint32_t)es, 1};
     return get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -326,30 +327,38 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, WgradParams p, cudaStream
 
 }  // namespace
 
-// dw[Cout][k][k][Cin] (fp32) += dY[Nb,H,W,Cout]ᵀ ⊛ X[Nb,H,W,Cin]; stride 1, pad = k/2, NHWC bf16.
-// Cin % 64 == 0; W a power of two <= 64; (Nb·H·W) % 64 == 0.
+// dw[Cout][k][k][Cin] (fp32) += dY[Nb,OH,OW,Cout]ᵀ ⊛ X[Nb,H,W,Cin]; stride 1 or 2, NHWC bf16, OH = (H + 2 pad - k)/stride + 1.
+// Cin % 64 == 0; OW a power of two <= 64; (Nb·OH·OW) % 64 == 0.  For stride 2 the X tensor map walks every second pixel.
 // alpha scales the result; multicast != 0 means `dw` is an NVLS multicast address and the accumulation is a
 // fused all-reduce (every rank's buffer receives alpha·tile).
-FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
-                           int pad, float alpha, int multicast, cudaStream_t st) {
-    if (Cin % 64 || Cout % 8 || W > 64 || (W & (W - 1)) || (64 % W)) return -1;
-    int bh = 64 / W, bn = 1;
-    if (bh > H) { if (bh % H) return -1; bn = bh / H; bh = H; }
-    else if (H % bh) return -1;
-    const int64_t P = (int64_t)Nb * H * W;
+FDT_API int fdt_conv_wgrad_ex(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
+                              int pad, int stride, float alpha, int multicast, cudaStream_t st) {
+    if (stride != 1 && stride != 2) return -1;
+    const int OH = (H + 2 * pad - ksize) / stride + 1, OW = (W + 2 * pad - ksize) / stride + 1;
+    if (Cin % 64 || Cout % 8 || OW > 64 || OW < 1 || (OW & (OW - 1)) || (64 % OW)) return -1;
+    if (stride == 2 && ((H & 1) || (W & 1))) return -1;
+    int bh = 64 / OW, bn = 1;
+    if (bh > OH) { if (bh % OH) return -1; bn = bh / OH; bh = OH; }
+    else if (OH % bh) return -1;
+    const int64_t P = (int64_t)Nb * OH * OW;
     if (P % 64 || (bn > 1 && Nb % bn)) return -1;
     CUtensorMap tmDY, tmX;
     if (!encode_pc(&tmDY, dy, Cout, P)) return -4;
     WgradParams p{};
     p.Cout = Cout; p.Cin = Cin; p.taps = ksize * ksize; p.kw = ksize; p.pad = pad; p.num_kb = (int)(P / 64); p.dw = dw;
-    p.H = H; p.W = W; p.bh = bh; p.bn = bn; p.alpha = alpha; p.multicast = multicast;
+    p.H = OH; p.W = OW; p.bh = bh; p.bn = bn; p.in_mul = stride; p.alpha = alpha; p.multicast = multicast;
     const bool wide = (Cin % 128 == 0);
-    if (ksize == 1) {
+    if (ksize == 1 && stride == 1) {
         if (!encode_pc(&tmX, x, Cin, P)) return -4;
         return wide ? launch<128, false>(tmDY, tmX, p, st) : launch<64, false>(tmDY, tmX, p, st);
     }
-    if (!encode_nhwc64(&tmX, x, Nb, H, W, Cin, W, bh, bn)) return -4;
+    if (!encode_nhwc64(&tmX, x, Nb, H, W, Cin, OW, bh, bn, stride)) return -4;
     return wide ? launch<128, true>(tmDY, tmX, p, st) : launch<64, true>(tmDY, tmX, p, st);
+}
+
+FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
+                           int pad, float alpha, int multicast, cudaStream_t st) {
+    return fdt_conv_wgrad_ex(dy, x, dw, Nb, H, W, Cin, Cout, ksize, pad, 1, alpha, multicast, st);
 }
 
 // dw[N][K] (fp32) += dY[M,N]ᵀ · X[M,K]   (linear layers).  K % 64 == 0, N % 8 == 0, M % 64 == 0.

@@ -44,9 +44,9 @@ class ConvBNStat(nn.Module):
         with torch.no_grad():
             self.conv_weight.uniform_(-bound, bound)
 
-    def forward(self, x, act="none", residual=None):
+    def forward(self, x, act="none", residual=None, passthrough=False):
         return ops.conv_bnstat_act(x, self.conv_weight, self.stride, self.padding, self.eps, act, residual,
-                                   getattr(self, "_fdt_arena", None))
+                                   getattr(self, "_fdt_arena", None), passthrough)
 
     def extra_repr(self):
         return f"{self.in_channels}, {self.out_channels}, k={self.kernel_size}, pad={self.padding}, eps={self.eps}"
@@ -67,18 +67,26 @@ class Act(nn.Module):
         return self.kind
 
 
-def _conv_bn(conv: nn.Conv2d, bn: nn.BatchNorm2d, x, act="none", residual=None):
+def _conv_bn(conv: nn.Conv2d, bn: nn.BatchNorm2d, x, act="none", residual=None, passthrough=False):
     return ops.conv_bnaffine_act(
         x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked,
         conv.stride[0], conv.padding[0], bn.eps, bn.momentum, bn.training, act, residual,
-        getattr(bn, "_fdt_arena", None))
+        getattr(bn, "_fdt_arena", None), passthrough)
 
 
 class _Block(nn.Module):
-    def _shortcut(self, x):
+    """A residual block's input feeds two branches, so its gradient is a sum.  With ``passthrough=True`` a fused unit also
+    returns its input as a second output; the OTHER branch consumes that alias, so both gradients reach the unit's
+    backward together and the sum happens in the epilogue of its data-gradient GEMM instead of in a separate add kernel
+    (16 of them per ResNet-50 step)."""
+
+    def _fork(self, x, first, act):
+        """Returns (first unit's output, shortcut tensor)."""
         if len(self.shortcut) == 0:
-            return x
-        return _conv_bn(self.shortcut[0], self.shortcut[1], x)
+            o, xp = first(x, act, True)
+            return o, xp
+        sc, xp = _conv_bn(self.shortcut[0], self.shortcut[1], x, passthrough=True)
+        return first(xp, act, False), sc
 
 
 class BasicBlock(_Block):
@@ -108,12 +116,12 @@ class BasicBlock(_Block):
     def forward(self, x):
         rf = self.residual_function
         if self.stride != 1:
-            o = _conv_bn(rf[0], rf[1], x, act="celu")
+            o, sc = self._fork(x, lambda t, a, pt: _conv_bn(rf[0], rf[1], t, act=a, passthrough=pt), "celu")
             last = rf[3]
         else:
-            o = rf[0](x, act="celu")
+            o, sc = self._fork(x, lambda t, a, pt: rf[0](t, act=a, passthrough=pt), "celu")
             last = rf[2]
-        return last(o, act="celu", residual=self._shortcut(x))
+        return last(o, act="celu", residual=sc)
 
 
 class BottleNeck(_Block):
@@ -146,14 +154,14 @@ class BottleNeck(_Block):
 
     def forward(self, x):
         rf = self.residual_function
-        o = rf[0](x, act="relu")
+        o, sc = self._fork(x, lambda t, a, pt: rf[0](t, act=a, passthrough=pt), "relu")
         if self.stride != 1:
             o = _conv_bn(rf[2], rf[3], o, act="relu")
             last = rf[5]
         else:
             o = rf[2](o, act="relu")
             last = rf[4]
-        return last(o, act="relu", residual=self._shortcut(x))
+        return last(o, act="relu", residual=sc)
 
 
 class ResNet(nn.Module):
@@ -181,7 +189,10 @@ class ResNet(nn.Module):
             if isinstance(m, ConvBNStat):
                 m.conv_weight._fdt_dgrad_mode = 0
             elif isinstance(m, nn.Conv2d):
-                m.weight._fdt_dgrad_mode = 0 if m.stride[0] == 1 and 2 * m.padding[0] == m.kernel_size[0] - 1 else 1
+                # stride 1 and stride 2 "same"-padded convs: tap-rotated filter (implicit-GEMM dgrad); anything else: [K, Cout]
+                native = (m.stride[0] in (1, 2) and 2 * m.padding[0] == m.kernel_size[0] - 1
+                          and m.in_channels % 64 == 0 and m.out_channels % 64 == 0)
+                m.weight._fdt_dgrad_mode = 0 if native else 1
 
     def _make_layer(self, block, out_channels, num_blocks, stride):
         layers = []

@@ -44,23 +44,27 @@ def launch_counter():
     return _lib.LAUNCHES
 
 
-def conv_bnstat_act(x, weight, stride=1, padding=0, eps=1e-3, act="none", residual=None, arena=None):
-    """``arena``: optional ``(BNArena, offset)`` — a statistics slot cleared once per forward pass by the model."""
+def conv_bnstat_act(x, weight, stride=1, padding=0, eps=1e-3, act="none", residual=None, arena=None, passthrough=False):
+    """``arena``: optional ``(BNArena, offset)`` — a statistics slot cleared once per forward pass by the model.
+    ``passthrough``: also return the input as a second output (an alias); whoever else consumes the input should consume
+    that alias, so its gradient is added inside this unit's data-gradient GEMM (see models/resnet.py::_Block)."""
     if use_native(x):
-        return _cu().conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena)
-    return ref.conv_bnstat_act(x, weight, stride, padding, eps, act, residual)
+        return _cu().conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena, passthrough)
+    out = ref.conv_bnstat_act(x, weight, stride, padding, eps, act, residual)
+    return (out, x) if passthrough else out
 
 
 def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_batches_tracked,
                       stride=1, padding=0, eps=1e-5, momentum=0.1, training=True,
-                      act="none", residual=None, arena=None):
+                      act="none", residual=None, arena=None, passthrough=False):
     if use_native(x):
         return _cu().conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
                                        num_batches_tracked, stride, padding, eps, momentum,
-                                       training, act, residual, arena)
-    return ref.conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
-                                 num_batches_tracked, stride, padding, eps, momentum,
-                                 training, act, residual)
+                                       training, act, residual, arena, passthrough)
+    out = ref.conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var,
+                                num_batches_tracked, stride, padding, eps, momentum,
+                                training, act, residual)
+    return (out, x) if passthrough else out
 
 
 def pool_fc(x, weight, bias):

@@ -227,7 +227,8 @@ def join_side_streams():
     _side["keep"].clear()
 
 
-def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=None, A=None):
+def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=None, A=None, addend=None):
+    """``addend``: gradient reaching x through the other branch of a residual fork; summed into dx in the dgrad epilogue."""
     dx = dw = None
     mc = _mc_slot(weight)
     if (_WGRAD_SIDE and need_dw and mc is None and _native_gemm() and weight is not None
@@ -246,8 +247,10 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
     if _native_gemm():
         from . import gemm_sm100
         if need_dx:
-            dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding, _wdgrad(weight, 0))
-            if dx is None:
+            dx = gemm_sm100.conv_dgrad(dy, w16, x.shape, stride, padding, _wdgrad(weight, 0), addend)
+            if dx is not None:
+                addend = None                   # already summed in the GEMM epilogue
+            else:
                 dx = gemm_sm100.conv_dgrad_im2col(dy, w16, x.shape, stride, padding, _wdgrad(weight, 1))
         if need_dw:
             if mc is not None:      # tile-by-tile in-switch all-reduce fused into the wgrad epilogue
@@ -271,6 +274,9 @@ def _conv_bwd(dy, x, w16, stride, padding, need_dx, need_dw, w_shape, weight=Non
     if dw is not None and mc is not None:
         _mc_accumulate(weight, dw)
         dw = None
+    if addend is not None and dx is not None:
+        _lib.note_fallback("conv_bwd", "residual-gradient sum as a separate ATen add (dgrad not on the implicit-GEMM kernel)")
+        dx = dx + addend
     return dx, dw
 
 
@@ -316,10 +322,12 @@ class _ConvBNAct(torch.autograd.Function):
                  i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=4 if form != 2 else 2)
         ctx.save_for_backward(x, weight, w16, y, out, bnctx)
         ctx.cfg = (stride, padding, act, form, residual is not None, gamma is not None)
+        if cfg.get("passthrough"):
+            return out, x.view_as(x)            # alias of the input: its consumer's gradient comes back through this node
         return out
 
     @staticmethod
-    def backward(ctx, gout):
+    def backward(ctx, gout, gpass=None):
         x, weight, w16, y, out, bnctx = ctx.saved_tensors
         stride, padding, act, form, has_res, affine = ctx.cfg
         Nb, C, Ho, Wo = y.shape
@@ -343,22 +351,25 @@ class _ConvBNAct(torch.autograd.Function):
             dbeta = torch.empty(C, dtype=torch.float32, device=dev)
         dy = torch.empty_like(y)
         call("fdt_bn_bwd_apply", g, y, dy, sums, bnctx, dgamma, dbeta, i64(P), C, form)
+        addend = None
+        if gpass is not None and ctx.needs_input_grad[0]:
+            addend = _nhwc(gpass)
         dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape, weight,
-                           getattr(ctx, "im2col_A", None))
+                           getattr(ctx, "im2col_A", None), addend)
         return dx, dw, dgamma, dbeta, (g if has_res else None), None
 
 
-def conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena=None):
-    cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=0, arena=arena)
+def conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena=None, passthrough=False):
+    cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=0, arena=arena, passthrough=passthrough)
     return _ConvBNAct.apply(x, weight, None, None, residual, cfg)
 
 
 def conv_bnaffine_act(x, weight, gamma, beta, running_mean, running_var, num_batches_tracked, stride, padding,
-                      eps, momentum, training, act, residual, arena=None):
+                      eps, momentum, training, act, residual, arena=None, passthrough=False):
     if training and num_batches_tracked is not None:
         num_batches_tracked.add_(1)
     cfg = dict(stride=stride, padding=padding, eps=eps, act=act, form=1 if training else 2,
-               running_mean=running_mean, running_var=running_var, momentum=momentum, arena=arena)
+               running_mean=running_mean, running_var=running_var, momentum=momentum, arena=arena, passthrough=passthrough)
     return _ConvBNAct.apply(x, weight, gamma, beta, residual, cfg)
 
 
@@ -658,12 +669,13 @@ def ngd_eig_update_multi(pending, max_sweeps: int = 12):
     call("fdt_ngd_eig_update_multi", ent[0], ent[1], int(max_sweeps))
 
 
-def ngd_norms_rescale(X: torch.Tensor, Xhat: torch.Tensor):
+def ngd_norms_rescale(X: torch.Tensor, Xhat: torch.Tensor, sums: Optional[torch.Tensor] = None):
     """(p0, out): p0[f] = ΣX_f², out_f = X̂_f·sqrt(p0/(p1+1e-30)) (X_f if p1 is NaN), written in place into
     ``Xhat``.  Three launches (memset, reduce, rescale) instead of ~10 tensor ops."""
     n = X.shape[0]
     M = X[0].numel()
-    sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
+    if sums is None:            # else: the factor batch's slice of the optimizer's per-step arena (cleared by one fill)
+        sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
     call("fdt_ngd_sumsq2", X, Xhat, sums, n, i64(M))
     call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(M))
     return sums[:n], Xhat
@@ -748,7 +760,7 @@ def ngd_tf32_ok(n, N, D, R, left) -> bool:
     return NGD_TC and R % 4 == 0 and 16 <= R <= 128 and D % 4 == 0 and (not left or N % 4 == 0)
 
 
-def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool):
+def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool, sums: Optional[torch.Tensor] = None):
     """H = X Wᵀ and X̂ = X − H W for a factor batch on the tensor cores, then the norm-restoring rescale.  ``X`` is
     [n, N, D] (left=False) or the transposed gradient [n, D, N] (left=True), used where it lies.
     Returns (H [n, N, R], out (same layout as X), p0 [n])."""
@@ -756,7 +768,8 @@ def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool):
     N = X[0].numel() // D
     H = torch.empty(n, N, R, dtype=torch.float32, device=X.device)
     Xhat = torch.empty_like(X)
-    sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
+    if sums is None:
+        sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
     call("fdt_ngd_project", X, W, H, Xhat, sums, n, N, D, R, int(bool(left)), launches=2)
     call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(N * D))
     return H, Xhat, sums[:n]

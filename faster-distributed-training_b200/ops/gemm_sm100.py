@@ -32,8 +32,8 @@ def available() -> bool:
 
 
 def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act: str = "none",
-            out_dtype=BF16, sums: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
-    """act(a[M,K] @ b[N,K]ᵀ + bias) with fp32 accumulation; a, b bf16 row-major."""
+            out_dtype=BF16, sums: Optional[torch.Tensor] = None, addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """act(a[M,K] @ b[N,K]ᵀ + bias) [+ addend] with fp32 accumulation; a, b bf16 row-major; ``addend`` bf16 [M, N]."""
     M, K = a.shape
     N = b.shape[0]
     if K % 64 or N % 64 or M < 1 or not (a.is_contiguous() and b.is_contiguous()):
@@ -41,16 +41,21 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
     out = torch.empty(M, N, dtype=out_dtype, device=a.device)
     o16 = out if out_dtype == BF16 else None
     o32 = out if out_dtype == torch.float32 else None
-    call("fdt_gemm_nt", a, b, o16, o32, bias, sums, M, N, K, ACT[act])
+    call("fdt_gemm_nt_ex", a, b, o16, o32, bias, sums, addend, M, N, K, ACT[act])
     return out
 
 
 def _conv_ok(x, w16, stride, padding) -> bool:
+    """Shapes the implicit-GEMM kernel covers: stride 1 or 2, "same"-style padding (pad = k // 2), channel counts that are
+    multiples of 64 and an OUTPUT width that is a power of two <= 128 (a 128-pixel tile = whole rows / whole images)."""
     N, Cin, H, W = x.shape
     Cout, _, kh, kw = w16.shape
-    if stride != 1 or kh != kw or padding != kh // 2 or Cin % 64 or Cout % 64:
+    if stride not in (1, 2) or kh != kw or kh > 3 or padding != kh // 2 or Cin % 64 or Cout % 64:
         return False
-    if W > 128 or W & (W - 1) or 128 % W:
+    if stride == 2 and (H % 2 or W % 2):
+        return False
+    H, W = (H + 2 * padding - kh) // stride + 1, (W + 2 * padding - kw) // stride + 1
+    if W < 1 or W > 128 or W & (W - 1) or 128 % W:
         return False
     bh = 128 // W
     if bh > H:
@@ -59,17 +64,20 @@ def _conv_ok(x, w16, stride, padding) -> bool:
 
 
 def conv_fwd(x: torch.Tensor, w16: torch.Tensor, stride: int, padding: int,
-             sums: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
-    """x: bf16 logical [N,Cin,H,W] channels_last; w16: bf16 logical [Cout,Cin,kh,kw] channels_last."""
+             sums: Optional[torch.Tensor] = None, addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """x: bf16 logical [N,Cin,H,W] channels_last; w16: bf16 logical [Cout,Cin,kh,kw] channels_last.  Stride 2 runs on
+    the same implicit-GEMM kernel (the TMA tensor map walks every second pixel).  ``addend`` (bf16, shaped like the
+    result) is added in the epilogue."""
     if not _conv_ok(x, w16, stride, padding):
         return None
     N, Cin, H, W = x.shape
     Cout, _, kh, _ = w16.shape
-    y = torch.empty((N, Cout, H, W), dtype=BF16, device=x.device, memory_format=torch.channels_last)
-    if kh == 1:
-        call("fdt_gemm_nt", x, w16, y, None, None, sums, N * H * W, Cout, Cin, 0)
+    Ho, Wo = (H + 2 * padding - kh) // stride + 1, (W + 2 * padding - kh) // stride + 1
+    y = torch.empty((N, Cout, Ho, Wo), dtype=BF16, device=x.device, memory_format=torch.channels_last)
+    if kh == 1 and stride == 1:
+        call("fdt_gemm_nt_ex", x, w16, y, None, None, sums, addend, N * H * W, Cout, Cin, 0)
     else:
-        call("fdt_conv_fwd", x, w16, y, sums, N, H, W, Cin, Cout, kh, padding)
+        call("fdt_conv_ex", x, w16, y, sums, addend, N, H, W, Cin, Cout, kh, padding, stride)
     return y
 
 
@@ -80,18 +88,36 @@ def dgrad_weight(w16: torch.Tensor) -> torch.Tensor:
 
 
 def conv_dgrad(dy: torch.Tensor, w16: torch.Tensor, x_shape, stride: int, padding: int,
-               wt: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
-    """dX of a stride-1 "same" convolution = the same implicit GEMM with the rotated, transposed filter
-    (``wt``: that filter if the caller already has it — FlatParameters.refresh_dgrad_shadow)."""
+               wt: Optional[torch.Tensor] = None, addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """dX of a "same"-padded convolution on the implicit-GEMM kernel with the rotated, transposed filter (``wt``: that
+    filter if the caller already has it — FlatParameters.refresh_dgrad_shadow).  Stride 1: one launch.  Stride 2: four
+    parity-class launches that store straight to their pixels (``fdt_conv_dgrad_s2``) — no col2im.
+    ``addend``: the gradient arriving at the same tensor through the other branch of a residual fork (bf16, shape of dX);
+    it is added in the GEMM epilogue (stride 2: accumulated IN PLACE, the returned tensor is ``addend`` itself)."""
     N, Cin, H, W = x_shape
     Cout, _, kh, kw = w16.shape
-    if not _conv_ok(dy, w16, stride, padding):      # shape-only and symmetric in (Cin, Cout): same answer as for wt
-        return None
     if wt is None:
         wt = dgrad_weight(w16)
-    if not _conv_ok(dy, wt, stride, padding):
+    if stride == 1:
+        if not _conv_ok(dy, wt, 1, padding):
+            return None
+        return conv_fwd(dy, wt, 1, padding, None, addend)
+    if stride != 2 or kh != kw or kh > 3 or padding != kh // 2 or Cin % 64 or Cout % 64 or H % 2 or W % 2:
         return None
-    return conv_fwd(dy, wt, stride, padding)
+    Ho, Wo = H // 2, W // 2
+    if tuple(dy.shape[2:]) != (Ho, Wo) or Wo > 128 or Wo & (Wo - 1):
+        return None
+    bh = 128 // Wo
+    if (bh > Ho and bh % Ho) or (bh <= Ho and Ho % bh):
+        return None
+    if addend is not None:
+        if not (addend.dtype == BF16 and addend.is_contiguous(memory_format=torch.channels_last)):
+            addend = addend.to(dtype=BF16, memory_format=torch.channels_last)
+        dx = addend
+    else:
+        dx = torch.empty((N, Cin, H, W), dtype=BF16, device=dy.device, memory_format=torch.channels_last)
+    call("fdt_conv_dgrad_s2", dy, wt, dx, int(addend is not None), N, H, W, Cin, Cout, kh, padding, launches=4 if kh > 1 else 1)
+    return dx
 
 
 def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha=1.0, multicast=False):

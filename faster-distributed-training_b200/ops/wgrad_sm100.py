@@ -19,9 +19,14 @@ def available() -> bool:
 def _conv_ok(x_shape, w_shape, stride, padding) -> bool:
     Cout, Cin, kh, kw = w_shape
     N, _, H, W = x_shape
-    if stride != 1 or kh != kw or padding != kh // 2 or Cin % 64 or Cout % 8:
+    if stride not in (1, 2) or kh != kw or Cin % 64 or Cout % 8:
         return False
-    if W > 64 or W & (W - 1) or 64 % W:
+    if stride == 1 and padding != kh // 2:
+        return False
+    if stride == 2 and (H % 2 or W % 2 or padding != kh // 2):
+        return False
+    H, W = (H + 2 * padding - kh) // stride + 1, (W + 2 * padding - kw) // stride + 1     # output grid
+    if W < 1 or W > 64 or W & (W - 1) or 64 % W:
         return False
     bh = 64 // W
     if bh > H:
@@ -33,7 +38,7 @@ def _conv_ok(x_shape, w_shape, stride, padding) -> bool:
 
 
 def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha: float = 1.0, multicast: bool = False):
-    """fp32 weight gradient of a stride-1 "same" convolution.  ``accumulate_into`` (a physically
+    """fp32 weight gradient of a stride-1 or stride-2 "same"-padded convolution.  ``accumulate_into`` (a physically
     [Cout, kh, kw, Cin]-contiguous fp32 tensor, e.g. the parameter's slice of the flat gradient buffer)
     receives the result by atomic accumulation and ``True`` is returned; otherwise a fresh tensor in the
     logical [Cout, Cin, kh, kw] view comes back."""
@@ -44,10 +49,10 @@ def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha: flo
     if accumulate_into is not None:
         # a tensor, or a raw (possibly multicast) device address
         dst = accumulate_into if torch.is_tensor(accumulate_into) else _lib.ctypes.c_void_p(int(accumulate_into))
-        call("fdt_conv_wgrad", dy, x, dst, N, H, W, Cin, Cout, kh, padding, float(alpha), int(multicast))
+        call("fdt_conv_wgrad_ex", dy, x, dst, N, H, W, Cin, Cout, kh, padding, stride, float(alpha), int(multicast))
         return True
     dw = torch.zeros((Cout, kh, kw, Cin), dtype=torch.float32, device=x.device)
-    call("fdt_conv_wgrad", dy, x, dw, N, H, W, Cin, Cout, kh, padding, 1.0, 0)
+    call("fdt_conv_wgrad_ex", dy, x, dw, N, H, W, Cin, Cout, kh, padding, stride, 1.0, 0)
     return dw.permute(0, 3, 1, 2)
 
 

@@ -289,7 +289,7 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
         cu = ops._cu()
         if cu.ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, left):
             fb._h_rows = True
-            H, out, p0 = cu.ngd_project(Xc, fb.W, left)      # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale
+            H, out, p0 = cu.ngd_project(Xc, fb.W, left, getattr(fb, "_sums", None))   # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale
             if updating:
                 if pending is None:
                     _refresh(fb, Xc, left, H, p0)
@@ -301,7 +301,7 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
     H, Xhat = project()
     if native:
         from .. import ops
-        p0, out = ops._cu().ngd_norms_rescale(Xc, Xhat)      # fused Σx², Σx̂², rescale + NaN guard
+        p0, out = ops._cu().ngd_norms_rescale(Xc, Xhat, getattr(fb, "_sums", None))      # fused Σx², Σx̂², rescale + NaN guard
         if updating:
             if pending is None:
                 _refresh(fb, Xm, left, H, p0)
@@ -530,6 +530,25 @@ class NGD(Optimizer):
                 t.copy_(torch.tensor(vals, dtype=torch.float32))
                 self._hyper_host[gi] = vals
 
+    def _begin_sums_arena(self):
+        """The Σx² / Σx̂² accumulators of every factor batch live in ONE buffer cleared by one fill per step (they were
+        ~60 separate zero-fills).  Built once every factor batch exists (after the first step); before that each call
+        allocates its own."""
+        arena = getattr(self, "_sums_arena", None)
+        if arena is not None:
+            arena.zero_()
+            return
+        fbs = [fb for fb in self._factor_batches() if fb.W.is_cuda and fb.W.dtype == torch.float32]
+        if not fbs or any(fb.t == 0 for fb in fbs):
+            return
+        total = sum(2 * fb.n for fb in fbs)
+        arena = torch.zeros(total, dtype=torch.float32, device=fbs[0].W.device)
+        off = 0
+        for fb in fbs:
+            fb._sums = arena[off:off + 2 * fb.n]
+            off += 2 * fb.n
+        self._sums_arena = arena
+
     def fused_clip_wd(self, sq: torch.Tensor, max_norm: Optional[float], skipped: Optional[torch.Tensor]) -> bool:
         """Global-norm clip + non-finite guard + weight decay over the flat gradient range in ONE kernel,
         called by the Trainer between the gradient reduction and :meth:`step`.  Returns False (nothing done) when the
@@ -621,6 +640,7 @@ class NGD(Optimizer):
                 loss = closure()
         pending: List[FactorBatch] = []
         self.sync_lr()
+        self._begin_sums_arena()
         wd_done, self._wd_done = self._wd_done, False
         for gi, group in enumerate(self.param_groups):
             wd, mom, damp = group["weight_decay"], group["momentum"], group["dampening"]
@@ -775,6 +795,7 @@ class NGD(Optimizer):
                 if span is not None and fm.numel() != span[2] - span[1]:
                     raise ValueError(f"flat momentum has {fm.numel()} elements, this rank's span has {span[2] - span[1]}")
             plan.append((gi, group, entry, sgs))
+        self._sums_arena = None
         for gi, group, entry, sgs in plan:
             for k, v in entry.items():
                 if k not in ("shape_groups", "flat_momentum"):

@@ -134,10 +134,23 @@ int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out_f32, co
 /* y[Nb,H,W,Cout] = conv(x[Nb,H,W,Cin], w[Cout,k,k,Cin]), stride 1, pad = k/2, NHWC bf16 (implicit GEMM: shifted 4-D TMA boxes). */
 int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int Nb, int H, int W, int Cin, int Cout,
                  int ksize, int pad, cudaStream_t st);
+/* generalised forms: `addend` (optional bf16 tensor indexed like the output, may alias it) is added in the epilogue — the
+ * other branch's gradient at a residual fork; fdt_conv_ex also takes stride 2 (TMA element strides, no im2col);
+ * fdt_conv_dgrad_s2 is the data gradient of a stride-2 convolution as four parity-class implicit GEMMs (no col2im):
+ * dy [Nb,H/2,W/2,Cout], wt = tap-rotated transposed filter [Cin][k][k][Cout], dx [Nb,H,W,Cin]; accumulate != 0 adds into dx. */
+int fdt_gemm_nt_ex(const void* A, const void* B, void* out_bf16, float* out_f32, const float* bias, float* sums,
+                   const void* addend, int M, int N, int K, int act, cudaStream_t st);
+int fdt_conv_ex(const void* x, const void* w, void* y, float* sums, const void* addend, int Nb, int H, int W, int Cin,
+                int Cout, int ksize, int pad, int stride, cudaStream_t st);
+int fdt_conv_dgrad_s2(const void* dy, const void* wt, void* dx, int accumulate, int Nb, int H, int W, int Cin, int Cout,
+                      int ksize, int pad, cudaStream_t st);
 /* dw[Cout][k][k][Cin] (fp32) += alpha * dY^T (*) X  (MN-major operands, split-K).  multicast != 0: dw is an NVLS multicast
  * address and the accumulation is an in-switch all-reduce (multimem.red) of finished tiles. */
 int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
                    int pad, float alpha, int multicast, cudaStream_t st);
+/* same with stride 1 or 2 (H, W are the INPUT extents; the X tensor map walks every second pixel for stride 2) */
+int fdt_conv_wgrad_ex(const void* dy, const void* x, float* dw, int Nb, int H, int W, int Cin, int Cout, int ksize,
+                      int pad, int stride, float alpha, int multicast, cudaStream_t st);
 /* dw[N][K] (fp32) += alpha * dY[M,N]^T · X[M,K] */
 int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, float alpha, int multicast,
                      cudaStream_t st);
