@@ -1,10 +1,15 @@
-// Fused multi-head attention forward / backward on tcgen05 for sequences of up to 128 tokens, d_head = 64.
+// Fused multi-head attention forward / backward on tcgen05 for sequences of up to 512 tokens, d_head = 64.
 //
 //   P = dropout(softmax(Q Kᵀ / sqrt(d) + key mask)),   O = P V
 //
-// One CTA per (batch, head).  Q, K, V (and dO) are read straight out of the projection outputs —
-// [B·L, heads·64] matrices — with 2-D TMA boxes at column offset head·64, and O / dQ / dK / dV are written
-// back in the same layout, so there is no head transpose anywhere.  S = QKᵀ and all other products live in
+// Forward: one CTA per (128-query tile, batch, head) walks the key/value tiles with an online softmax (running max and
+// sum per query row in registers; the partial P·V of each tile is read back from tensor memory and folded into a
+// register accumulator with the usual rescale), the next K / V tile streaming in by TMA while the current one is used.
+// Backward: one CTA per (128-key tile, batch, head) keeps K, V resident, accumulates dK, dV in tensor memory over the query
+// tiles, and emits its dQ contribution per query tile (stored directly when there is a single key tile, fp32 red.add
+// into an accumulation buffer otherwise).  Q, K, V (and dO) are read straight out of the projection outputs —
+// [B·L, heads·64] slices of a packed [B·L, 3·heads·64] QKV matrix or separate matrices, any row stride — with 2-D TMA boxes
+// at column offset head·64, and O / dQ / dK / dV are written back the same way, so there is no head transpose anywhere.  S = QKᵀ and all other products live in
 // tensor memory; the softmax warps (one thread per query row) read S with tcgen05.ld, write the bf16
 // probabilities into shared memory in the 128B-swizzled layout the next MMA expects, and the second MMA
 // consumes them.  Every product of the backward pass is expressed with K-major or MN-major operand
@@ -25,15 +30,18 @@
 using namespace fdt;
 using namespace sm100;
 
+
 namespace {
 
 constexpr int kT = 128;        // tile: queries = keys = 128
 constexpr int kD = 64;         // head dim
+constexpr int kMaxL = 512;     // longest sequence (the reference's maxlen, transformer.py:35)
 constexpr int kThreads = 192;
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct AttnParams {
-    int B, H, L, ld;               // ld: row stride (elements) of the [B·L, H·64] matrices
+    int B, H, L;
+    int ldq, ldo, ldg;             // row strides (elements): q/k/v inputs; o and dO; dq/dk/dv outputs
     const int64_t* key_mask;       // [B, L] (nonzero = keep) or null
     int mask_compat;
     float scale, p_drop;
@@ -43,6 +51,7 @@ struct AttnParams {
     const __nv_bfloat16* dO;       // bwd in (also via TMA)
     const __nv_bfloat16* Oin;      // bwd in
     __nv_bfloat16 *dQ, *dK, *dV;   // bwd out
+    float* dQacc;                  // bwd: fp32 [B·L, H·64] accumulation buffer (zero on entry) when L > 128, else null
 };
 
 // byte offset of element (row, col) inside a [128 rows][64 bf16] 128B-swizzled atom
@@ -50,20 +59,20 @@ __device__ __forceinline__ uint32_t swz(int row, int col) {
     return (uint32_t)(row * 128 + ((((col >> 3) ^ (row & 7)) << 4) | ((col & 7) << 1)));
 }
 
-__device__ __forceinline__ float drop_scale(const Philox& rng, uint64_t off, int bh, int row, int col4, float p, float inv_keep,
-                                            float* m4) {
-    uint4 r = rng(((uint64_t)bh * kT + row) * 32 + col4, off);
+// dropout keep-scales of 4 consecutive keys (global key index 4*col4 ..) for global query row qrow of (batch, head) bh
+__device__ __forceinline__ void drop_scale(const Philox& rng, uint64_t off, int bh, int qrow, int col4, float p, float inv_keep,
+                                           float* m4) {
+    uint4 r = rng(((uint64_t)bh * kMaxL + qrow) * (kMaxL / 4) + col4, off);
     m4[0] = u32_to_unit(r.x) >= p ? inv_keep : 0.f;
     m4[1] = u32_to_unit(r.y) >= p ? inv_keep : 0.f;
     m4[2] = u32_to_unit(r.z) >= p ? inv_keep : 0.f;
     m4[3] = u32_to_unit(r.w) >= p ? inv_keep : 0.f;
-    return 0.f;
 }
 
-// additive bias / replacement for key j of batch b (evaluated once per CTA into shared memory)
-__device__ __forceinline__ void load_key_bias(const AttnParams& p, int b, float* kbias, int* kfill) {
-    for (int j = threadIdx.x; j < kT; j += kThreads) {
-        float bias = 0.f; int fill = 0;
+// additive bias / replacement for every key of batch b (evaluated once per CTA into shared memory; keys >= L get -inf)
+__device__ __forceinline__ void load_key_bias(const AttnParams& p, int b, float* kbias, uint8_t* kfill) {
+    for (int j = threadIdx.x; j < kMaxL; j += kThreads) {
+        float bias = 0.f; uint8_t fill = 0;
         if (j >= p.L) bias = -INFINITY;
         else if (p.key_mask && p.key_mask[(size_t)b * p.L + j] == 0) {
             if (p.mask_compat) fill = 1; else bias = -INFINITY;
@@ -72,8 +81,11 @@ __device__ __forceinline__ void load_key_bias(const AttnParams& p, int b, float*
     }
 }
 
+constexpr int kFwdSmem = 4 * 16384 + 16384;                    // Q, K, V, P (2 atoms)
+constexpr int kAuxBytes = 16 * 8 + 16 + kMaxL * 4 + kMaxL;     // barriers, tmem ptr, key bias, key fill
+
 // ------------------------------------------------------------------ forward
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -82,18 +94,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint8_t* sK = smem + 16384;
     uint8_t* sV = smem + 32768;
     uint8_t* sP = smem + 49152;         // 2 atoms (keys 0-63 | 64-127), 32 KB
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 81920);   // [0] qkv, [1] S ready, [2] P ready, [3] O ready
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 4);
-    float* kbias = reinterpret_cast<float*>(bars + 6);
-    int* kfill = reinterpret_cast<int*>(kbias + kT);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kFwdSmem);   // [0] Q, [1] K, [2] V, [3] S ready, [4] P ready, [5] PV done
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
+    float* kbias = reinterpret_cast<float*>(tmem_ptr + 4);
+    uint8_t* kfill = reinterpret_cast<uint8_t*>(kbias + kMaxL);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int bh = blockIdx.x, b = bh / p.H, h = bh % p.H;
+    const int qt = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh % p.H;
     const int row0 = b * p.L, col0 = h * kD;
+    const int nkv = (p.L + kT - 1) / kT;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
-        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 128); mbar_init(&bars[3], 1);
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1);
+        mbar_init(&bars[3], 1); mbar_init(&bars[4], 128); mbar_init(&bars[5], 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<256>(tmem_ptr);
@@ -106,106 +120,131 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
     if (warp == 0) {
         if (lane == 0) {
-            mbar_arrive_expect_tx(&bars[0], 3 * 16384);
-            tma_load_2d(sQ, &tmQ, &bars[0], col0, row0);
-            tma_load_2d(sK, &tmK, &bars[0], col0, row0);
-            tma_load_2d(sV, &tmV, &bars[0], col0, row0);
+            mbar_arrive_expect_tx(&bars[0], 16384);
+            tma_load_2d(sQ, &tmQ, &bars[0], col0, row0 + qt * kT);
+            for (int j = 0; j < nkv; ++j) {
+                if (j > 0) mbar_wait(&bars[3], (j - 1) & 1);            // S_{j-1} done: K buffer is free
+                mbar_arrive_expect_tx(&bars[1], 16384);
+                tma_load_2d(sK, &tmK, &bars[1], col0, row0 + j * kT);
+                if (j > 0) mbar_wait(&bars[5], (j - 1) & 1);            // P·V_{j-1} done: V buffer is free
+                mbar_arrive_expect_tx(&bars[2], 16384);
+                tma_load_2d(sV, &tmV, &bars[2], col0, row0 + j * kT);
+            }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            mbar_wait(&bars[0], 0);
-            tc_fence_after();
             const uint64_t dq = make_smem_desc(smem_u32(sQ), 16, 1024), dk = make_smem_desc(smem_u32(sK), 16, 1024);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16(tmS, dq + 2 * k, dk + 2 * k, make_idesc_bf16(128, 128, 0, 0), k != 0);
-            umma_commit(&bars[1]);
-            mbar_wait(&bars[2], 0);                       // probabilities are in shared memory
-            tc_fence_after();
             const uint64_t dv = make_smem_desc(smem_u32(sV), 8192, 1024);       // B = V, N(d)-major, K = keys
+            mbar_wait(&bars[0], 0);
+            for (int j = 0; j < nkv; ++j) {
+                mbar_wait(&bars[1], j & 1);
+                if (j > 0) mbar_wait(&bars[4], (j - 1) & 1);            // softmax has consumed S_{j-1}
+                tc_fence_after();
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const uint64_t dp = make_smem_desc(smem_u32(sP) + (k >> 2) * 16384, 16, 1024) + 2 * (k & 3);
-                umma_bf16(tmO, dp, dv + 128 * k, make_idesc_bf16(128, 64, 0, 1), k != 0);
+                for (int k = 0; k < 4; ++k) umma_bf16(tmS, dq + 2 * k, dk + 2 * k, make_idesc_bf16(128, 128, 0, 0), k != 0);
+                umma_commit(&bars[3]);
+                mbar_wait(&bars[4], j & 1);                             // probabilities of tile j are in shared memory
+                mbar_wait(&bars[2], j & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint64_t dp = make_smem_desc(smem_u32(sP) + (k >> 2) * 16384, 16, 1024) + 2 * (k & 3);
+                    umma_bf16(tmO, dp, dv + 128 * k, make_idesc_bf16(128, 64, 0, 1), k != 0);
+                }
+                umma_commit(&bars[5]);
             }
-            umma_commit(&bars[3]);
         }
     } else {
         const int q = warp & 3, row = q * 32 + lane;
+        const int qrow = qt * kT + row;                          // query index inside the sequence
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         const float sl2 = p.scale * kLog2e;
-        mbar_wait(&bars[1], 0);
-        tc_fence_after();
-        // pass 1: row maximum (in scaled log2 units)
-        float mx = -INFINITY;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tmS + lane_addr + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int key = c * 32 + j;
-                float s = kfill[key] ? -1e-9f : __uint_as_float(r[j]);
-                s = s * sl2 + kbias[key];
-                mx = fmaxf(mx, s);
-            }
-        }
-        if (mx == -INFINITY) mx = 0.f;
-        // pass 2: exponentials, row sum, dropout, bf16 P into swizzled shared memory
         Philox rng(p.seed_off ? (uint64_t)p.seed_off[0] : 0ull);
         const uint64_t off = p.seed_off ? (uint64_t)p.seed_off[1] : 0ull;
         const float inv_keep = 1.f / (1.f - p.p_drop);
-        float sum = 0.f;
+        float m_run = -INFINITY, l_run = 0.f;
+        float o_acc[kD];
+#pragma unroll
+        for (int i = 0; i < kD; ++i) o_acc[i] = 0.f;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tmS + lane_addr + c * 32, r);
-            tmem_ld_wait();
-            float pv[32];
+        for (int j = 0; j < nkv; ++j) {
+            const float* kb = kbias + j * kT;
+            const uint8_t* kf = kfill + j * kT;
+            mbar_wait(&bars[3], j & 1);
+            tc_fence_after();
+            // pass 1: tile row maximum (scaled log2 units)
+            float mx = m_run;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmS + lane_addr + c * 32, r);
+                tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int key = c * 32 + j;
-                float s = kfill[key] ? -1e-9f : __uint_as_float(r[j]);
-                s = s * sl2 + kbias[key];
-                const float e = exp2f(s - mx);
-                sum += e;
-                pv[j] = e;
-            }
-            if (p.p_drop > 0.f) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    float m4[4];
-                    drop_scale(rng, off, bh, row, c * 8 + (j >> 2), p.p_drop, inv_keep, m4);
-                    pv[j] *= m4[0]; pv[j + 1] *= m4[1]; pv[j + 2] *= m4[2]; pv[j + 3] *= m4[3];
+                for (int jj = 0; jj < 32; ++jj) {
+                    const int key = c * 32 + jj;
+                    float s = kf[key] ? -1e-9f : __uint_as_float(r[jj]);
+                    mx = fmaxf(mx, s * sl2 + kb[key]);
                 }
             }
-            uint8_t* atom = sP + (c >> 1) * 16384;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-                const int col = (c & 1) * 32 + j;
-                *reinterpret_cast<uint4*>(atom + swz(row, col)) = pack8(pv + j).u;
-            }
-        }
-        fence_proxy_async();                                // generic-proxy smem writes → visible to the MMA
-        mbar_arrive(&bars[2]);
-        mbar_wait(&bars[3], 0);
-        tc_fence_after();
-        const float inv = 1.f / sum;
-        const bool row_ok = row < p.L;
-        if (row_ok) p.lse[(size_t)bh * p.L + row] = (mx + log2f(sum)) / kLog2e;   // natural-log units of the SCALED scores
-        __nv_bfloat16* o = p.O + (size_t)(row0 + row) * p.ld + col0;
+            const float m_new = (mx == -INFINITY) ? 0.f : mx;
+            const float alpha = (m_run == -INFINITY) ? 0.f : exp2f(m_run - m_new);
+            // pass 2: exponentials, row sum, dropout, bf16 P into swizzled shared memory
+            // (the P buffer is free: P·V_{j-1} completed before O_{j-1} was read at the end of the previous iteration)
+            float sum = 0.f;
 #pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tmO + lane_addr + c * 32, r);       // warp-collective: executed by every lane
-            tmem_ld_wait();
-            if (row_ok) {
-                float v[32];
+            for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmS + lane_addr + c * 32, r);
+                tmem_ld_wait();
+                float pv[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * inv;
+                for (int jj = 0; jj < 32; ++jj) {
+                    const int key = c * 32 + jj;
+                    float s = kf[key] ? -1e-9f : __uint_as_float(r[jj]);
+                    const float e = exp2f(s * sl2 + kb[key] - m_new);
+                    sum += e;
+                    pv[jj] = e;
+                }
+                if (p.p_drop > 0.f) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) st8(o + c * 32 + j, pack8(v + j));
+                    for (int jj = 0; jj < 32; jj += 4) {
+                        float m4[4];
+                        drop_scale(rng, off, bh, qrow, j * 32 + c * 8 + (jj >> 2), p.p_drop, inv_keep, m4);
+                        pv[jj] *= m4[0]; pv[jj + 1] *= m4[1]; pv[jj + 2] *= m4[2]; pv[jj + 3] *= m4[3];
+                    }
+                }
+                uint8_t* atom = sP + (c >> 1) * 16384;
+#pragma unroll
+                for (int jj = 0; jj < 32; jj += 8) {
+                    const int col = (c & 1) * 32 + jj;
+                    *reinterpret_cast<uint4*>(atom + swz(row, col)) = pack8(pv + jj).u;
+                }
             }
+            tc_fence_before();
+            fence_proxy_async();                                // generic-proxy smem writes → visible to the MMA
+            mbar_arrive(&bars[4]);
+            l_run = l_run * alpha + sum;
+            m_run = m_new;
+            mbar_wait(&bars[5], j & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {               // unrolled: o_acc stays in registers
+                uint32_t r[32];
+                tmem_ld_32x32(tmO + lane_addr + c * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int jj = 0; jj < 32; ++jj) o_acc[c * 32 + jj] = o_acc[c * 32 + jj] * alpha + __uint_as_float(r[jj]);
+            }
+            tc_fence_before();
+        }
+        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+        if (qrow < p.L) {
+            p.lse[(size_t)bh * p.L + qrow] = (m_run + log2f(l_run)) / kLog2e;   // natural-log units of the SCALED scores
+            __nv_bfloat16* o = p.O + (size_t)(row0 + qrow) * p.ldo + col0;
+#pragma unroll
+            for (int i = 0; i < kD; ++i) o_acc[i] *= inv;
+#pragma unroll
+            for (int i = 0; i < kD; i += 8) st8(o + i, pack8(o_acc + i));
         }
     }
     tc_fence_before();
@@ -214,6 +253,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 }
 
 // ------------------------------------------------------------------ backward
+constexpr int kBwdSmem = 4 * 16384 + 2 * 32768;               // Q, K, V, dO, P (2 atoms), dS (2 atoms)
+
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO, const AttnParams p) {
@@ -225,18 +266,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint8_t* sdO = smem + 49152;
     uint8_t* sP = smem + 65536;          // 32 KB
     uint8_t* sdS = smem + 98304;         // 32 KB
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 131072);   // [0] loads, [1] S & dP ready, [2] P & dS ready, [3] grads ready
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 4);
-    float* kbias = reinterpret_cast<float*>(bars + 6);
-    int* kfill = reinterpret_cast<int*>(kbias + kT);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kBwdSmem);   // [0] K,V  [1] Q,dO  [2] S & dP ready  [3] P & dS ready  [4] grads done
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
+    float* kbias = reinterpret_cast<float*>(tmem_ptr + 4);
+    uint8_t* kfill = reinterpret_cast<uint8_t*>(kbias + kMaxL);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int bh = blockIdx.x, b = bh / p.H, h = bh % p.H;
+    const int kt = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh % p.H;
     const int row0 = b * p.L, col0 = h * kD;
+    const int nq = (p.L + kT - 1) / kT;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV); prefetch_tmap(&tmdO);
-        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 128); mbar_init(&bars[3], 1);
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); mbar_init(&bars[3], 128); mbar_init(&bars[4], 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<512>(tmem_ptr);
@@ -249,120 +291,162 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
     if (warp == 0) {
         if (lane == 0) {
-            mbar_arrive_expect_tx(&bars[0], 4 * 16384);
-            tma_load_2d(sQ, &tmQ, &bars[0], col0, row0);
-            tma_load_2d(sK, &tmK, &bars[0], col0, row0);
-            tma_load_2d(sV, &tmV, &bars[0], col0, row0);
-            tma_load_2d(sdO, &tmdO, &bars[0], col0, row0);
+            mbar_arrive_expect_tx(&bars[0], 2 * 16384);
+            tma_load_2d(sK, &tmK, &bars[0], col0, row0 + kt * kT);
+            tma_load_2d(sV, &tmV, &bars[0], col0, row0 + kt * kT);
+            for (int i = 0; i < nq; ++i) {
+                if (i > 0) mbar_wait(&bars[4], (i - 1) & 1);            // the gradient MMAs of tile i-1 have read Q, dO
+                mbar_arrive_expect_tx(&bars[1], 2 * 16384);
+                tma_load_2d(sQ, &tmQ, &bars[1], col0, row0 + i * kT);
+                tma_load_2d(sdO, &tmdO, &bars[1], col0, row0 + i * kT);
+            }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            mbar_wait(&bars[0], 0);
-            tc_fence_after();
             const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV), adO = smem_u32(sdO);
             const uint32_t aP = smem_u32(sP), adS = smem_u32(sdS);
             const uint32_t iKK = make_idesc_bf16(128, 128, 0, 0);
-            {   // S = Q Kᵀ ; dP = dO Vᵀ   (all K-major, K = d = 64)
-                const uint64_t dq = make_smem_desc(aQ, 16, 1024), dk = make_smem_desc(aK, 16, 1024);
-                const uint64_t ddo = make_smem_desc(adO, 16, 1024), dv = make_smem_desc(aV, 16, 1024);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(tmS, dq + 2 * k, dk + 2 * k, iKK, k != 0);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(tmdP, ddo + 2 * k, dv + 2 * k, iKK, k != 0);
-            }
-            umma_commit(&bars[1]);
-            mbar_wait(&bars[2], 0);
-            tc_fence_after();
-            // MN-major views: tile [128 q rows (K)][128 keys (M)] = 2 atoms 16 KB apart; 8-row groups 1 KB apart
-            const uint64_t dPt = make_smem_desc(aP, 16384, 1024), dSt = make_smem_desc(adS, 16384, 1024);
-            const uint64_t ddoN = make_smem_desc(adO, 8192, 1024);     // B = dO, N(d)-major, K = q
-            const uint64_t dqN = make_smem_desc(aQ, 8192, 1024);       // B = Q,  N(d)-major, K = q
-            const uint64_t dkN = make_smem_desc(aK, 8192, 1024);       // B = K,  N(d)-major, K = keys
             const uint32_t iMM = make_idesc_bf16(128, 64, 1, 1), iKM = make_idesc_bf16(128, 64, 0, 1);
+            mbar_wait(&bars[0], 0);
+            for (int i = 0; i < nq; ++i) {
+                mbar_wait(&bars[1], i & 1);
+                tc_fence_after();
+                {   // S = Q Kᵀ ; dP = dO Vᵀ   (all K-major, K = d = 64)
+                    const uint64_t dq = make_smem_desc(aQ, 16, 1024), dk = make_smem_desc(aK, 16, 1024);
+                    const uint64_t ddo = make_smem_desc(adO, 16, 1024), dv = make_smem_desc(aV, 16, 1024);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) umma_bf16(tmdV, dPt + 128 * k, ddoN + 128 * k, iMM, k != 0);   // dV = Pᵀ dO
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmS, dq + 2 * k, dk + 2 * k, iKK, k != 0);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) umma_bf16(tmdK, dSt + 128 * k, dqN + 128 * k, iMM, k != 0);    // dK = dSᵀ Q
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmdP, ddo + 2 * k, dv + 2 * k, iKK, k != 0);
+                }
+                umma_commit(&bars[2]);
+                mbar_wait(&bars[3], i & 1);
+                tc_fence_after();
+                // MN-major views: tile [128 q rows (K)][128 keys (M)] = 2 atoms 16 KB apart; 8-row groups 1 KB apart
+                const uint64_t dPt = make_smem_desc(aP, 16384, 1024), dSt = make_smem_desc(adS, 16384, 1024);
+                const uint64_t ddoN = make_smem_desc(adO, 8192, 1024);     // B = dO, N(d)-major, K = q
+                const uint64_t dqN = make_smem_desc(aQ, 8192, 1024);       // B = Q,  N(d)-major, K = q
+                const uint64_t dkN = make_smem_desc(aK, 8192, 1024);       // B = K,  N(d)-major, K = keys
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {                                                             // dQ = dS K
-                const uint64_t ds = make_smem_desc(adS + (k >> 2) * 16384, 16, 1024) + 2 * (k & 3);
-                umma_bf16(tmdQ, ds, dkN + 128 * k, iKM, k != 0);
+                for (int k = 0; k < 8; ++k) umma_bf16(tmdV, dPt + 128 * k, ddoN + 128 * k, iMM, (i | k) != 0);   // dV += Pᵀ dO
+#pragma unroll
+                for (int k = 0; k < 8; ++k) umma_bf16(tmdK, dSt + 128 * k, dqN + 128 * k, iMM, (i | k) != 0);    // dK += dSᵀ Q
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {                                                                  // dQ_i = dS K
+                    const uint64_t ds = make_smem_desc(adS + (k >> 2) * 16384, 16, 1024) + 2 * (k & 3);
+                    umma_bf16(tmdQ, ds, dkN + 128 * k, iKM, k != 0);
+                }
+                umma_commit(&bars[4]);
             }
-            umma_commit(&bars[3]);
         }
     } else {
         const int q = warp & 3, row = q * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         const float sl2 = p.scale * kLog2e;
-        const bool row_ok = row < p.L;
-        // D_r = Σ_d dO[r,d]·O[r,d]
-        float Dr = 0.f, lse2 = 0.f;
-        if (row_ok) {
-            const __nv_bfloat16* o = p.Oin + (size_t)(row0 + row) * p.ld + col0;
-            const __nv_bfloat16* g = p.dO + (size_t)(row0 + row) * p.ld + col0;
-#pragma unroll
-            for (int j = 0; j < kD; j += 8) {
-                float fo[8], fg[8];
-                unpack8(ld8(o + j), fo);
-                unpack8(ld8(g + j), fg);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) Dr += fo[i] * fg[i];
-            }
-            lse2 = p.lse[(size_t)bh * p.L + row] * kLog2e;
-        }
         Philox rng(p.seed_off ? (uint64_t)p.seed_off[0] : 0ull);
         const uint64_t off = p.seed_off ? (uint64_t)p.seed_off[1] : 0ull;
         const float inv_keep = 1.f / (1.f - p.p_drop);
-        mbar_wait(&bars[1], 0);
-        tc_fence_after();
+        const float* kb = kbias + kt * kT;
+        const uint8_t* kf = kfill + kt * kT;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            uint32_t rs[32], rp[32];
-            tmem_ld_32x32(tmS + lane_addr + c * 32, rs);
-            tmem_ld_32x32(tmdP + lane_addr + c * 32, rp);
-            tmem_ld_wait();
-            float pd[32], ds[32];
+        for (int i = 0; i < nq; ++i) {
+            const int qrow = i * kT + row;
+            const bool row_ok = qrow < p.L;
+            // D_r = Σ_d dO[r,d]·O[r,d]
+            float Dr = 0.f, lse2 = 0.f;
+            if (row_ok) {
+                const __nv_bfloat16* o = p.Oin + (size_t)(row0 + qrow) * p.ldo + col0;
+                const __nv_bfloat16* g = p.dO + (size_t)(row0 + qrow) * p.ldo + col0;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                float m4[4] = {1.f, 1.f, 1.f, 1.f};
-                if (p.p_drop > 0.f) drop_scale(rng, off, bh, row, c * 8 + (j >> 2), p.p_drop, inv_keep, m4);
+                for (int j = 0; j < kD; j += 8) {
+                    float fo[8], fg[8];
+                    unpack8(ld8(o + j), fo);
+                    unpack8(ld8(g + j), fg);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int key = c * 32 + j + i;
-                    float s = kfill[key] ? -1e-9f : __uint_as_float(rs[j + i]);
-                    s = s * sl2 + kbias[key];
-                    const float pr = row_ok ? exp2f(s - lse2) : 0.f;          // softmax probability
-                    const float dpe = __uint_as_float(rp[j + i]) * m4[i];     // dropout applied to dP
-                    pd[j + i] = pr * m4[i];
-                    // masked-by-fill keys (compat mode) have a constant score: no gradient flows to Q, K
-                    ds[j + i] = kfill[key] ? 0.f : pr * (dpe - Dr) * p.scale;
+                    for (int u = 0; u < 8; ++u) Dr += fo[u] * fg[u];
+                }
+                lse2 = p.lse[(size_t)bh * p.L + qrow] * kLog2e;
+            }
+            mbar_wait(&bars[2], i & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t rs[32], rp[32];
+                tmem_ld_32x32(tmS + lane_addr + c * 32, rs);
+                tmem_ld_32x32(tmdP + lane_addr + c * 32, rp);
+                tmem_ld_wait();
+                float pd[32], ds[32];
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    float m4[4] = {1.f, 1.f, 1.f, 1.f};
+                    if (p.p_drop > 0.f) drop_scale(rng, off, bh, qrow, kt * 32 + c * 8 + (j >> 2), p.p_drop, inv_keep, m4);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int key = c * 32 + j + u;
+                        float s = kf[key] ? -1e-9f : __uint_as_float(rs[j + u]);
+                        s = s * sl2 + kb[key];
+                        const float pr = row_ok ? exp2f(s - lse2) : 0.f;          // softmax probability
+                        const float dpe = __uint_as_float(rp[j + u]) * m4[u];     // dropout applied to dP
+                        pd[j + u] = pr * m4[u];
+                        // masked-by-fill keys (compat mode) have a constant score: no gradient flows to Q, K
+                        ds[j + u] = kf[key] ? 0.f : pr * (dpe - Dr) * p.scale;
+                    }
+                }
+                uint8_t* aP = sP + (c >> 1) * 16384;
+                uint8_t* aS = sdS + (c >> 1) * 16384;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    const int col = (c & 1) * 32 + j;
+                    *reinterpret_cast<uint4*>(aP + swz(row, col)) = pack8(pd + j).u;
+                    *reinterpret_cast<uint4*>(aS + swz(row, col)) = pack8(ds + j).u;
                 }
             }
-            uint8_t* aP = sP + (c >> 1) * 16384;
-            uint8_t* aS = sdS + (c >> 1) * 16384;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-                const int col = (c & 1) * 32 + j;
-                *reinterpret_cast<uint4*>(aP + swz(row, col)) = pack8(pd + j).u;
-                *reinterpret_cast<uint4*>(aS + swz(row, col)) = pack8(ds + j).u;
-            }
-        }
-        fence_proxy_async();
-        mbar_arrive(&bars[2]);
-        mbar_wait(&bars[3], 0);
-        tc_fence_after();
-        {
-            const size_t base = (size_t)(row0 + row) * p.ld + col0;
-            const uint32_t srcs[3] = {tmdQ, tmdK, tmdV};
-            __nv_bfloat16* dsts[3] = {p.dQ, p.dK, p.dV};
+            tc_fence_before();
+            fence_proxy_async();
+            mbar_arrive(&bars[3]);
+            mbar_wait(&bars[4], i & 1);
+            tc_fence_after();
+            // this key tile's contribution to dQ of query tile i
 #pragma unroll 1
-            for (int t = 0; t < 3; ++t) {
+            for (int c = 0; c < 2; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmdQ + lane_addr + c * 32, r);       // warp-collective: executed by every lane
+                tmem_ld_wait();
+                if (row_ok) {
+                    if (p.dQacc) {
+                        float* dst = p.dQacc + (size_t)(row0 + qrow) * (p.H * kD) + col0 + c * 32;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(r[j])),
+                                         "f"(__uint_as_float(r[j + 1])), "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                                         : "memory");
+                    } else {
+                        float v[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                        __nv_bfloat16* dst = p.dQ + (size_t)(row0 + qrow) * p.ldg + col0 + c * 32;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) st8(dst + j, pack8(v + j));
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+        // dK, dV of this key tile (complete after the last query tile)
+        {
+            const int krow = kt * kT + row;
+            const bool k_ok = krow < p.L;
+            const size_t base = (size_t)(row0 + krow) * p.ldg + col0;
+            const uint32_t srcs[2] = {tmdK, tmdV};
+            __nv_bfloat16* dsts[2] = {p.dK, p.dV};
+#pragma unroll 1
+            for (int t = 0; t < 2; ++t) {
 #pragma unroll 1
                 for (int c = 0; c < 2; ++c) {
                     uint32_t r[32];
-                    tmem_ld_32x32(srcs[t] + lane_addr + c * 32, r);   // warp-collective: executed by every lane
+                    tmem_ld_32x32(srcs[t] + lane_addr + c * 32, r);
                     tmem_ld_wait();
-                    if (row_ok) {
+                    if (k_ok) {
                         float v[32];
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
@@ -376,6 +460,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<512>(tm);
+}
+
+// dq (bf16, row stride ldg) = the fp32 accumulation buffer [rows, cols]
+__global__ void attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int64_t rows, int cols, int ldg) {
+    const int64_t n8 = rows * (cols / 8);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / (cols / 8);
+        const int c = (int)(i - r * (cols / 8)) * 8;
+        const float4 a = *reinterpret_cast<const float4*>(acc + r * cols + c);
+        const float4 b2 = *reinterpret_cast<const float4*>(acc + r * cols + c + 4);
+        const float v[8] = {a.x, a.y, a.z, a.w, b2.x, b2.y, b2.z, b2.w};
+        st8(dq + r * ldg + c, pack8(v));
+    }
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -414,45 +511,66 @@ bool encode_rows(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, 
     return r == CUDA_SUCCESS;
 }
 
+
 }  // namespace
 
-// q, k, v, o: bf16 [B·L, H·64] views with row stride `ld` elements (heads side by side); lse: fp32 [B, H, L].
-// key_mask: int64 [B, L] (0 = masked) or null.  L <= 128.
+// q, k, v: bf16 [B·L, H·64] matrices with row stride `ldq` elements (e.g. three column slices of one packed [B·L, 3·H·64] QKV
+// projection output, ldq = 3·H·64); o: bf16 [B·L, H·64] with row stride `ldo`; lse: fp32 [B, H, L].
+// key_mask: int64 [B, L] (0 = masked) or null.  1 <= L <= 512.
 FDT_API int fdt_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const int64_t* key_mask,
-                         int B, int H, int L, int ld, float scale, float p_drop, const int64_t* seed_off, int mask_compat,
-                         cudaStream_t st) {
-    if (L < 1 || L > kT || ld % 8) return -1;
+                         int B, int H, int L, int ldq, int ldo, float scale, float p_drop, const int64_t* seed_off,
+                         int mask_compat, cudaStream_t st) {
+    if (L < 1 || L > kMaxL || ldq % 8 || ldo % 8 || B < 1 || H < 1) return -1;
     CUtensorMap tq, tk, tv;
     const uint64_t rows = (uint64_t)B * L, cols = (uint64_t)H * kD;
-    if (!encode_rows(&tq, q, rows, cols, ld) || !encode_rows(&tk, k, rows, cols, ld) || !encode_rows(&tv, v, rows, cols, ld)) return -4;
+    if (!encode_rows(&tq, q, rows, cols, ldq) || !encode_rows(&tk, k, rows, cols, ldq) || !encode_rows(&tv, v, rows, cols, ldq))
+        return -4;
     AttnParams p{};
-    p.B = B; p.H = H; p.L = L; p.ld = ld; p.key_mask = key_mask; p.mask_compat = mask_compat; p.scale = scale; p.p_drop = p_drop;
-    p.seed_off = p_drop > 0.f ? seed_off : nullptr; p.O = (__nv_bfloat16*)o; p.lse = lse;
-    const int smem = 81920 + 64 + kT * 8 + 1024;
+    p.B = B; p.H = H; p.L = L; p.ldq = ldq; p.ldo = ldo; p.key_mask = key_mask; p.mask_compat = mask_compat; p.scale = scale;
+    p.p_drop = p_drop; p.seed_off = p_drop > 0.f ? seed_off : nullptr; p.O = (__nv_bfloat16*)o; p.lse = lse;
+    const int smem = kFwdSmem + kAuxBytes + 1024;
     cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    attn_fwd_kernel<<<B * H, kThreads, smem, st>>>(tq, tk, tv, p);
+    attn_fwd_kernel<<<dim3((L + kT - 1) / kT, B * H), kThreads, smem, st>>>(tq, tk, tv, p);
     FDT_CHECK_LAUNCH();
     return 0;
 }
 
+// dq, dk, dv: bf16 outputs with row stride `ldg` (e.g. the three column slices of one packed [B·L, 3·H·64] gradient, the
+// operand of the fused QKV data-/weight-gradient GEMMs).  dq_acc: fp32 [B·L, H·64] work buffer, required when L > 128
+// (the key tiles of a sequence add their dQ contributions into it; cleared and converted here), ignored otherwise.
 FDT_API int fdt_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dO, const float* lse,
-                         void* dq, void* dk, void* dv, const int64_t* key_mask, int B, int H, int L, int ld, float scale,
-                         float p_drop, const int64_t* seed_off, int mask_compat, cudaStream_t st) {
-    if (L < 1 || L > kT || ld % 8) return -1;
+                         void* dq, void* dk, void* dv, float* dq_acc, const int64_t* key_mask, int B, int H, int L, int ldq,
+                         int ldo, int ldg, float scale, float p_drop, const int64_t* seed_off, int mask_compat, cudaStream_t st) {
+    if (L < 1 || L > kMaxL || ldq % 8 || ldo % 8 || ldg % 8 || B < 1 || H < 1) return -1;
+    const int nkv = (L + kT - 1) / kT;
+    if (nkv > 1 && !dq_acc) return -1;
     CUtensorMap tq, tk, tv, tdo;
     const uint64_t rows = (uint64_t)B * L, cols = (uint64_t)H * kD;
-    if (!encode_rows(&tq, q, rows, cols, ld) || !encode_rows(&tk, k, rows, cols, ld) || !encode_rows(&tv, v, rows, cols, ld) ||
-        !encode_rows(&tdo, dO, rows, cols, ld)) return -4;
+    if (!encode_rows(&tq, q, rows, cols, ldq) || !encode_rows(&tk, k, rows, cols, ldq) || !encode_rows(&tv, v, rows, cols, ldq) ||
+        !encode_rows(&tdo, dO, rows, cols, ldo)) return -4;
     AttnParams p{};
-    p.B = B; p.H = H; p.L = L; p.ld = ld; p.key_mask = key_mask; p.mask_compat = mask_compat; p.scale = scale; p.p_drop = p_drop;
+    p.B = B; p.H = H; p.L = L; p.ldq = ldq; p.ldo = ldo; p.ldg = ldg; p.key_mask = key_mask; p.mask_compat = mask_compat;
+    p.scale = scale; p.p_drop = p_drop;
     p.seed_off = p_drop > 0.f ? seed_off : nullptr; p.lse = const_cast<float*>(lse);
     p.dO = (const __nv_bfloat16*)dO; p.Oin = (const __nv_bfloat16*)o;
     p.dQ = (__nv_bfloat16*)dq; p.dK = (__nv_bfloat16*)dk; p.dV = (__nv_bfloat16*)dv;
-    const int smem = 131072 + 64 + kT * 8 + 1024;
+    p.dQacc = nkv > 1 ? dq_acc : nullptr;
+    if (p.dQacc) {
+        cudaError_t e = cudaMemsetAsync(dq_acc, 0, sizeof(float) * rows * cols, st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    const int smem = kBwdSmem + kAuxBytes + 1024;
     cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    attn_bwd_kernel<<<B * H, kThreads, smem, st>>>(tq, tk, tv, tdo, p);
+    attn_bwd_kernel<<<dim3(nkv, B * H), kThreads, smem, st>>>(tq, tk, tv, tdo, p);
     FDT_CHECK_LAUNCH();
+    if (p.dQacc) {
+        const int64_t n8 = (int64_t)rows * (cols / 8);
+        int blocks = (int)((n8 + 255) / 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        attn_dq_convert_kernel<<<blocks, 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dq, (int64_t)rows, (int)cols, ldg);
+        FDT_CHECK_LAUNCH();
+    }
     return 0;
 }

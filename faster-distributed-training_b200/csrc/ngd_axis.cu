@@ -137,3 +137,30 @@ FDT_API int fdt_ngd_small_axis(const float* X, const float* W, float* Xhat, floa
     }
     return -1;
 }
+
+namespace {
+// K[f] = J Jᵀ, L[f] = J Wᵀ for the short-axis factors (R <= 6, D <= 12): one thread per output element.
+__global__ void small_kl_kernel(const float* __restrict__ J, const float* __restrict__ W, float* __restrict__ K,
+                                float* __restrict__ L, int n, int R, int D) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * R * R) return;
+    const int f = i / (R * R), rc = i - f * R * R, r = rc / R, c = rc - r * R;
+    const float* jr = J + ((size_t)f * R + r) * D;
+    const float* jc = J + ((size_t)f * R + c) * D;
+    const float* wc = W + ((size_t)f * R + c) * D;
+    float k = 0.f, l = 0.f;
+    for (int d = 0; d < D; ++d) { k = fmaf(jr[d], jc[d], k); l = fmaf(jr[d], wc[d], l); }
+    K[i] = k;
+    L[i] = l;
+}
+}  // namespace
+
+// The R x R Fisher statistics of the short-axis factors: K [n,R,R] = J Jᵀ, L [n,R,R] = J Wᵀ (J, W: [n,R,D] contiguous).
+// ref: ngd_optimizer.py:205-218 (two torch.mm per factor).
+FDT_API int fdt_ngd_small_kl(const float* J, const float* W, float* K, float* L, int n, int R, int D, cudaStream_t st) {
+    if (n <= 0 || R < 1 || R > 16 || D < 1 || D > 32) return -1;
+    const int total = n * R * R;
+    small_kl_kernel<<<(total + 127) / 128, 128, 0, st>>>(J, W, K, L, n, R, D);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

@@ -360,17 +360,22 @@ int pick_bn(int N) { return N >= 128 ? 128 : ((N + 15) / 16) * 16; }
 //   X [n, N, D] (x_trans == 0) or the transposed gradient [n, D, N] (x_trans != 0);  W [n, R, D]
 //   H out [n, N, R] = X Wᵀ;  Xhat out (same layout as X) = X − H W;  sums [2n], zero on entry → Σ X², Σ Xhat².
 // Requirements: R % 4 == 0, R <= 128, D % 4 == 0, (x_trans ? N % 4 == 0 : true).
-FDT_API int fdt_ngd_project(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int R,
-                            int x_trans, cudaStream_t st) {
-    if (R % 4 || R > 128 || D % 4 || (x_trans && N % 4) || n <= 0) return -1;
+// Dw: row pitch (in elements) of W — D rounded up to a multiple of 4 with zero padding columns, so that a factor whose axis
+// length is not a multiple of 4 (the 30522-row token embedding) still has 16-byte-aligned rows for TMA.  The gradient X is
+// used where it lies with its true extent D: the rows a padded K loop reaches beyond D are zero-filled by the TMA unit.
+// Only the transposed layout (x_trans, D = number of rows of X) can have D % 4 != 0.
+FDT_API int fdt_ngd_project_ex(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int Dw,
+                               int R, int x_trans, cudaStream_t st) {
+    if (Dw == 0) Dw = D;
+    if (R % 4 || R > 128 || Dw % 4 || Dw < D || (!x_trans && D % 4) || (x_trans && N % 4) || n <= 0) return -1;
     CUtensorMap tA, tB;
     TfParams p{};
     p.batches = n;
     // ---- H[N, R] = X Wᵀ :  M = N, N = R, K = D;  A = X (K-major, or [D][N] when transposed), B = W [R][D] K-major
-    p.M = N; p.N = R; p.K = D; p.BN = pick_bn(R); p.epi = EPI_STORE; p.c_trans = 0; p.a_mn = x_trans ? 1 : 0; p.b_mn = 0;
+    p.M = N; p.N = R; p.K = Dw; p.BN = pick_bn(R); p.epi = EPI_STORE; p.c_trans = 0; p.a_mn = x_trans ? 1 : 0; p.b_mn = 0;
     p.out = H; p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)N * R; p.sums = nullptr;
     if (!encode_operand(&tA, X, p.a_mn, N, D, n, BM)) return -4;
-    if (!encode_operand(&tB, W, 0, R, D, n, p.BN)) return -4;
+    if (!encode_operand(&tB, W, 0, R, Dw, n, p.BN)) return -4;
     int rc = launch(tA, tB, p, 1, st);
     if (rc) return rc;
     // ---- Xhat = X − H W :  M = N, N = D, K = R;  A = H [N][R] K-major, B[n = d, k = r] = W[r][d]: stored [K][rows]
@@ -379,25 +384,53 @@ FDT_API int fdt_ngd_project(const float* X, const float* W, float* H, float* Xha
     if (x_trans) { p.c_trans = 1; p.ldc = N; } else { p.c_trans = 0; p.ldc = D; }
     p.batch_stride_c = (int64_t)N * D;
     if (!encode_operand(&tA, H, 0, N, R, n, BM)) return -4;
-    if (!encode_operand(&tB, W, 1, D, R, n, p.BN)) return -4;
+    if (!encode_operand(&tB, W, 1, Dw, R, n, p.BN)) return -4;
     return launch(tA, tB, p, 1, st);
+}
+
+FDT_API int fdt_ngd_project(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int R,
+                            int x_trans, cudaStream_t st) {
+    return fdt_ngd_project_ex(X, W, H, Xhat, sums, n, N, D, D, R, x_trans, st);
 }
 
 // J[n, R, D] = Hᵀ X with H [n, N, R] and X [n, N, D] (x_trans == 0) or [n, D, N] (x_trans != 0).  J is zeroed here;
 // split-K partial tiles are red.add-ed.  R % 4 == 0, D % 4 == 0, (x_trans ? N % 4 == 0 : true).
-FDT_API int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int N, int D, int R, int x_trans, cudaStream_t st) {
-    if (R % 4 || R > 128 || D % 4 || (x_trans && N % 4) || n <= 0) return -1;
-    cudaMemsetAsync(J, 0, sizeof(float) * (size_t)n * R * D, st);
+// Dw: row pitch of J (see fdt_ngd_project_ex); columns D .. Dw-1 of J come out zero.
+FDT_API int fdt_ngd_stats_j_ex(const float* H, const float* X, float* J, int n, int N, int D, int Dw, int R, int x_trans,
+                               cudaStream_t st) {
+    if (Dw == 0) Dw = D;
+    if (R % 4 || R > 128 || Dw % 4 || Dw < D || (!x_trans && D % 4) || (x_trans && N % 4) || n <= 0) return -1;
+    cudaMemsetAsync(J, 0, sizeof(float) * (size_t)n * R * Dw, st);
     CUtensorMap tA, tB;
     TfParams p{};
     p.batches = n;
     // M = R, N = D, K = N;  A[m = r, k = i] = H[i][r]: stored [K][rows];  B[n = d, k = i] = X[i][d] ([K][rows]) or X'[d][i] (K-major)
     p.M = R; p.N = D; p.K = N; p.BN = pick_bn(D); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = x_trans ? 0 : 1;
-    p.out = J; p.cin = nullptr; p.ldc = D; p.batch_stride_c = (int64_t)R * D; p.sums = nullptr;
+    p.out = J; p.cin = nullptr; p.ldc = Dw; p.batch_stride_c = (int64_t)R * Dw; p.sums = nullptr;
     if (!encode_operand(&tA, H, 1, R, N, n, BM)) return -4;
     if (!encode_operand(&tB, X, p.b_mn, D, N, n, p.BN)) return -4;
     const int tiles = ((D + p.BN - 1) / p.BN) * n;
     int splits = (148 + tiles - 1) / tiles;
+    return launch(tA, tB, p, splits, st);
+}
+
+FDT_API int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int N, int D, int R, int x_trans, cudaStream_t st) {
+    return fdt_ngd_stats_j_ex(H, X, J, n, N, D, D, R, x_trans, st);
+}
+
+// L[n, R, R] = Hᵀ H with H [n, N, R] — the rank-deficient case N <= D of the Fisher statistics (ngd_optimizer.py:215-217),
+// both operands read M/N-major where they lie; the reduction over N is split over CTAs and red.add-ed.  L is zeroed here.
+FDT_API int fdt_ngd_stats_hh(const float* H, float* L, int n, int N, int R, cudaStream_t st) {
+    if (R % 4 || R < 16 || R > 128 || n <= 0 || N <= 0) return -1;
+    cudaMemsetAsync(L, 0, sizeof(float) * (size_t)n * R * R, st);
+    CUtensorMap tA, tB;
+    TfParams p{};
+    p.batches = n;
+    p.M = R; p.N = R; p.K = N; p.BN = pick_bn(R); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = 1;
+    p.out = L; p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)R * R; p.sums = nullptr;
+    if (!encode_operand(&tA, H, 1, R, N, n, BM)) return -4;
+    if (!encode_operand(&tB, H, 1, R, N, n, p.BN)) return -4;
+    const int splits = (148 + n - 1) / n;
     return launch(tA, tB, p, splits, st);
 }
 

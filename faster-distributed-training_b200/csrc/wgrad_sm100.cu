@@ -361,14 +361,15 @@ FDT_API int fdt_conv_wgrad(const void* dy, const void* x, float* dw, int Nb, int
     return fdt_conv_wgrad_ex(dy, x, dw, Nb, H, W, Cin, Cout, ksize, pad, 1, alpha, multicast, st);
 }
 
-// dw[N][K] (fp32) += dY[M,N]ᵀ · X[M,K]   (linear layers).  K % 64 == 0, N % 8 == 0, M % 64 == 0.
+// dw[N][K] (fp32) += dY[M,N]ᵀ · X[M,K]   (linear layers).  K % 64 == 0, N % 8 == 0; any M (the rows a 64-row box reaches
+// beyond M are zero-filled by the TMA unit and contribute nothing).
 FDT_API int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int K, float alpha, int multicast,
                              cudaStream_t st) {
-    if (K % 64 || N % 8 || M % 64) return -1;
+    if (K % 64 || N % 8 || M < 1) return -1;
     CUtensorMap tmDY, tmX;
     if (!encode_pc(&tmDY, dy, N, M) || !encode_pc(&tmX, x, K, M)) return -4;
     WgradParams p{};
-    p.Cout = N; p.Cin = K; p.taps = 1; p.kw = 1; p.pad = 0; p.num_kb = M / 64; p.dw = dw;
+    p.Cout = N; p.Cin = K; p.taps = 1; p.kw = 1; p.pad = 0; p.num_kb = (M + 63) / 64; p.dw = dw;
     p.alpha = alpha; p.multicast = multicast;
     return (K % 128 == 0) ? launch<128, false>(tmDY, tmX, p, st) : launch<64, false>(tmDY, tmX, p, st);
 }

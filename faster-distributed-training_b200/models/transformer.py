@@ -79,13 +79,22 @@ class MultiheadAttention(nn.Module):
         self.d_k, self.h, self.p, self.mask_compat = d_model // h, h, dropout, mask_compat
         self.heads = nn.ModuleList([nn.Linear(d_model, d_model) for _ in range(3)])
         self.output = nn.Linear(d_model, d_model)
+        # The three projections stay separate parameters (checkpoint keys of the reference), but same-shaped tensors are
+        # neighbours in the flat buffers: Q | K | V weights form one [3*d_model, d_model] matrix there, so the projection
+        # is ONE GEMM whose packed output the attention kernel reads in place.
+        self.heads[0].weight._fdt_fuse_with = [self.heads[1].weight, self.heads[2].weight]
+        for l in list(self.heads) + [self.output]:
+            l.weight._fdt_group_unit = 4
 
     def forward(self, x, key_mask=None):
         B, L, _ = x.shape
-        q, k, v = [ops.linear(x, l.weight, l.bias).view(B, L, self.h, self.d_k).transpose(1, 2)
-                   for l in self.heads]
-        o = ops.attention(q, k, v, key_mask, self.p, self.training, self.mask_compat)
-        o = o.transpose(1, 2).reshape(B, L, self.h * self.d_k)
+        o = ops.qkv_attention(x, [l.weight for l in self.heads], [l.bias for l in self.heads], self.h, key_mask,
+                              self.p, self.training, self.mask_compat)
+        if o is None:
+            q, k, v = [ops.linear(x, l.weight, l.bias).view(B, L, self.h, self.d_k).transpose(1, 2)
+                       for l in self.heads]
+            o = ops.attention(q, k, v, key_mask, self.p, self.training, self.mask_compat)
+            o = o.transpose(1, 2).reshape(B, L, self.h * self.d_k)
         return ops.linear(o, self.output.weight, self.output.bias)
 
 

@@ -104,6 +104,15 @@ def attention(q, k, v, key_mask=None, dropout_p=0.0, training=True, mask_compat=
     return ref.attention(q, k, v, key_mask, dropout_p, training, mask_compat)
 
 
+def qkv_attention(x, weights, biases, heads, key_mask=None, dropout_p=0.0, training=True, mask_compat=False):
+    """Fused Q/K/V projection (one GEMM over the back-to-back weights) + attention on the packed result.  Returns
+    [B, L, d_model], or None when the fused path does not apply (CPU, parameters not adjacent in a flat buffer) — the
+    caller then runs the three projections separately."""
+    if use_native(x):
+        return _cu().qkv_attention(x, weights, biases, heads, key_mask, dropout_p if training else 0.0, mask_compat)
+    return None
+
+
 def embed(tokens, token_types, tok_w, pos_w, seg_w, scale):
     if use_native(tok_w):
         return _cu().embed(tokens, token_types, tok_w, pos_w, seg_w, scale)

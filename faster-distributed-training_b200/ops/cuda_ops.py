@@ -554,6 +554,20 @@ def attention(q, k, v, key_mask, dropout_p, training, mask_compat):
     return F.scaled_dot_product_attention(q, k, v, attn_mask=m, dropout_p=dropout_p if training else 0.0)
 
 
+def qkv_attention(x, weights, biases, heads, key_mask, dropout_p, mask_compat):
+    """One GEMM for Q | K | V (weights adjacent in the flat buffer) + attention reading the packed result in place."""
+    if not _native_gemm():
+        return None
+    from . import attention_sm100, linear_sm100
+    B, L, _ = x.shape
+    if L > 512 or weights[0].shape[0] // heads != 64:
+        return None
+    qkv = linear_sm100.linear_fused(x, weights, biases)
+    if qkv is None:
+        return None
+    return attention_sm100.attention_packed(qkv, heads, key_mask, dropout_p, mask_compat)
+
+
 class _Embed(torch.autograd.Function):
     @staticmethod
     def forward(ctx, tokens, types, tok_w, pos_w, seg_w, scale):
@@ -697,6 +711,11 @@ def ngd_small_axis(X: torch.Tensor, W: torch.Tensor, A: int, D: int, B: int, J: 
     return sums[:n], Xhat
 
 
+def ngd_small_kl(J, W, K, L):
+    n, R, D = J.shape
+    call("fdt_ngd_small_kl", J, W, K, L, n, R, D)
+
+
 _commit_cache = {}
 
 
@@ -710,14 +729,15 @@ def ngd_commit_multi(pending):
         for fb in pending:
             R, D = fb.R, fb.D
             for f in range(fb.n):
-                rows.append(struct.pack("<6Q2i", fb.W1.data_ptr() + f * R * D * 4, fb.d1.data_ptr() + f * R * 4,
-                                        fb.rho1.data_ptr() + f * 4, fb.W.data_ptr() + f * R * D * 4,
+                D = fb.Dp
+                rows.append(struct.pack("<6Q2i", fb.W1p.data_ptr() + f * R * D * 4, fb.d1.data_ptr() + f * R * 4,
+                                        fb.rho1.data_ptr() + f * 4, fb.Wp.data_ptr() + f * R * D * 4,
                                         fb.d.data_ptr() + f * R * 4, fb.rho.data_ptr() + f * 4, R, D))
         blob = b"".join(rows)
         dev = torch.empty(len(blob), dtype=torch.uint8, device=pending[0].W.device)
         dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
         flags = torch.zeros(len(rows), dtype=torch.int32, device=dev.device)
-        ent = (dev, len(rows), list(pending), flags, max(fb.R * fb.D for fb in pending))
+        ent = (dev, len(rows), list(pending), flags, max(fb.R * fb.Dp for fb in pending))
         _commit_cache[key] = ent
     call("fdt_ngd_commit_multi", ent[0], ent[1], ent[3], ent[4], launches=3)
 
@@ -736,15 +756,16 @@ def ngd_finish_multi(pending):
         for fb in pending:
             R, D = fb.R, fb.D
             for f in range(fb.n):
+                Dp = fb.Dp            # the kernels walk the padded [R, Dp] storage (padding columns are and stay zero)
                 rows.append(struct.pack(
-                    "<9Q2i", fb.W1.data_ptr() + f * R * D * 4, fb.d1.data_ptr() + f * R * 4, fb.rho1.data_ptr() + f * 4,
-                    fb.W.data_ptr() + f * R * D * 4, fb.d.data_ptr() + f * R * 4, fb.rho.data_ptr() + f * 4,
-                    fb.A.data_ptr() + f * R * R * 4, fb.J.data_ptr() + f * R * D * 4, fb.wc.data_ptr() + f * R * 4, R, D))
+                    "<9Q2i", fb.W1p.data_ptr() + f * R * Dp * 4, fb.d1.data_ptr() + f * R * 4, fb.rho1.data_ptr() + f * 4,
+                    fb.Wp.data_ptr() + f * R * Dp * 4, fb.d.data_ptr() + f * R * 4, fb.rho.data_ptr() + f * 4,
+                    fb.A.data_ptr() + f * R * R * 4, fb.Jp.data_ptr() + f * R * Dp * 4, fb.wc.data_ptr() + f * R * 4, R, Dp))
         blob = b"".join(rows)
         dev = torch.empty(len(blob), dtype=torch.uint8, device=pending[0].W.device)
         dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
         flags = torch.zeros(len(rows), dtype=torch.int32, device=dev.device)
-        ent = (dev, len(rows), list(pending), flags, max(fb.D for fb in pending), max(fb.R * fb.D for fb in pending))
+        ent = (dev, len(rows), list(pending), flags, max(fb.Dp for fb in pending), max(fb.R * fb.Dp for fb in pending))
         _finish_cache[key] = ent
     call("fdt_ngd_finish_multi", ent[0], ent[1], ent[3], ent[4], ent[5], launches=3)
 
@@ -756,30 +777,41 @@ NGD_TF32 = NGD_TC       # old name
 
 
 def ngd_tf32_ok(n, N, D, R, left) -> bool:
-    """Shapes the batched tcgen05 NGD kernels cover; the rest stays on torch.bmm / the short-axis kernel."""
-    return NGD_TC and R % 4 == 0 and 16 <= R <= 128 and D % 4 == 0 and (not left or N % 4 == 0)
+    """Shapes the batched tcgen05 NGD kernels cover; the rest stays on torch.bmm / the short-axis kernel.  With the
+    gradient used transposed (``left``: the preconditioned axis is the tensor's first) D may be any length — W / J are
+    stored with a padded row pitch; otherwise D is the contiguous axis of the gradient itself and must be a multiple of 4."""
+    return NGD_TC and R % 4 == 0 and 16 <= R <= 128 and ((N % 4 == 0) if left else (D % 4 == 0))
 
 
-def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool, sums: Optional[torch.Tensor] = None):
+def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool, sums: Optional[torch.Tensor] = None, D: Optional[int] = None):
     """H = X Wᵀ and X̂ = X − H W for a factor batch on the tensor cores, then the norm-restoring rescale.  ``X`` is
     [n, N, D] (left=False) or the transposed gradient [n, D, N] (left=True), used where it lies.
     Returns (H [n, N, R], out (same layout as X), p0 [n])."""
-    n, R, D = W.shape
+    n, R, Dw = W.shape              # W: padded storage [n, R, Dw] (Dw = D rounded up to 4, zero padding columns)
+    D = Dw if D is None else D
     N = X[0].numel() // D
     H = torch.empty(n, N, R, dtype=torch.float32, device=X.device)
     Xhat = torch.empty_like(X)
     if sums is None:
         sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
-    call("fdt_ngd_project", X, W, H, Xhat, sums, n, N, D, R, int(bool(left)), launches=2)
+    call("fdt_ngd_project_ex", X, W, H, Xhat, sums, n, N, D, Dw, R, int(bool(left)), launches=2)
     call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(N * D))
     return H, Xhat, sums[:n]
 
 
-def ngd_stats_j(H: torch.Tensor, X: torch.Tensor, J: torch.Tensor, left: bool):
-    """J = Hᵀ X on the tensor cores.  H [n, N, R]; X [n, N, D] (left=False) or [n, D, N] (left=True)."""
-    n, R, D = J.shape
+def ngd_stats_j(H: torch.Tensor, X: torch.Tensor, J: torch.Tensor, left: bool, D: Optional[int] = None):
+    """J = Hᵀ X on the tensor cores.  H [n, N, R]; X [n, N, D] (left=False) or [n, D, N] (left=True); J: padded storage
+    [n, R, Dw]."""
+    n, R, Dw = J.shape
+    D = Dw if D is None else D
     N = H.shape[1]
-    call("fdt_ngd_stats_j", H, X, J, n, N, D, R, int(bool(left)))
+    call("fdt_ngd_stats_j_ex", H, X, J, n, N, D, Dw, R, int(bool(left)))
+
+
+def ngd_stats_hh(H: torch.Tensor, L: torch.Tensor):
+    """L [n, R, R] = Hᵀ H (the N <= D case of the Fisher statistics)."""
+    n, N, R = H.shape
+    call("fdt_ngd_stats_hh", H, L, n, N, R)
 
 
 def ngd_stats_kl(J: torch.Tensor, W: torch.Tensor, K: torch.Tensor, L: Optional[torch.Tensor]):

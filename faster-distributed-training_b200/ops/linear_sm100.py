@@ -75,8 +75,12 @@ class _Linear(torch.autograd.Function):
             db = db.view(ctx.bshape)
         if ctx.needs_input_grad[0]:
             wt = _wdgrad(weight, 0)                  # [in, out], produced once per step for all layers
+            if wt is not None and tuple(wt.shape) != (w16.shape[1], N):
+                wt = None                            # the slot holds the fused Q|K|V transpose, not this weight's alone
             dx = g.gemm_nt(gz, wt if wt is not None else w16.t().contiguous(), None, "none")
             if dx is None:
+                from ._lib import note_fallback
+                note_fallback("linear_bwd", "cuBLAS data-gradient GEMM")
                 dx = gz @ w16
             dx = dx.view(ctx.shp).to(ctx.xdtype)
         if ctx.needs_input_grad[1]:
@@ -96,8 +100,77 @@ class _Linear(torch.autograd.Function):
                 if dw is True:
                     dw = None
                 elif dw is None:
+                    from ._lib import note_fallback
+                    note_fallback("linear_bwd", "cuBLAS weight-gradient GEMM")
                     dw = (gz.t() @ x16).float()
         return dx, dw, db, None, None
+
+
+class _LinearFused(torch.autograd.Function):
+    """y = x [W_0; W_1; ...]ᵀ + [b_0; b_1; ...] for k same-shaped Linear layers whose parameters sit back to back in the
+    flat buffers (the Q / K / V projections): ONE forward GEMM with N = k*out, one data-gradient GEMM against the fused
+    transposed weight, one weight-gradient GEMM accumulating into the k adjacent gradient slots, one bias-gradient pass.
+    ``weights`` / ``biases`` are passed so autograd sees them, but every operand is addressed through the flat buffers."""
+
+    @staticmethod
+    def forward(ctx, x, flat, w_off, b_off, k, *params):
+        weights, biases = params[:k], params[k:]
+        N1, K = weights[0].shape
+        N = k * N1
+        shp = x.shape
+        x16 = x.to(BF16).reshape(-1, K).contiguous()
+        w16 = flat.shadow_flat[w_off:w_off + N * K].view(N, K)
+        b32 = flat.param_flat[b_off:b_off + N] if b_off is not None else None
+        out = g.gemm_nt(x16, w16, b32, "none")
+        ctx.save_for_backward(x16, w16)
+        ctx.flat, ctx.w_off, ctx.b_off, ctx.k, ctx.shp, ctx.xdtype, ctx.leader = flat, w_off, b_off, k, shp, x.dtype, weights[0]
+        return out.view(*shp[:-1], N)
+
+    @staticmethod
+    def backward(ctx, gout):
+        from ._lib import call, i64
+        from .cuda_ops import _wdgrad
+        from . import wgrad_sm100
+        x16, w16 = ctx.saved_tensors
+        flat, k = ctx.flat, ctx.k
+        N, K = w16.shape
+        g2 = gout.reshape(-1, N)
+        if g2.dtype != BF16 or not g2.is_contiguous():
+            g2 = g2.to(BF16).contiguous()
+        T = g2.shape[0]
+        if ctx.b_off is not None:         # Σ_rows straight into the k adjacent bias-gradient slots
+            call("fdt_linear_bwd_prep", g2, 0, None, None, flat.grad_flat[ctx.b_off:ctx.b_off + N], i64(T), N, 0)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            wt = _wdgrad(ctx.leader, 0)   # [in, k*out]: the fused transpose made once per step
+            if wt is None or tuple(wt.shape) != (K, N):
+                wt = w16.t().contiguous()
+            dx = g.gemm_nt(g2, wt, None, "none").view(ctx.shp).to(ctx.xdtype)
+        slot = flat.grad_flat[ctx.w_off:ctx.w_off + N * K].view(N, K)
+        if wgrad_sm100.linear_wgrad(g2, x16, slot) is not True:
+            from ._lib import note_fallback
+            note_fallback("linear_bwd", "cuBLAS weight-gradient GEMM (fused QKV)")
+            slot.add_((g2.t() @ x16).float())
+        return (dx, None, None, None, None) + (None,) * (2 * k)
+
+
+def linear_fused(x, weights, biases) -> Optional[torch.Tensor]:
+    """See :class:`_LinearFused`; None when the parameters are not adjacent in one flat buffer (caller falls back)."""
+    f = getattr(weights[0], "_fdt_flat", None)
+    if f is None or not g.available():
+        return None
+    flat = f[0]
+    if flat.shadow_flat is None or weights[0].shape[1] % 64 or weights[0].shape[0] % 64:
+        return None
+    w_off = flat.adjacent_block(list(weights))
+    b_off = None
+    if biases[0] is not None:
+        b_off = flat.adjacent_block(list(biases))
+        if b_off is None:
+            return None
+    if w_off is None or (w_off * 2) % 16 or (b_off is not None and (b_off * 4) % 16):
+        return None
+    return _LinearFused.apply(x, flat, w_off, b_off, len(weights), *weights, *[b for b in biases if b is not None])
 
 
 def linear(x, weight, bias, act, drop_p: float = 0.0) -> Optional[torch.Tensor]:

@@ -62,7 +62,7 @@ def linear_wgrad(gz: torch.Tensor, x16: torch.Tensor, accumulate_into=None, alph
         return None
     M, N = gz.shape
     K = x16.shape[1]
-    if K % 64 or N % 8 or M % 64 or not (gz.is_contiguous() and x16.is_contiguous()):
+    if K % 64 or N % 8 or M < 1 or not (gz.is_contiguous() and x16.is_contiguous()):
         return None
     if accumulate_into is not None:
         dst = accumulate_into if torch.is_tensor(accumulate_into) else _lib.ctypes.c_void_p(int(accumulate_into))

@@ -70,7 +70,13 @@ class FactorBatch:
         self.t = 0
         E_tii = 1.0 / (2.0 + (D + rank) * self.alpha / D)
         W0 = math.sqrt(E_tii) * orthonormal_special(rank, D, dtype, device)
-        self.W = W0.unsqueeze(0).repeat(n, 1, 1).contiguous()
+        # Row pitch Dp = D rounded up to 4 (zero padding columns): the tensor-core kernels need 16-byte-aligned rows, and
+        # an axis such as the 30522-row token embedding is not a multiple of 4.  ``W`` is the [n, R, D] view everything
+        # else uses; ``Wp`` the padded storage the native kernels address.
+        self.Dp = D if D < 32 else (D + 3) // 4 * 4        # short axes never reach the tensor-core kernels
+        self.Wp = torch.zeros(n, rank, self.Dp, dtype=dtype, device=device)
+        self.W = self.Wp[:, :, :D]
+        self.W.copy_(W0.unsqueeze(0))
         self.d = torch.full((n, rank), EPSILON, dtype=dtype, device=device)
         self.rho = torch.full((n,), EPSILON, dtype=dtype, device=device)
 
@@ -149,11 +155,13 @@ def _alloc_stats(fb: FactorBatch):
     """Persistent work buffers of a factor batch's Fisher refresh (stable addresses for graph replay)."""
     n, R, D = fb.n, fb.R, fb.D
     kw = dict(dtype=fb.W.dtype, device=fb.W.device)
-    fb.J = torch.empty(n, R, D, **kw)
+    fb.Jp = torch.zeros(n, R, fb.Dp, **kw)
+    fb.J = fb.Jp[:, :, :D]
     fb.K = torch.empty(n, R, R, **kw)
     fb.L = torch.empty(n, R, R, **kw)
     fb.A = torch.empty(n, R, R, **kw)
-    fb.W1 = torch.empty(n, R, D, **kw)
+    fb.W1p = torch.zeros(n, R, fb.Dp, **kw)
+    fb.W1 = fb.W1p[:, :, :D]
     fb.wc = torch.empty(n, R, **kw)
     fb.d1 = torch.empty(n, R, **kw)
     fb.rho1 = torch.empty(n, **kw)
@@ -169,12 +177,12 @@ def _statistics(fb: FactorBatch, Xm: torch.Tensor, left: bool, H: torch.Tensor):
         # H is [n, N, R] for both layouts (tcgen05 path): J on the tensor cores, L / K are R x R
         from .. import ops
         cu = ops._cu()
-        cu.ngd_stats_j(H, Xm, fb.J, left)
+        cu.ngd_stats_j(H, Xm, fb.Jp, left, fb.D)
         if fb.N > fb.D:
-            cu.ngd_stats_kl(fb.J, W, fb.K, fb.L)          # K = J Jᵀ, L = J Wᵀ
+            cu.ngd_stats_kl(fb.Jp, fb.Wp, fb.K, fb.L)     # K = J Jᵀ, L = J Wᵀ
         else:
-            torch.bmm(H.transpose(1, 2), H, out=fb.L)
-            cu.ngd_stats_kl(fb.J, W, fb.K, None)
+            cu.ngd_stats_hh(H, fb.L)                      # L = Hᵀ H
+            cu.ngd_stats_kl(fb.Jp, fb.Wp, fb.K, None)
         return
     S = _split_factor(fb.N)
     if left:   # Xm: [n, D, N], H: [n, R, N];  J = H Xᵀ reduces over N
@@ -274,22 +282,33 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
         H = torch.bmm(Xm, W.transpose(1, 2))
         return H, torch.baddbmm(Xm, H, W, alpha=-1.0)
 
+    tc = False
+    if native:
+        from .. import ops
+        tc = ops._cu().ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, left)
     if fb.t == 0:
         # warm start: 3 refreshes on the same gradient (ngd_optimizer.py:356-376)
-        if p0 is None:
-            p0 = (Xm * Xm).sum((1, 2))
-        fb._h_rows = False
-        for _ in range(3):
-            H, _ = project()
-            _refresh(fb, Xm, left, H, p0)
+        if tc:          # same tensor-core kernels as the steady state: no library GEMM anywhere in the optimizer
+            from .. import ops
+            fb._h_rows = True
+            for _ in range(3):
+                H, _, p0w = ops._cu().ngd_project(Xc, fb.Wp, left, None, fb.D)
+                _refresh(fb, Xc, left, H, p0w)
+        else:
+            if p0 is None:
+                p0 = (Xm * Xm).sum((1, 2))
+            fb._h_rows = False
+            for _ in range(3):
+                H, _ = project()
+                _refresh(fb, Xm, left, H, p0)
     updating = fb.updating()
     fb.t += 1
     if native:
         from .. import ops
         cu = ops._cu()
-        if cu.ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, left):
+        if tc:
             fb._h_rows = True
-            H, out, p0 = cu.ngd_project(Xc, fb.W, left, getattr(fb, "_sums", None))   # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale
+            H, out, p0 = cu.ngd_project(Xc, fb.Wp, left, getattr(fb, "_sums", None), fb.D)   # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale
             if updating:
                 if pending is None:
                     _refresh(fb, Xc, left, H, p0)
@@ -352,8 +371,7 @@ def precondition_small_axis(fb: FactorBatch, d_p: torch.Tensor, pa: int, pending
         _alloc_stats(fb)
     p0, out = cu.ngd_small_axis(X, fb.W, A, fb.D, B, fb.J if updating else None)
     if updating:
-        torch.bmm(fb.J, fb.W.transpose(1, 2), out=fb.L)
-        torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+        cu.ngd_small_kl(fb.J, fb.W, fb.K, fb.L)      # K = J Jᵀ, L = J Wᵀ in one small launch
         fb.tr.copy_(p0)
         if pending is None:
             A_, w_coeff, d1, rho1 = _fisher_update(fb, fb.J, fb.K, fb.L, fb.tr)
@@ -815,5 +833,6 @@ class NGD(Optimizer):
                     fb = FactorBatch(len(sg.params), N, D, group["alpha"], group["rank"],
                                      group["update_period"], group["eta"], dt, dev)
                     fb.t = int(f["t"])
-                    fb.W, fb.d, fb.rho = f["W"].to(dev, dt), f["d"].to(dev, dt), f["rho"].to(dev, dt)
+                    fb.W.copy_(f["W"].to(dev, dt))          # into the padded storage
+                    fb.d, fb.rho = f["d"].to(dev, dt), f["rho"].to(dev, dt)
                     sg.factors[int(axis)] = fb

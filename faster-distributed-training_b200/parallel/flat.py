@@ -74,6 +74,9 @@ class FlatParameters:
             cut: "OrderedDict[Tuple, List[torch.nn.Parameter]]" = OrderedDict()
             for s, ps in buckets.items():
                 per = max(1, target // max(1, ps[0].numel()))
+                unit = int(getattr(ps[0], "_fdt_group_unit", 1))       # keep tensors that are used as one fused operand
+                if unit > 1 and len(ps) % unit == 0:                   # (Q/K/V projection weights) in the same part
+                    per = max(unit, per // unit * unit)
                 if len(ps) <= per:
                     cut[s] = ps
                 else:
@@ -211,11 +214,19 @@ class FlatParameters:
         1: col2im dgrad) get a slot in one bf16 buffer that :meth:`refresh_dgrad_shadow` fills from the shadow."""
         import struct
         ents, total = [], 0
+        fused_followers = set()
+        for p in self.params:
+            mates = getattr(p, "_fdt_fuse_with", None)
+            if mates and p.dim() == 2 and self.adjacent_block([p] + list(mates)) is not None:
+                fused_followers.update(id(m) for m in mates)
         for idx, p in enumerate(self.params):
             mode = getattr(p, "_fdt_dgrad_mode", None)
-            if mode is None or p.dim() not in (2, 4):
+            if mode is None or p.dim() not in (2, 4) or id(p) in fused_followers:
                 continue
             O, I = p.shape[0], p.shape[1]
+            mates = getattr(p, "_fdt_fuse_with", None)
+            if mates and all(id(m) in fused_followers for m in mates):
+                O = O * (1 + len(mates))            # Q|K|V weights back to back = one [3*out, in] matrix → one [in, 3*out] transpose
             T = p.shape[2] * p.shape[3] if p.dim() == 4 else 1
             if O % 8 or I % 8:
                 continue
@@ -282,6 +293,19 @@ class FlatParameters:
         lo = min(self._index[i][0].offset + self._index[i][1] * self._index[i][0].numel for i in idxs)
         hi = max(self._index[i][0].offset + (self._index[i][1] + 1) * self._index[i][0].numel for i in idxs)
         return lo, hi
+
+    def adjacent_block(self, params) -> Optional[int]:
+        """Element offset of ``params[0]`` when ``params`` (same shape) sit back to back in the flat buffers, i.e. form
+        ONE [k * rows, ...] matrix in the parameter, gradient and bf16 shadow buffers alike; None otherwise."""
+        try:
+            ent = [self._index[p._fdt_flat[1]] for p in params]
+        except (AttributeError, KeyError, TypeError):
+            return None
+        g0, i0 = ent[0]
+        for k, (g, i) in enumerate(ent):
+            if g is not g0 or i != i0 + k:
+                return None
+        return g0.offset + i0 * g0.numel
 
     @staticmethod
     def common_span(params) -> Optional[Tuple["FlatParameters", int, int]]:

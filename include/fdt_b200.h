@@ -163,14 +163,16 @@ int fdt_im2col(const void* x, void* A, int N, int H, int W, int C, int k, int st
 int fdt_col2im(const void* dA, void* dx, int N, int H, int W, int C, int k, int stride, int pad, int Ho, int Wo, int Kp,
                cudaStream_t st);
 
-/* ---- fused attention, csrc/attention_sm100.cu (one CTA per batch*head; L <= 128, d_head = 64) -----------------
- * ref: ScaledDotProduct / MultiheadAttention (transformer.py:180-227).  q,k,v,o,dO,dq,dk,dv: bf16 [B*L, H*64] with row stride ld. */
+/* ---- fused attention, csrc/attention_sm100.cu (L <= 512, d_head = 64; KV-tile loop with online softmax) ---------
+ * ref: ScaledDotProduct / MultiheadAttention (transformer.py:180-227).  q,k,v: bf16 [B*L, H*64] with row stride ldq (column
+ * slices of a packed QKV matrix are fine); o, dO: row stride ldo; dq,dk,dv: row stride ldg; dq_acc: fp32 [B*L, H*64] work
+ * buffer, needed when L > 128. */
 int fdt_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const int64_t* key_mask,
-                 int B, int H, int L, int ld, float scale, float p_drop, const int64_t* seed_off, int mask_compat,
+                 int B, int H, int L, int ldq, int ldo, float scale, float p_drop, const int64_t* seed_off, int mask_compat,
                  cudaStream_t st);
 int fdt_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dO, const float* lse,
-                 void* dq, void* dk, void* dv, const int64_t* key_mask, int B, int H, int L, int ld, float scale,
-                 float p_drop, const int64_t* seed_off, int mask_compat, cudaStream_t st);
+                 void* dq, void* dk, void* dv, float* dq_acc, const int64_t* key_mask, int B, int H, int L, int ldq, int ldo,
+                 int ldg, float scale, float p_drop, const int64_t* seed_off, int mask_compat, cudaStream_t st);
 
 /* ---- input / head kernels, csrc/input_head.cu ------------------------------------------------------------------
  * ref: loader transforms + mixup_data(_meta) (resnet50_test.py:301-318,355-401); AdaptiveAvgPool2d + Linear (resnet.py:279-281) */
@@ -196,12 +198,23 @@ int fdt_ngd_finish_multi(const void* descs, int count, int* flags, int max_D, in
 int fdt_ngd_project(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int R,
                     int x_trans, cudaStream_t st);
 int fdt_ngd_stats_j(const float* H, const float* X, float* J, int n, int N, int D, int R, int x_trans, cudaStream_t st);
+/* padded-pitch forms: W and J are [n, R, Dw] with Dw = D rounded up to 4 and zero padding columns, so that an axis length that
+ * is not a multiple of 4 (x_trans only: the 30522-row token embedding) runs on the tensor cores too; Dw == 0 means D.
+ * fdt_ngd_stats_hh: L [n,R,R] = H^T H (the N <= D case of ngd_optimizer.py:215-217). */
+int fdt_ngd_project_ex(const float* X, const float* W, float* H, float* Xhat, float* sums, int n, int N, int D, int Dw,
+                       int R, int x_trans, cudaStream_t st);
+int fdt_ngd_stats_j_ex(const float* H, const float* X, float* J, int n, int N, int D, int Dw, int R, int x_trans,
+                       cudaStream_t st);
+int fdt_ngd_stats_hh(const float* H, float* L, int n, int N, int R, cudaStream_t st);
 /* K [n,R,R] = J J^T and (L != NULL) L [n,R,R] = J W^T on the tensor cores (zeroed inside; 16 <= R <= 128, R % 4 == 0, D % 4 == 0) */
 int fdt_ngd_stats_kl(const float* J, const float* W, float* K, float* L, int n, int D, int R, cudaStream_t st);
 /* short axis (2 <= D <= 12, R == (D+1)/2) of the [n, A, D, B] view of a gradient: x̂ = x − Wᵀ(W x) in place of two
  * inner-dimension-3 SGEMMs and a transpose; sums [2n] = Σx², Σx̂²; J [n, R, D] = Σ h xᵀ or NULL.  csrc/ngd_axis.cu */
 int fdt_ngd_small_axis(const float* X, const float* W, float* Xhat, float* sums, float* J, int n, int64_t A, int D,
                        int64_t B, int R, cudaStream_t st);
+
+/* K [n,R,R] = J J^T and L [n,R,R] = J W^T of the short-axis factors (R <= 16, D <= 32; J, W [n,R,D] contiguous) */
+int fdt_ngd_small_kl(const float* J, const float* W, float* K, float* L, int n, int R, int D, cudaStream_t st);
 
 /* ---- in-kernel NVLink collectives over a symmetric heap, csrc/comm.cu -------------------------------------------
  * ref: DDP bucket all-reduce (resnet50_test.py:716), FSDP all-gather / reduce-scatter (transformer_test.py:387-392).

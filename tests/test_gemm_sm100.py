@@ -272,3 +272,72 @@ def test_resnet50_step_takes_no_library_fallback():
     assert torch.isfinite(loss)
     assert dict(_lib.FALLBACKS.by_name) == before
     assert torch.isfinite(eng.flat.grad_flat).all()
+
+
+# ----------------------------------------------------------------------------- attention beyond one tile, packed QKV
+@pytest.mark.parametrize("B,H,L", [(3, 8, 77), (2, 8, 128), (3, 4, 200), (2, 8, 384), (2, 8, 512), (5, 2, 130)])
+@pytest.mark.parametrize("masked", [False, True])
+def test_attention_long_sequences(B, H, L, masked):
+    """KV-tile loop with online softmax (forward) and per-key-tile dK/dV + accumulated dQ (backward) vs the fp32 oracle,
+    at the reference's sequence range (maxlen 512, padding='longest': transformer.py:35, transformer_test.py:97)."""
+    from fdt import ops
+    from fdt.ops import attention_sm100 as at
+    torch.manual_seed(17)
+    D = 64
+
+    def mk():
+        return torch.randn(B, L, H * D, device="cuda").bfloat16().view(B, L, H, D).transpose(1, 2).requires_grad_(True)
+
+    q, k, v = mk(), mk(), mk()
+    km = None
+    if masked:
+        lens = torch.randint(L // 3, L + 1, (B,), device="cuda")
+        km = (torch.arange(L, device="cuda")[None, :] < lens[:, None]).long()
+    g = torch.randn(B, H, L, D, device="cuda").bfloat16()
+    out = at.attention(q, k, v, km, 0.0, False)
+    assert out is not None and out.shape == (B, H, L, D)
+    out.backward(g)
+    qr, kr, vr = [t.detach().float().requires_grad_(True) for t in (q, k, v)]
+    ref = ops.ref.attention(qr, kr, vr, km, 0.0, False, False)
+    ref.backward(g.float())
+    assert _rel(out, ref) < 1e-2, _rel(out, ref)
+    for name, a, b in (("dq", q.grad, qr.grad), ("dk", k.grad, kr.grad), ("dv", v.grad, vr.grad)):
+        assert _rel(a, b) < 2e-2, (name, _rel(a, b))
+
+
+@pytest.mark.parametrize("B,L", [(4, 128), (3, 200), (2, 512)])
+def test_attention_packed_qkv(B, L):
+    """The packed [B, L, 3*h*d] form (output of the fused Q/K/V GEMM) equals attention on the three slices."""
+    from fdt import ops
+    from fdt.ops import attention_sm100 as at
+    torch.manual_seed(18)
+    H, D = 8, 64
+    qkv = torch.randn(B, L, 3 * H * D, device="cuda").bfloat16().requires_grad_(True)
+    lens = torch.randint(L // 2, L + 1, (B,), device="cuda")
+    km = (torch.arange(L, device="cuda")[None, :] < lens[:, None]).long()
+    g = torch.randn(B, L, H * D, device="cuda").bfloat16()
+    o = at.attention_packed(qkv, H, km, 0.0, False)
+    assert o is not None and o.shape == (B, L, H * D)
+    o.backward(g)
+    ref_in = qkv.detach().float().requires_grad_(True)
+    q, k, v = [t.reshape(B, L, H, D).transpose(1, 2) for t in ref_in.split(H * D, dim=-1)]
+    ref = ops.ref.attention(q, k, v, km, 0.0, False, False).transpose(1, 2).reshape(B, L, H * D)
+    ref.backward(g.float())
+    assert _rel(o, ref) < 1e-2, _rel(o, ref)
+    assert _rel(qkv.grad, ref_in.grad) < 2e-2, _rel(qkv.grad, ref_in.grad)
+
+
+def test_attention_dropout_long_sequence_consistent():
+    """Dropout masks are regenerated identically in the backward pass for multi-tile sequences."""
+    from fdt.ops import attention_sm100 as at
+    torch.manual_seed(19)
+    B, H, L, D = 2, 4, 300, 64
+    mk = lambda: torch.randn(B, L, H * D, device="cuda").bfloat16().view(B, L, H, D).transpose(1, 2)
+    q, k = mk(), mk()
+    vv = mk().clone().requires_grad_(True)
+    o = at.attention(q, k, vv, None, 0.1, False)
+    o.float().sum().backward()
+    col = vv.grad.float()[..., 0]
+    assert torch.isfinite(vv.grad.float()).all()
+    assert torch.allclose(vv.grad.float(), col.unsqueeze(-1).expand_as(vv.grad), rtol=2e-2, atol=2e-2)
+    assert abs(col.sum().item() / (B * H * L) - 1.0) < 0.05

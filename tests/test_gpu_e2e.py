@@ -149,3 +149,35 @@ def test_cli_transformer_gpu(tmp_path):
     out = _run_cli("transformer_test.py", "--batch_size", "32", "--ngd", "--epoch", "1", "--steps_per_epoch", "14",
                    "--eval_steps", "2", "--cuda_graph", "--ckpt_dir", str(tmp_path))
     assert "Loss" in out or "loss" in out
+
+
+def test_transformer_variable_length_epoch_is_native():
+    """AG_NEWS-shape batches padded to the longest sequence (up to 512 tokens): every step stays on the native kernels
+    (no SDPA / cuBLAS fallback), with the fused Q|K|V projection active."""
+    import torch
+    from fdt.models.transformer import Transformer
+    from fdt.ops import _lib
+    from fdt.parallel.ddp import DataParallelEngine
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    eng = DataParallelEngine(Transformer(4, 30522).to(dev))
+    before = _lib.FALLBACKS.count
+    n_fused0 = _lib.LAUNCHES.by_name.get("fdt_attn_fwd", 0)
+    _lib.set_strict(True)
+    try:
+        for L in (77, 200, 512):
+            B = 8
+            tok = torch.randint(1000, 30522, (B, L), device=dev)
+            lens = torch.randint(L // 4, L + 1, (B,), device=dev)
+            mask = (torch.arange(L, device=dev)[None] < lens[:, None]).long()
+            eng.zero_grad()
+            logits, perm, lam = eng(tok * mask, torch.zeros_like(tok), None, mask)
+            loss = logits.float().square().mean()
+            loss.backward()
+            assert torch.isfinite(loss)
+    finally:
+        _lib.set_strict(False)
+    torch.cuda.synchronize()
+    assert _lib.FALLBACKS.count == before
+    assert _lib.LAUNCHES.by_name.get("fdt_attn_fwd", 0) - n_fused0 == 3 * 6
+    assert torch.isfinite(eng.flat.grad_flat).all()
