@@ -148,6 +148,15 @@ class ResNetStep:
             with torch.no_grad():
                 correct = mx.mixup_correct(logits, ya, yb, lam)
             return loss, correct
+        if self.meta is not None and images.dtype == torch.uint8 and ops.use_native(images):
+            # meta-mixup: one kernel for augmentation + per-sample sigmoid(theta) blend, dtheta from its backward kernel
+            x, ya, yb, lam = self.meta.fused_from_uint8(images, targets, cifar_data.MEAN, cifar_data.STD)
+            lam = lam.reshape(-1)
+            logits = engine(x)
+            loss = mx.mixup_criterion(logits, ya, yb, lam)
+            with torch.no_grad():
+                correct = mx.mixup_correct(logits, ya, yb, lam)
+            return loss, correct
         x = cifar_data.gpu_transform(images, train=True) if images.dtype == torch.uint8 else images
         if self.meta is not None:
             x, ya, yb, lam = self.meta(x, targets)

@@ -13,7 +13,7 @@ using namespace fdt;
 
 namespace {
 
-struct AugParams { float mean[3], inv_std[3]; int H, W, pad, train; };
+struct AugParams { float mean[3], inv_std[3]; int H, W, pad, train, lam_mode; };
 
 __device__ __forceinline__ void sample_aug(const Philox& rng, uint64_t off, int b, int pad, int& dx, int& dy, int& flip) {
     uint4 r = rng((uint64_t)b, off);
@@ -42,7 +42,8 @@ input_aug_mixup_kernel(const uint8_t* __restrict__ x, const int64_t* __restrict_
         sample_aug(rng, (uint64_t)seed_off[1], b, a.pad, dx0, dy0, f0);
         sample_aug(rng, (uint64_t)seed_off[1], pb, a.pad, dx1, dy1, f1);
     }
-    const float l = lam ? (lam_n == 1 ? lam[0] : lam[b]) : 1.f;
+    float l = lam ? (lam_n == 1 ? lam[0] : lam[b]) : 1.f;
+    if (a.lam_mode == 1 && lam) l = 1.f / (1.f + __expf(-l));          // meta-mixup: the array holds theta, lam = sigmoid(theta)
     const uint8_t* i0 = x + (size_t)b * npix * 3;
     const uint8_t* i1 = x + (size_t)pb * npix * 3;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix * 3; i += gridDim.x * blockDim.x) {
@@ -50,6 +51,43 @@ input_aug_mixup_kernel(const uint8_t* __restrict__ x, const int64_t* __restrict_
         float v = fetch(i0, h, w, c, dx0, dy0, f0, a);
         if (perm) v = l * v + (1.f - l) * fetch(i1, h, w, c, dx1, dy1, f1, a);
         out[(size_t)b * npix * 3 + i] = __float2bfloat16(v);
+    }
+}
+
+// Backward of the blend w.r.t. the per-sample mixing weight (meta-mixup, resnet50_test.py:388-401: lam_b = sigmoid(theta_b)):
+//   dlam[b] += Σ_pixels g[b, ·] · (v0 − v1),   v0 / v1 = the augmented, normalised partners recomputed from the uint8 images
+// with the forward's (seed, offset) — nothing of the forward is stored.  lam_mode 1: chain through the sigmoid
+// (dtheta[b] += dlam · lam (1 − lam), lam = sigmoid(lamsrc[b])); lam_mode 0: plain dlam.
+__global__ void __launch_bounds__(256)
+input_aug_mixup_bwd_kernel(const uint8_t* __restrict__ x, const int64_t* __restrict__ perm, const float* __restrict__ lamsrc,
+                           int lam_mode, const int64_t* __restrict__ seed_off, const __nv_bfloat16* __restrict__ g,
+                           float* __restrict__ dlam, const AugParams a) {
+    const int b = blockIdx.y;
+    const int npix = a.H * a.W;
+    const int pb = (int)perm[b];
+    int dx0 = 0, dy0 = 0, f0 = 0, dx1 = 0, dy1 = 0, f1 = 0;
+    if (a.train) {
+        Philox rng((uint64_t)seed_off[0]);
+        sample_aug(rng, (uint64_t)seed_off[1], b, a.pad, dx0, dy0, f0);
+        sample_aug(rng, (uint64_t)seed_off[1], pb, a.pad, dx1, dy1, f1);
+    }
+    const uint8_t* i0 = x + (size_t)b * npix * 3;
+    const uint8_t* i1 = x + (size_t)pb * npix * 3;
+    float acc = 0.f;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix * 3; i += gridDim.x * blockDim.x) {
+        const int c = i % 3, p = i / 3, w = p % a.W, h = p / a.W;
+        const float d = fetch(i0, h, w, c, dx0, dy0, f0, a) - fetch(i1, h, w, c, dx1, dy1, f1, a);
+        acc += __bfloat162float(g[(size_t)b * npix * 3 + i]) * d;
+    }
+    acc = warp_sum(acc);
+    __shared__ float red[8];
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int i = 0; i < 8; ++i) t += red[i];
+        if (lam_mode == 1) { const float l = 1.f / (1.f + __expf(-lamsrc[b])); t *= l * (1.f - l); }
+        atomicAdd(dlam + b, t);
     }
 }
 
@@ -105,15 +143,37 @@ pool_fc_bwd_kernel(const float* __restrict__ dlogits, const float* __restrict__ 
 
 // x: uint8 [B,H,W,3]; perm: int64 [B] or null (no mixup); lam: fp32 [1] or [B] or null; seed_off: int64 (seed, offset),
 // required when train != 0; out: bf16 [B,H,W,3].
-FDT_API int fdt_input_aug_mixup(const void* x, const int64_t* perm, const float* lam, int lam_n, const int64_t* seed_off,
-                                void* out, int B, int H, int W, int pad, int train, const float* mean3, const float* std3,
-                                cudaStream_t st) {
+FDT_API int fdt_input_aug_mixup_ex(const void* x, const int64_t* perm, const float* lam, int lam_n, int lam_mode,
+                                   const int64_t* seed_off, void* out, int B, int H, int W, int pad, int train,
+                                   const float* mean3, const float* std3, cudaStream_t st) {
     AugParams a;
     for (int c = 0; c < 3; ++c) { a.mean[c] = mean3[c]; a.inv_std[c] = 1.f / std3[c]; }
-    a.H = H; a.W = W; a.pad = pad; a.train = train;
+    a.H = H; a.W = W; a.pad = pad; a.train = train; a.lam_mode = lam_mode;
     if (train && !seed_off) return -1;
     dim3 grid((H * W * 3 + 255) / 256, B);
     input_aug_mixup_kernel<<<grid, 256, 0, st>>>((const uint8_t*)x, perm, lam, lam_n, seed_off, (__nv_bfloat16*)out, B, a);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+FDT_API int fdt_input_aug_mixup(const void* x, const int64_t* perm, const float* lam, int lam_n, const int64_t* seed_off,
+                                void* out, int B, int H, int W, int pad, int train, const float* mean3, const float* std3,
+                                cudaStream_t st) {
+    return fdt_input_aug_mixup_ex(x, perm, lam, lam_n, 0, seed_off, out, B, H, W, pad, train, mean3, std3, st);
+}
+
+// dlam [B] (+=, per-sample; zero it first for a fresh gradient): gradient of the blended batch w.r.t. the mixing weights.
+// g: bf16 [B, H, W, 3] = dL/d(out of fdt_input_aug_mixup_ex); seed_off: the SAME (seed, offset) pair the forward used.
+FDT_API int fdt_input_aug_mixup_bwd(const void* x, const int64_t* perm, const float* lamsrc, int lam_mode,
+                                    const int64_t* seed_off, const void* g, float* dlam, int B, int H, int W, int pad, int train,
+                                    const float* mean3, const float* std3, cudaStream_t st) {
+    if (!perm || !lamsrc || !dlam || (train && !seed_off)) return -1;
+    AugParams a;
+    for (int c = 0; c < 3; ++c) { a.mean[c] = mean3[c]; a.inv_std[c] = 1.f / std3[c]; }
+    a.H = H; a.W = W; a.pad = pad; a.train = train; a.lam_mode = lam_mode;
+    dim3 grid(2, B);
+    input_aug_mixup_bwd_kernel<<<grid, 256, 0, st>>>((const uint8_t*)x, perm, lamsrc, lam_mode, seed_off,
+                                                     (const __nv_bfloat16*)g, dlam, a);
     FDT_CHECK_LAUNCH();
     return 0;
 }

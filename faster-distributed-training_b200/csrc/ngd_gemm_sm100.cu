@@ -376,7 +376,23 @@ FDT_API int fdt_ngd_project_ex(const float* X, const float* W, float* H, float* 
     p.out = H; p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)N * R; p.sums = nullptr;
     if (!encode_operand(&tA, X, p.a_mn, N, D, n, BM)) return -4;
     if (!encode_operand(&tB, W, 0, R, Dw, n, p.BN)) return -4;
-    int rc = launch(tA, tB, p, 1, st);
+    // A long reduction with few output tiles (the token embedding's first axis: N = 512 rows, K = 30522) would run on a
+    // handful of CTAs: split K over the SMs and red.add the partial tiles into a zeroed H instead.
+    int splits = 1;
+    {
+        const int tiles = ((N + BM - 1) / BM) * ((R + p.BN - 1) / p.BN) * n;
+        const int num_kb = (Dw + BKE - 1) / BKE;
+        if (tiles < 74 && num_kb >= 64) {
+            splits = 148 / tiles;
+            if (splits > num_kb / 8) splits = num_kb / 8;
+            if (splits < 1) splits = 1;
+        }
+    }
+    if (splits > 1) {
+        cudaMemsetAsync(H, 0, sizeof(float) * (size_t)n * N * R, st);
+        p.epi = EPI_RED;
+    }
+    int rc = launch(tA, tB, p, splits, st);
     if (rc) return rc;
     // ---- Xhat = X − H W :  M = N, N = D, K = R;  A = H [N][R] K-major, B[n = d, k = r] = W[r][d]: stored [K][rows]
     p.M = N; p.N = D; p.K = R; p.BN = pick_bn(D); p.epi = EPI_SUB; p.a_mn = 0; p.b_mn = 1;

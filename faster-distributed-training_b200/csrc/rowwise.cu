@@ -197,7 +197,8 @@ __global__ void dropout_bwd_kernel(const float* __restrict__ g, T* __restrict__ 
 // dlogits = (softmax − lam·1[y_a] − (1−lam)·1[y_b]) / B ; correct += Σ_i lam·[argmax==y_a] + (1−lam)·[argmax==y_b]
 __global__ void mixup_ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ ya,
                                 const int64_t* __restrict__ yb, const float* __restrict__ lam, int lam_n,
-                                float* __restrict__ out /*[2]: loss, correct*/, float* __restrict__ dlogits, int B, int C) {
+                                float* __restrict__ out /*[2]: loss, correct*/, float* __restrict__ dlogits,
+                                float* __restrict__ dlam, int B, int C) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     float loss = 0.f, corr = 0.f;
     if (i < B) {
@@ -211,6 +212,7 @@ __global__ void mixup_ce_kernel(const float* __restrict__ logits, const int64_t*
         const int a = (int)ya[i], b = (int)yb[i];
         loss = (l * (lse - z[a]) + (1.f - l) * (lse - z[b])) / B;
         corr = l * (am == a) + (1.f - l) * (am == b);
+        if (dlam) dlam[i] = (z[b] - z[a]) / B;            // d/dlam of lam·(lse − z_a) + (1 − lam)·(lse − z_b), per-sample lam
         if (dlogits) {
             float* d = dlogits + (int64_t)i * C;
             const float invB = 1.f / B;
@@ -420,7 +422,119 @@ FDT_API int fdt_dropout_bwd(const float* g, void* dx, int dx_is_bf16, int64_t n,
 // out[2] must be zero on entry.
 FDT_API int fdt_mixup_ce(const float* logits, const int64_t* ya, const int64_t* yb, const float* lam, int lam_n,
                          float* out, float* dlogits, int B, int C, cudaStream_t st) {
-    mixup_ce_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ya, yb, lam, lam_n, out, dlogits, B, C);
+    mixup_ce_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ya, yb, lam, lam_n, out, dlogits, nullptr, B, C);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// same, plus dlam [B] = d loss / d lam_i for a per-sample (learnable) mixing weight (lam_n == B)
+FDT_API int fdt_mixup_ce_ex(const float* logits, const int64_t* ya, const int64_t* yb, const float* lam, int lam_n,
+                            float* out, float* dlogits, float* dlam, int B, int C, cudaStream_t st) {
+    if (dlam && lam_n != B) return -1;
+    mixup_ce_kernel<<<(B + 127) / 128, 128, 0, st>>>(logits, ya, yb, lam, lam_n, out, dlogits, dlam, B, C);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// ------------------------------------------------------------------ pooled classification head (transformer.py:61-84, 94-101)
+// CLS gather, pooled-vector dropout and manifold mixup as three small kernels around the two tcgen05 GEMMs of the head
+// (the reference: index + Linear + tanh + dropout + randperm gather + lerp = ~10 ATen launches each way).
+namespace {
+
+// cls[b, :] = bf16(x[b, 0, :])            x fp32 [B, L, D]
+__global__ void cls_gather_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ cls, int B, int L, int D) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;          // one thread per 4 elements
+    if (i >= B * (D / 4)) return;
+    const int b = i / (D / 4), c = (i - b * (D / 4)) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(x + ((int64_t)b * L) * D + c);
+    *reinterpret_cast<uint2*>(cls + (int64_t)b * D + c) = make_uint2(f2_to_bf2(v.x, v.y), f2_to_bf2(v.z, v.w));
+}
+// dx[b, l, :] = (l == 0) ? g[b, :] : 0     dx fp32 [B, L, D] (the gradient buffer the residual stream then accumulates into)
+__global__ void cls_scatter_kernel(const float* __restrict__ g, float* __restrict__ dx, int B, int L, int D) {
+    const int64_t n4 = (int64_t)B * L * (D / 4);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / (D / 4);
+        const int c = (int)(i - row * (D / 4)) * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row % L == 0) v = *reinterpret_cast<const float4*>(g + (row / L) * D + c);
+        *reinterpret_cast<float4*>(dx + row * D + c) = v;
+    }
+}
+__device__ __forceinline__ float head_keep(const Philox& rng, uint64_t off, int row, int c, int D, float p, float inv_keep) {
+    if (p <= 0.f) return 1.f;
+    const uint4 r = rng((uint64_t)row * (D / 4) + (c >> 2), off);
+    const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+    return u32_to_unit(rr[c & 3]) >= p ? inv_keep : 0.f;
+}
+// out[i, :] = lam * drop(z[i, :]) + (1 - lam) * drop(z[perm[i], :])     z, out bf16 [B, D]; perm == NULL: no mixing (eval)
+__global__ void head_mix_fwd_kernel(const __nv_bfloat16* __restrict__ z, const int64_t* __restrict__ perm,
+                                    const float* __restrict__ lam, __nv_bfloat16* __restrict__ out, int B, int D, float p,
+                                    const int64_t* __restrict__ seed_off) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * D) return;
+    const int b = i / D, c = i - b * D;
+    Philox rng(seed_off ? (uint64_t)seed_off[0] : 0ull);
+    const uint64_t off = seed_off ? (uint64_t)seed_off[1] : 0ull;
+    const float ik = 1.f / (1.f - p);
+    float v = __bfloat162float(z[i]) * head_keep(rng, off, b, c, D, p, ik);
+    if (perm) {
+        const int pb = (int)perm[b];
+        const float l = lam[0];
+        v = l * v + (1.f - l) * __bfloat162float(z[(int64_t)pb * D + c]) * head_keep(rng, off, pb, c, D, p, ik);
+    }
+    out[i] = __float2bfloat16(v);
+}
+// dz[j, :] = keep(j, :) * (lam * g[j, :] + (1 - lam) * Σ_{i: perm[i] = j} g[i, :])     dz fp32 [B, D], ZERO on entry
+__global__ void head_mix_bwd_kernel(const __nv_bfloat16* __restrict__ g, const int64_t* __restrict__ perm,
+                                    const float* __restrict__ lam, float* __restrict__ dz, int B, int D, float p,
+                                    const int64_t* __restrict__ seed_off) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * D) return;
+    const int b = i / D, c = i - b * D;
+    Philox rng(seed_off ? (uint64_t)seed_off[0] : 0ull);
+    const uint64_t off = seed_off ? (uint64_t)seed_off[1] : 0ull;
+    const float ik = 1.f / (1.f - p);
+    const float gv = __bfloat162float(g[i]);
+    if (perm) {
+        const int pb = (int)perm[b];
+        const float l = lam[0];
+        atomicAdd(dz + i, l * gv * head_keep(rng, off, b, c, D, p, ik));
+        atomicAdd(dz + (int64_t)pb * D + c, (1.f - l) * gv * head_keep(rng, off, pb, c, D, p, ik));
+    } else {
+        dz[i] = gv * head_keep(rng, off, b, c, D, p, ik);
+    }
+}
+
+}  // namespace
+
+FDT_API int fdt_cls_gather(const float* x, void* cls_bf16, int B, int L, int D, cudaStream_t st) {
+    if (D % 4 || B < 1) return -1;
+    cls_gather_kernel<<<(B * (D / 4) + 255) / 256, 256, 0, st>>>(x, (__nv_bfloat16*)cls_bf16, B, L, D);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+FDT_API int fdt_cls_scatter(const float* g, float* dx, int B, int L, int D, cudaStream_t st) {
+    if (D % 4 || B < 1) return -1;
+    int64_t blocks = ((int64_t)B * L * (D / 4) + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    cls_scatter_kernel<<<(int)blocks, 256, 0, st>>>(g, dx, B, L, D);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+FDT_API int fdt_head_mix_fwd(const void* z, const int64_t* perm, const float* lam, void* out, int B, int D, float p,
+                             const int64_t* seed_off, cudaStream_t st) {
+    if (D % 4 || B < 1 || p < 0.f || p >= 1.f) return -1;
+    head_mix_fwd_kernel<<<(B * D + 255) / 256, 256, 0, st>>>((const __nv_bfloat16*)z, perm, lam, (__nv_bfloat16*)out, B, D, p,
+                                                              p > 0.f ? seed_off : nullptr);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+FDT_API int fdt_head_mix_bwd(const void* g, const int64_t* perm, const float* lam, float* dz, int B, int D, float p,
+                             const int64_t* seed_off, cudaStream_t st) {
+    if (D % 4 || B < 1 || p < 0.f || p >= 1.f) return -1;
+    cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)B * D, st);
+    head_mix_bwd_kernel<<<(B * D + 255) / 256, 256, 0, st>>>((const __nv_bfloat16*)g, perm, lam, dz, B, D, p,
+                                                              p > 0.f ? seed_off : nullptr);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -5,7 +5,7 @@ Capability parity with ``resnet50_test.py:355-457`` (and the copies in
 ``transformer_test.py:186-202``), re-designed so that nothing crosses to the host:
 λ ~ Beta(α, α) is drawn on the device (the reference samples on the CPU and calls ``.item()``,
 ``resnet50_test.py:359``), the permutation is a device ``randperm``, and the blend for CUDA
-tensors is the fused gather+lerp kernel in ``csrc/mixup_loss.cu``.
+tensors is the fused augmentation + gather + lerp kernel in ``csrc/input_head.cu`` (``fdt_input_aug_mixup*``).
 
 Differences from the reference that are deliberate: :class:`MetaMixup` is a
 *persistent* module whose per-sample λ is a real learnable parameter — what the reference's
@@ -84,6 +84,19 @@ class MetaMixup(nn.Module):
         else:
             mixed = blend(x, index, lam.reshape(-1))
         return mixed, y, y[index], lam
+
+
+    def fused_from_uint8(self, images_u8, y, mean, std, generator=None):
+        """The whole input path of ``--meta_learning`` on a raw uint8 NHWC batch in one native kernel (crop + flip +
+        normalise both partners + blend with sigmoid(θ_i)); differentiable w.r.t. θ.  Returns what :meth:`forward` does."""
+        B = images_u8.size(0)
+        if self.compat:
+            with torch.no_grad():
+                self.lam.copy_(torch.rand(self.lam.shape, device=self.lam.device, generator=generator))
+        index = randperm(B, images_u8.device, generator)
+        theta = self.lam[:B].detach() if self.compat else self.lam[:B]     # compat: lambda is resampled, never learned
+        mixed = ops._cu().input_aug_meta_mixup(images_u8, theta, index, mean, std)
+        return mixed, y, y[index], torch.sigmoid(theta)
 
 
 class AttnMixup(nn.Module):

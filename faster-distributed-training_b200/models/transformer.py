@@ -35,8 +35,8 @@ class LayerNorm(nn.Module):
         self.b_2 = nn.Parameter(torch.zeros(features))
         self.eps = eps
 
-    def forward(self, x):
-        return ops.layernorm_ref(x, self.a_2, self.b_2, self.eps)
+    def forward(self, x, passthrough=False):
+        return ops.layernorm_ref(x, self.a_2, self.b_2, self.eps, passthrough)
 
 
 class Embeddings(nn.Module):
@@ -118,7 +118,8 @@ class sublayerConnectionAttention(nn.Module):
         self.p = dropout_connection
 
     def forward(self, x, key_mask=None):
-        return ops.dropout_add(self.multiheads(self.layernorm(x), key_mask), x, self.p, self.training)
+        y, xp = self.layernorm(x, passthrough=True)     # the residual consumes the alias: gradients meet inside the LN backward
+        return ops.dropout_add(self.multiheads(y, key_mask), xp, self.p, self.training)
 
 
 class sublayerConnectionFFN(nn.Module):
@@ -129,7 +130,8 @@ class sublayerConnectionFFN(nn.Module):
         self.p = dropout_connection
 
     def forward(self, x):
-        return ops.dropout_add(self.ffn(self.layernorm(x)), x, self.p, self.training)
+        y, xp = self.layernorm(x, passthrough=True)
+        return ops.dropout_add(self.ffn(y), xp, self.p, self.training)
 
 
 class Pooler(nn.Module):
@@ -138,7 +140,7 @@ class Pooler(nn.Module):
         self.dense = nn.Linear(hidden_size, hidden_size)
 
     def forward(self, x):
-        return ops.linear(x[:, 0, :].contiguous(), self.dense.weight, self.dense.bias, act="tanh")
+        return ops.linear(ops.cls_gather(x), self.dense.weight, self.dense.bias, act="tanh")
 
 
 class FusedMLP(nn.Module):
@@ -236,10 +238,7 @@ class Transformer(nn.Module):
                 ops.stage_begin(self, 2)
                 x = ops.bucket_boundary(x, self, 0)
             x = ffn(att(x, key_mask))
-        x = self.pooler(x)
-        if self.training:
-            x = torch.nn.functional.dropout(x, self.p_post, True)
-        return x
+        return self.pooler(x)       # post-pooler dropout is fused with the manifold mixup (ops.head_mix)
 
     def forward(self, tokens, token_types, index=None, mask=None, generator=None):
         """``mask`` may be [B, L] or the reference's [B, 1, 1, L] (transformer_test.py:260).
@@ -251,6 +250,5 @@ class Transformer(nn.Module):
             return self.classifier(x)
         lam = mx.sample_beta(self.alpha, x.device, generator=generator)
         perm = mx.randperm(x.size(0), x.device, generator)
-        l = lam.to(x.dtype)
-        mixed = l * x + (1.0 - l) * x[perm]
+        mixed = ops.head_mix(x, perm, lam, self.p_post, True)      # dropout(0.1) + lam*x + (1-lam)*x[perm], one kernel
         return self.classifier(mixed), perm, lam

@@ -83,10 +83,12 @@ def mixup_correct(logits, y_a, y_b, lam):
     return ref.mixup_correct(logits, y_a, y_b, lam)
 
 
-def layernorm_ref(x, a_2, b_2, eps=1e-6):
+def layernorm_ref(x, a_2, b_2, eps=1e-6, passthrough=False):
+    """``passthrough``: also return the input (an alias) for the residual branch to consume — see cuda_ops._LayerNorm."""
     if use_native(x):
-        return _cu().layernorm_ref(x, a_2, b_2, eps)
-    return ref.layernorm_ref(x, a_2, b_2, eps)
+        return _cu().layernorm_ref(x, a_2, b_2, eps, passthrough)
+    y = ref.layernorm_ref(x, a_2, b_2, eps)
+    return (y, x) if passthrough else y
 
 
 def linear(x, weight, bias=None, act="none", dropout_p=0.0, training=False):
@@ -123,6 +125,26 @@ def mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat=False):
     if use_native(x):
         return _cu().mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat)
     return ref.mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat)
+
+
+def cls_gather(x):
+    """First-token rows of the [B, L, D] residual stream (the pooler's input, transformer.py:99-101)."""
+    if use_native(x):
+        return _cu().cls_gather(x)
+    return x[:, 0, :].contiguous()
+
+
+def head_mix(z, perm, lam, p, training):
+    """Pooled-vector dropout followed by manifold mixup ``lam*z + (1-lam)*z[perm]`` (transformer.py:70-80); ``perm`` None
+    = no mixing."""
+    p = float(p) if training else 0.0
+    if use_native(z):
+        return _cu().head_mix(z, perm, lam, p)
+    z = torch.nn.functional.dropout(z, p, True) if p > 0 else z
+    if perm is None:
+        return z
+    l = lam.to(z.dtype)
+    return l * z + (1.0 - l) * z[perm]
 
 
 def dropout_add(x, residual, p, training):

@@ -426,6 +426,45 @@ def input_aug_mixup(images_u8: torch.Tensor, train: bool, perm=None, lam=None, m
     return out
 
 
+class _InputAugMeta(torch.autograd.Function):
+    """Meta-mixup on the raw uint8 batch (resnet50_test.py:388-401, 525): crop + flip + normalise both partners and blend
+    them with the per-sample weight sigmoid(theta_b) in ONE kernel; the backward recomputes the partners from the uint8
+    images (same Philox stream) and reduces dL/dx · (a − b) · sigmoid'(theta) to dtheta — the learnable-lambda path of
+    ``--meta_learning`` with no torch ops and nothing saved but the seed."""
+
+    @staticmethod
+    def forward(ctx, images_u8, theta, perm, mean, std, pad):
+        import ctypes
+        B, H, W, C = images_u8.shape
+        images_u8 = images_u8.contiguous()
+        th = theta.detach().reshape(-1).float().contiguous()
+        out = torch.empty((B, 3, H, W), dtype=BF16, device=images_u8.device, memory_format=torch.channels_last)
+        so = _next_seed_off(images_u8.device)
+        m3, s3 = (ctypes.c_float * 3)(*mean), (ctypes.c_float * 3)(*std)
+        call("fdt_input_aug_mixup_ex", images_u8, perm, th, B, 1, so, out, B, H, W, pad, 1, m3, s3)
+        ctx.save_for_backward(images_u8, th, perm, so)
+        ctx.cfg = (tuple(mean), tuple(std), pad, theta.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        import ctypes
+        images_u8, th, perm, so = ctx.saved_tensors
+        mean, std, pad, tshape = ctx.cfg
+        B, H, W, _ = images_u8.shape
+        g = _nhwc(g)
+        dth = torch.zeros(B, dtype=torch.float32, device=g.device)
+        m3, s3 = (ctypes.c_float * 3)(*mean), (ctypes.c_float * 3)(*std)
+        call("fdt_input_aug_mixup_bwd", images_u8, perm, th, 1, so, g, dth, B, H, W, pad, 1, m3, s3)
+        return None, dth.view(tshape), None, None, None, None
+
+
+def input_aug_meta_mixup(images_u8, theta, perm, mean, std, pad: int = 4):
+    """uint8 [B,H,W,3] + learnable theta [B,...] → blended bf16 batch, differentiable w.r.t. theta."""
+    assert images_u8.dtype == torch.uint8 and images_u8.shape[-1] == 3
+    return _InputAugMeta.apply(images_u8, theta, perm.long().contiguous(), tuple(mean), tuple(std), int(pad))
+
+
 # ----------------------------------------------------------------------------- mixup
 def mixup_blend(x, index, lam):
     lam = lam.to(x.dtype)
@@ -441,30 +480,39 @@ class _MixupCE(torch.autograd.Function):
         B, C = logits.shape
         out = torch.zeros(2, dtype=torch.float32, device=logits.device)
         dlogits = torch.empty_like(logits)
-        lam = lam.reshape(-1).float().contiguous()
-        call("fdt_mixup_ce", logits, y_a.contiguous(), y_b.contiguous(), lam, lam.numel(), out, dlogits, B, C)
-        ctx.save_for_backward(dlogits)
+        lshape = lam.shape
+        lam_f = lam.detach().reshape(-1).float().contiguous()
+        want_dlam = lam.requires_grad and lam_f.numel() == B
+        dlam = torch.empty(B, dtype=torch.float32, device=logits.device) if want_dlam else None
+        call("fdt_mixup_ce_ex", logits, y_a.contiguous(), y_b.contiguous(), lam_f, lam_f.numel(), out, dlogits, dlam, B, C)
+        ctx.save_for_backward(dlogits, dlam)
+        ctx.lshape = lshape
         return out[0]
 
     @staticmethod
     def backward(ctx, g):
-        (dlogits,) = ctx.saved_tensors
-        return dlogits * g, None, None, None
+        dlogits, dlam = ctx.saved_tensors
+        return dlogits * g, None, None, (None if dlam is None else (dlam * g).view(ctx.lshape))
 
 
 def mixup_cross_entropy(logits, y_a, y_b, lam):
     if not torch.is_tensor(lam):
         lam = torch.tensor([float(lam)], device=logits.device)
-    if lam.requires_grad or logits.shape[1] > 32:
-        _lib.note_fallback("mixup_cross_entropy", "ATen log_softmax path (learnable lambda or > 32 classes)")
-        return ref.mixup_cross_entropy(logits, y_a, y_b, lam)       # learnable λ: differentiable path
+    if logits.shape[1] > 32 or (lam.requires_grad and lam.numel() != logits.shape[0]):
+        _lib.note_fallback("mixup_cross_entropy", "ATen log_softmax path (> 32 classes, or a learnable scalar lambda)")
+        return ref.mixup_cross_entropy(logits, y_a, y_b, lam)
     return _MixupCE.apply(logits, y_a, y_b, lam)
 
 
 # ----------------------------------------------------------------------------- transformer ops
 class _LayerNorm(torch.autograd.Function):
+    """``passthrough``: also return the input as a second output.  In a pre-LN sub-layer x feeds both the LayerNorm and the
+    residual add; when the residual consumes the alias, its gradient arrives here together with the LayerNorm's own and
+    the kernel accumulates dx straight into it (the fp32 residual-stream gradient flows down the network in ONE buffer, no
+    add kernels, no zero fills).  da / db accumulate directly into the parameters' slots of the flat gradient buffer."""
+
     @staticmethod
-    def forward(ctx, x, a, b, eps):
+    def forward(ctx, x, a, b, eps, passthrough):
         shp = x.shape
         D = shp[-1]
         x2 = x.float().contiguous().view(-1, D)
@@ -472,27 +520,36 @@ class _LayerNorm(torch.autograd.Function):
         y = torch.empty(M, D, dtype=BF16, device=x.device)
         stats = torch.empty(M, 2, dtype=torch.float32, device=x.device)
         call("fdt_ln_fwd", x2, a, b, y, stats, M, D, float(eps))
-        ctx.save_for_backward(x2, a, stats)
+        ctx.save_for_backward(x2, a, b, stats)
         ctx.eps, ctx.shp = eps, shp
+        if passthrough:
+            return y.view(shp), x.view_as(x)
         return y.view(shp)
 
     @staticmethod
-    def backward(ctx, g):
-        x2, a, stats = ctx.saved_tensors
+    def backward(ctx, g, gpass=None):
+        x2, a, b, stats = ctx.saved_tensors
         M, D = x2.shape
         g = g.to(BF16).contiguous().view(M, D)
-        dx = torch.zeros_like(x2)
-        da = torch.zeros(D, dtype=torch.float32, device=x2.device)
-        db = torch.zeros(D, dtype=torch.float32, device=x2.device)
+        if gpass is not None and gpass.dtype == torch.float32 and gpass.is_contiguous():
+            dx = gpass.view(M, D)                       # accumulate in place into the residual-stream gradient
+        elif gpass is not None:
+            dx = gpass.float().contiguous().view(M, D)
+        else:
+            dx = torch.zeros_like(x2)
+        da_slot, db_slot = _flat_grad_slot(a), _flat_grad_slot(b)
+        da = da_slot if da_slot is not None else torch.zeros(D, dtype=torch.float32, device=x2.device)
+        db = db_slot if db_slot is not None else torch.zeros(D, dtype=torch.float32, device=x2.device)
         call("fdt_ln_bwd", x2, a, stats, g, dx, da, db, M, D, float(ctx.eps))
-        return dx.view(ctx.shp), da, db, None
+        return dx.view(ctx.shp), (None if da_slot is not None else da), (None if db_slot is not None else db), None, None
 
 
-def layernorm_ref(x, a_2, b_2, eps):
+def layernorm_ref(x, a_2, b_2, eps, passthrough=False):
     if x.shape[-1] not in (128, 256, 512, 1024):
         _lib.note_fallback("layernorm", f"ATen ops for D={x.shape[-1]} (native: 128/256/512/1024)")
-        return ref.layernorm_ref(x, a_2, b_2, eps)
-    return _LayerNorm.apply(x, a_2, b_2, eps)
+        y = ref.layernorm_ref(x, a_2, b_2, eps)
+        return (y, x) if passthrough else y
+    return _LayerNorm.apply(x, a_2, b_2, eps, bool(passthrough))
 
 
 class _LinearLib(torch.autograd.Function):
@@ -577,21 +634,24 @@ class _Embed(torch.autograd.Function):
         types = types.long().contiguous()
         out = torch.empty(B, L, D, dtype=torch.float32, device=tok_w.device)
         call("fdt_embed_fwd", tokens, types, tok_w, pos_w, seg_w, out, B * L, L, D, float(scale))
-        ctx.save_for_backward(tokens, types)
+        ctx.save_for_backward(tokens, types, tok_w, pos_w, seg_w)
         ctx.shapes = (tok_w.shape, pos_w.shape, seg_w.shape, scale)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        tokens, types = ctx.saved_tensors
+        tokens, types, tok_w, pos_w, seg_w = ctx.saved_tensors
         ts, ps, ss, scale = ctx.shapes
         B, L = tokens.shape
         D = ts[1]
         g = g.float().contiguous()
-        dtok = torch.zeros(ts, dtype=torch.float32, device=g.device)
-        dpos = torch.zeros(ps, dtype=torch.float32, device=g.device)
-        dseg = torch.zeros(ss, dtype=torch.float32, device=g.device)
-        call("fdt_embed_bwd", tokens, types, g, dtok, dpos, dseg, B * L, L, D, float(scale))
+        # scatter-add straight into the tables' slots of the flat gradient buffer (cleared once per step): no 62 MB zero
+        # fill of a dense [30522, 512] temporary and no dense accumulate pass for a gradient that touches <= B*L rows
+        slots = [_flat_grad_slot(w) for w in (tok_w, pos_w, seg_w)]
+        outs = [sl if sl is not None else torch.zeros(shp, dtype=torch.float32, device=g.device)
+                for sl, shp in zip(slots, (ts, ps, ss))]
+        call("fdt_embed_bwd", tokens, types, g, outs[0], outs[1], outs[2], B * L, L, D, float(scale))
+        dtok, dpos, dseg = [None if sl is not None else o for sl, o in zip(slots, outs)]
         return None, None, dtok, dpos, dseg, None
 
 
@@ -600,13 +660,78 @@ def embed(tokens, token_types, tok_w, pos_w, seg_w, scale):
 
 
 def mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat):
-    """Linear → ReLU (tcgen05 GEMM with fused bias+ReLU epilogue) → Linear(hidden → n_class) (4-wide: torch)."""
+    """Linear → ReLU (tcgen05 GEMM with fused bias+ReLU epilogue) → Linear(hidden → n_class): the narrow second layer runs on
+    the small-N head kernel (``fdt_pool_fc_*`` with a 1-pixel "pool": logits, dX, dW, db in one launch each way)."""
     if bias_grad_mean_compat:
         B = x.shape[0]
         b1 = ref._ScaleGrad.apply(b1, 1.0 / B)
         b2 = ref._ScaleGrad.apply(b2, 1.0 / B)
     h = linear(x, W1, b1, "relu")
+    n_out, hid = W2.shape
+    if n_out <= 32 and hid * 4 <= 48 * 1024 and h.dtype == BF16:
+        return _PoolFC.apply(h.reshape(-1, hid, 1, 1), W2, b2.reshape(-1))
+    _lib.note_fallback("mlp_head", f"cuBLAS F.linear for the {n_out}-wide output layer (native: <= 32 outputs)")
     return F.linear(h.float(), W2, b2.reshape(-1))
+
+
+class _ClsGather(torch.autograd.Function):
+    """[B, L, D] fp32 residual stream → bf16 [B, D] first-token rows; the backward writes the whole [B, L, D] gradient
+    (zero except row 0) in one pass — the buffer the residual-stream backward then accumulates into in place."""
+
+    @staticmethod
+    def forward(ctx, x):
+        B, L, D = x.shape
+        x = x.float().contiguous()
+        out = torch.empty(B, D, dtype=BF16, device=x.device)
+        call("fdt_cls_gather", x, out, B, L, D)
+        ctx.geom = (B, L, D)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        B, L, D = ctx.geom
+        dx = torch.empty(B, L, D, dtype=torch.float32, device=g.device)
+        call("fdt_cls_scatter", g.float().contiguous(), dx, B, L, D)
+        return dx
+
+
+def cls_gather(x):
+    if x.shape[-1] % 4:
+        return x[:, 0, :].contiguous()
+    return _ClsGather.apply(x)
+
+
+class _HeadMix(torch.autograd.Function):
+    """out = lam * drop(z) + (1 - lam) * drop(z[perm]): pooled-vector dropout + manifold mixup, one kernel each way."""
+
+    @staticmethod
+    def forward(ctx, z, perm, lam, p):
+        B, D = z.shape
+        z = z.to(BF16).contiguous()
+        out = torch.empty_like(z)
+        so = _next_seed_off(z.device) if p > 0 else None
+        lam_t = None if lam is None else lam.detach().reshape(-1).float().contiguous()
+        perm_t = None if perm is None else perm.long().contiguous()
+        call("fdt_head_mix_fwd", z, perm_t, lam_t, out, B, D, float(p), so)
+        ctx.save_for_backward(perm_t, lam_t, so)
+        ctx.geom = (B, D, float(p), z.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        perm_t, lam_t, so = ctx.saved_tensors
+        B, D, p, _ = ctx.geom
+        dz = torch.empty(B, D, dtype=torch.float32, device=g.device)
+        call("fdt_head_mix_bwd", g.to(BF16).contiguous(), perm_t, lam_t, dz, B, D, p, so, launches=2)
+        return dz.to(BF16), None, None, None
+
+
+def head_mix(z, perm, lam, p):
+    if z.shape[-1] % 4 or (lam is not None and lam.numel() != 1):
+        _lib.note_fallback("head_mix", "ATen dropout + lerp (per-sample lambda or odd width)")
+        z = F.dropout(z, p, True) if p > 0 else z
+        return z if perm is None else lam.to(z.dtype) * z + (1.0 - lam.to(z.dtype)) * z[perm]
+    return _HeadMix.apply(z, perm, lam, float(p))
 
 
 class _DropoutAdd(torch.autograd.Function):

@@ -320,6 +320,9 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
     H, Xhat = project()
     if native:
         from .. import ops
+        from ..ops import _lib
+        _lib.note_fallback("ngd_precondition", f"cuBLAS fp32 bmm for a factor with N={fb.N}, D={fb.D}, R={fb.R} (native: R % 4 == 0, "
+                                               f"16 <= R <= 128, contiguous axis % 4 == 0, or D <= 12)")
         p0, out = ops._cu().ngd_norms_rescale(Xc, Xhat, getattr(fb, "_sums", None))      # fused Σx², Σx̂², rescale + NaN guard
         if updating:
             if pending is None:

@@ -94,6 +94,18 @@ int fdt_dropout_bwd(const float* g, void* dx, int dx_is_bf16, int64_t n, float p
 int fdt_mixup_ce(const float* logits, const int64_t* ya, const int64_t* yb, const float* lam, int lam_n,
                  float* out, float* dlogits, int B, int C, cudaStream_t st);
 
+/* + dlam [B] = d loss / d lam_i for per-sample (learnable, meta-mixup) mixing weights */
+int fdt_mixup_ce_ex(const float* logits, const int64_t* ya, const int64_t* yb, const float* lam, int lam_n,
+                    float* out, float* dlogits, float* dlam, int B, int C, cudaStream_t st);
+/* pooled classification head (transformer.py:61-84, 94-101): cls = bf16(x[:, 0, :]) and its gradient (zero elsewhere);
+ * out = lam * drop(z) + (1 - lam) * drop(z[perm]) (pooled-vector dropout + manifold mixup; perm NULL = no mixing), dz fp32. */
+int fdt_cls_gather(const float* x, void* cls_bf16, int B, int L, int D, cudaStream_t st);
+int fdt_cls_scatter(const float* g, float* dx, int B, int L, int D, cudaStream_t st);
+int fdt_head_mix_fwd(const void* z, const int64_t* perm, const float* lam, void* out, int B, int D, float p,
+                     const int64_t* seed_off, cudaStream_t st);
+int fdt_head_mix_bwd(const void* g, const int64_t* perm, const float* lam, float* dz, int B, int D, float p,
+                     const int64_t* seed_off, cudaStream_t st);
+
 /* ---- NGD Fisher-factor refresh, csrc/ngd_eig.cu -------------------------------------------------
  * ref: OnlineNaturalGradient._precondition_directions3 (ngd_optimizer.py:225-317) */
 int fdt_ngd_eig_update(const float* K, const float* L, const float* d, const float* rho, const float* trXXt,
@@ -179,6 +191,15 @@ int fdt_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
 int fdt_input_aug_mixup(const void* x_u8, const int64_t* perm, const float* lam, int lam_n, const int64_t* seed_off,
                         void* out_bf16, int B, int H, int W, int pad, int train, const float* mean3, const float* std3,
                         cudaStream_t st);
+/* meta-mixup (resnet50_test.py:388-401): lam_mode 1 = `lam` holds theta, lam_i = sigmoid(theta_i) computed in the kernel;
+ * _bwd: dlam[b] (+=) = sum_pixels g * (partner_a - partner_b) [* sigmoid'(theta_b)], partners recomputed from the uint8 images
+ * with the forward's (seed, offset) */
+int fdt_input_aug_mixup_ex(const void* x_u8, const int64_t* perm, const float* lam, int lam_n, int lam_mode,
+                           const int64_t* seed_off, void* out_bf16, int B, int H, int W, int pad, int train,
+                           const float* mean3, const float* std3, cudaStream_t st);
+int fdt_input_aug_mixup_bwd(const void* x_u8, const int64_t* perm, const float* lamsrc, int lam_mode, const int64_t* seed_off,
+                            const void* g_bf16, float* dlam, int B, int H, int W, int pad, int train, const float* mean3,
+                            const float* std3, cudaStream_t st);
 int fdt_pool_fc_fwd(const void* x, const float* W, const float* bias, float* pooled, float* logits, int N, int HW,
                     int C, int K, cudaStream_t st);
 int fdt_pool_fc_bwd(const float* dlogits, const float* W, const float* pooled, void* dx, float* dW, float* db,

@@ -412,3 +412,86 @@ def test_linear_gelu_dropout_fused():
     # eval / p = 0: plain gelu
     out0 = ops.linear(x.detach(), w, b, act="gelu", dropout_p=p, training=False)
     _close(out0, full, 3e-2, 3e-2, "eval")
+
+
+def test_meta_mixup_kernel_forward_and_dtheta():
+    """Fused meta-mixup (crop + flip + normalise + sigmoid(theta) blend): the blend is linear in lam, so with a fixed
+    (seed, offset) out(theta) = lam*A + (1-lam)*Bp for partner images A, Bp recovered from theta = ±inf; dtheta from the
+    backward kernel must equal sum g*(A - Bp) * sigmoid'(theta)."""
+    import ctypes
+    from fdt.ops._lib import call
+    torch.manual_seed(3)
+    B, H, W = 16, 32, 32
+    dev = "cuda"
+    x = torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8, device=dev)
+    perm = torch.randperm(B, device=dev)
+    so = torch.tensor([12345, 7], dtype=torch.int64, device=dev)
+    m3, s3 = (ctypes.c_float * 3)(0.49, 0.48, 0.45), (ctypes.c_float * 3)(0.25, 0.24, 0.26)
+
+    def fwd(theta):
+        out = torch.empty((B, 3, H, W), dtype=torch.bfloat16, device=dev, memory_format=torch.channels_last)
+        call("fdt_input_aug_mixup_ex", x, perm, theta.contiguous(), B, 1, so, out, B, H, W, 4, 1, m3, s3)
+        return out.permute(0, 2, 3, 1).float()          # [B, H, W, 3]
+
+    A = fwd(torch.full((B,), 40.0, device=dev))         # lam = 1
+    Bp = fwd(torch.full((B,), -40.0, device=dev))       # lam = 0
+    theta = torch.randn(B, device=dev)
+    lam = torch.sigmoid(theta)
+    out = fwd(theta)
+    ref = lam.view(B, 1, 1, 1) * A + (1 - lam.view(B, 1, 1, 1)) * Bp
+    assert (out - ref).abs().max() < 0.05
+    assert (A - Bp).abs().mean() > 0.1                  # the partners really differ (perm + independent crops)
+    g = torch.randn(B, 3, H, W, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    dth = torch.zeros(B, device=dev)
+    call("fdt_input_aug_mixup_bwd", x, perm, theta.contiguous(), 1, so, g, dth, B, H, W, 4, 1, m3, s3)
+    want = (g.permute(0, 2, 3, 1).float() * (A - Bp)).sum((1, 2, 3)) * lam * (1 - lam)
+    assert torch.allclose(dth, want, rtol=2e-2, atol=2e-2 * want.abs().max().item()), (dth - want).abs().max()
+
+
+def test_mixup_ce_per_sample_lambda_gradient():
+    from fdt import ops
+    torch.manual_seed(4)
+    B, C = 64, 10
+    logits = torch.randn(B, C, device="cuda", requires_grad=True)
+    ya, yb = torch.randint(0, C, (B,), device="cuda"), torch.randint(0, C, (B,), device="cuda")
+    lam = torch.rand(B, device="cuda", requires_grad=True)
+    loss = ops.mixup_cross_entropy(logits, ya, yb, lam)
+    loss.backward()
+    l2, lam2 = logits.detach().clone().requires_grad_(True), lam.detach().clone().requires_grad_(True)
+    ref = ops.ref.mixup_cross_entropy(l2, ya, yb, lam2)
+    ref.backward()
+    assert torch.allclose(loss, ref, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(logits.grad, l2.grad, rtol=1e-3, atol=1e-6)
+    assert torch.allclose(lam.grad, lam2.grad, rtol=1e-3, atol=1e-6)
+
+
+def test_head_kernels_match_torch():
+    """cls gather / scatter and the dropout + manifold-mixup kernel of the transformer head."""
+    from fdt import ops
+    torch.manual_seed(5)
+    B, L, D = 16, 9, 512
+    x = torch.randn(B, L, D, device="cuda", requires_grad=True)
+    cls = ops.cls_gather(x)
+    assert cls.dtype == torch.bfloat16 and torch.equal(cls, x[:, 0, :].bfloat16())
+    g = torch.randn(B, D, device="cuda").bfloat16()
+    cls.backward(g)
+    want = torch.zeros(B, L, D, device="cuda")
+    want[:, 0, :] = g.float()
+    assert torch.equal(x.grad, want)
+    z = torch.randn(B, D, device="cuda").bfloat16().requires_grad_(True)
+    perm = torch.randperm(B, device="cuda")
+    lam = torch.tensor(0.3, device="cuda")
+    out = ops.head_mix(z, perm, lam, 0.0, True)
+    ref = 0.3 * z.float() + 0.7 * z.float()[perm]
+    assert torch.allclose(out.float(), ref, rtol=2e-2, atol=2e-2)
+    go = torch.randn(B, D, device="cuda").bfloat16()
+    out.backward(go)
+    zr = z.detach().float().requires_grad_(True)
+    (0.3 * zr + 0.7 * zr[perm]).backward(go.float())
+    assert torch.allclose(z.grad.float(), zr.grad, rtol=2e-2, atol=2e-2)
+    # with dropout: same mask in forward and backward (d out / d z is the mask pattern), mean preserved
+    z2 = torch.ones(B, D, device="cuda").bfloat16().requires_grad_(True)
+    o2 = ops.head_mix(z2, None, None, 0.1, True)
+    o2.float().sum().backward()
+    assert torch.allclose(o2.float(), z2.grad.float(), rtol=1e-2, atol=1e-2)
+    assert abs(o2.float().mean().item() - 1.0) < 0.05
