@@ -164,3 +164,98 @@ FDT_API int fdt_ngd_small_kl(const float* J, const float* W, float* K, float* L,
     FDT_CHECK_LAUNCH();
     return 0;
 }
+
+// ---- whole small factors in shared memory -------------------------------------------------------------------------------
+// Factors whose gradient matrix is small and whose rows are not 16-byte aligned (the 3-channel stem's [64, 27] view, a
+// [B, 1, 1, 1] meta-mixup theta, odd-length vectors) cannot be fed to TMA; they are also far too small for tensor cores.
+// One CTA per factor keeps X, W and H in shared memory and does the complete step of ngd_optimizer.py:138-218 for it:
+//   H = X Wᵀ, X̂ = X − H W, p0 = ΣX², p1 = ΣX̂², out = X̂·sqrt(p0 / (p1 + 1e-30)) (X if p1 is NaN), and optionally J = Hᵀ X.
+namespace {
+constexpr int kSmallMaxElems = 8192;      // each of N*D, R*D, N*R (floats): 3 x 32 KB of shared memory
+
+__global__ void __launch_bounds__(256)
+ngd_small_matrix_kernel(const float* __restrict__ X, const float* __restrict__ W, int ldw, float* __restrict__ out,
+                        float* __restrict__ p0_out, float* __restrict__ J, int ldj, int N, int D, int R, int x_trans) {
+    extern __shared__ float sm[];
+    float* sX = sm;                    // [N][D]
+    float* sW = sm + N * D;            // [R][D]
+    float* sH = sW + R * D;            // [N][R]
+    __shared__ float red0[8], red1[8];
+    __shared__ float s_scale, s_nan;
+    const int f = blockIdx.x, tid = threadIdx.x;
+    const float* Xf = X + (size_t)f * N * D;
+    const float* Wf = W + (size_t)f * R * ldw;
+    for (int i = tid; i < N * D; i += 256) {
+        const int r = i / D, d = i - r * D;
+        sX[i] = x_trans ? Xf[(size_t)d * N + r] : Xf[i];
+    }
+    for (int i = tid; i < R * D; i += 256) { const int r = i / D, d = i - r * D; sW[i] = Wf[(size_t)r * ldw + d]; }
+    __syncthreads();
+    for (int i = tid; i < N * R; i += 256) {
+        const int row = i / R, r = i - row * R;
+        float a = 0.f;
+        for (int d = 0; d < D; ++d) a = fmaf(sX[row * D + d], sW[r * D + d], a);
+        sH[i] = a;
+    }
+    __syncthreads();
+    float p0 = 0.f, p1 = 0.f;
+    float* outf = out + (size_t)f * N * D;
+    // X̂ overwrites nothing yet: keep it in registers per element, two passes (norms first, then the rescaled store)
+    for (int i = tid; i < N * D; i += 256) {
+        const int row = i / D, d = i - row * D;
+        float a = sX[i];
+        p0 = fmaf(a, a, p0);
+        float h = 0.f;
+        for (int r = 0; r < R; ++r) h = fmaf(sH[row * R + r], sW[r * D + d], h);
+        a -= h;
+        p1 = fmaf(a, a, p1);
+    }
+    p0 = warp_sum(p0); p1 = warp_sum(p1);
+    if ((tid & 31) == 0) { red0[tid >> 5] = p0; red1[tid >> 5] = p1; }
+    __syncthreads();
+    if (tid == 0) {
+        float a = 0.f, b = 0.f;
+        for (int i = 0; i < 8; ++i) { a += red0[i]; b += red1[i]; }
+        p0_out[f] = a;
+        s_nan = (b != b) ? 1.f : 0.f;
+        s_scale = sqrtf(a / (b + 1e-30f));
+    }
+    __syncthreads();
+    const float scale = s_scale;
+    const bool use_x = s_nan != 0.f;
+    for (int i = tid; i < N * D; i += 256) {
+        const int row = i / D, d = i - row * D;
+        float h = 0.f;
+        for (int r = 0; r < R; ++r) h = fmaf(sH[row * R + r], sW[r * D + d], h);
+        const float v = use_x ? sX[i] : (sX[i] - h) * scale;
+        if (x_trans) outf[(size_t)d * N + row] = v; else outf[i] = v;
+    }
+    if (J) {
+        float* Jf = J + (size_t)f * R * ldj;
+        for (int i = tid; i < R * D; i += 256) {
+            const int r = i / D, d = i - r * D;
+            float a = 0.f;
+            for (int row = 0; row < N; ++row) a = fmaf(sH[row * R + r], sX[row * D + d], a);
+            Jf[(size_t)r * ldj + d] = a;
+        }
+    }
+}
+}  // namespace
+
+// X [n, N, D] (x_trans == 0) or [n, D, N] (x_trans != 0); W [n, R, ldw] (ldw >= D: padded pitch); out: same layout as X
+// (may NOT alias X); p0 [n] = ΣX² per factor; J [n, R, ldj] or NULL.  N*D, R*D, N*R <= 8192 each.
+FDT_API int fdt_ngd_small_matrix(const float* X, const float* W, int ldw, float* out, float* p0, float* J, int ldj, int n,
+                                 int N, int D, int R, int x_trans, cudaStream_t st) {
+    if (n <= 0 || N < 1 || D < 1 || R < 1 || ldw < D || (J && ldj < D)) return -1;
+    if ((int64_t)N * D > kSmallMaxElems || (int64_t)R * D > kSmallMaxElems || (int64_t)N * R > kSmallMaxElems) return -1;
+    const size_t smem = sizeof(float) * ((size_t)N * D + (size_t)R * D + (size_t)N * R);
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(ngd_small_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * kSmallMaxElems * 4);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    ngd_small_matrix_kernel<<<n, 256, smem, st>>>(X, W, ldw, out, p0, J, ldj, N, D, R, x_trans);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

@@ -836,6 +836,32 @@ def ngd_small_axis(X: torch.Tensor, W: torch.Tensor, A: int, D: int, B: int, J: 
     return sums[:n], Xhat
 
 
+def ngd_small_matrix_ok(N: int, D: int, R: int) -> bool:
+    return N * D <= 8192 and R * D <= 8192 and N * R <= 8192
+
+
+def ngd_small_matrix(X: torch.Tensor, fb, left: bool, want_j: bool):
+    """Whole-factor-in-shared-memory step (csrc/ngd_axis.cu::fdt_ngd_small_matrix).  X [n, N, D] or [n, D, N] (left);
+    returns (p0 [n], preconditioned + rescaled X in the same layout); J goes to fb.Jp when ``want_j``."""
+    n = X.shape[0]
+    out = torch.empty_like(X)
+    p0 = torch.empty(n, dtype=torch.float32, device=X.device)
+    call("fdt_ngd_small_matrix", X, fb.Wp, fb.Dp, out, p0, fb.Jp if want_j else None, fb.Dp, n, fb.N, fb.D, fb.R, int(bool(left)))
+    return p0, out
+
+
+def ngd_kl_any(fb) -> bool:
+    """K = J Jᵀ, L = J Wᵀ for a factor batch on whichever native kernel covers its shape; False if none does."""
+    R, D = fb.R, fb.D
+    if R % 4 == 0 and 16 <= R <= 128 and fb.Dp % 4 == 0:
+        ngd_stats_kl(fb.Jp, fb.Wp, fb.K, fb.L)
+        return True
+    if R <= 16 and D <= 32 and fb.Dp == D:
+        ngd_small_kl(fb.J, fb.W, fb.K, fb.L)
+        return True
+    return False
+
+
 def ngd_small_kl(J, W, K, L):
     n, R, D = J.shape
     call("fdt_ngd_small_kl", J, W, K, L, n, R, D)

@@ -283,8 +283,8 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
         return H, torch.baddbmm(Xm, H, W, alpha=-1.0)
 
     tc = False
+    from .. import ops
     if native:
-        from .. import ops
         tc = ops._cu().ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, left)
     if fb.t == 0:
         # warm start: 3 refreshes on the same gradient (ngd_optimizer.py:356-376)
@@ -294,6 +294,17 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
             for _ in range(3):
                 H, _, p0w = ops._cu().ngd_project(Xc, fb.Wp, left, None, fb.D)
                 _refresh(fb, Xc, left, H, p0w)
+        elif native and fb.W.dtype == torch.float32 and ops._cu().ngd_small_matrix_ok(fb.N, fb.D, fb.R):
+            cu = ops._cu()
+            _alloc_stats(fb)
+            for _ in range(3):
+                p0s, _ = cu.ngd_small_matrix(Xc, fb, left, True)
+                if not cu.ngd_kl_any(fb):
+                    torch.bmm(fb.J, fb.W.transpose(1, 2), out=fb.L)
+                    torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+                fb.tr.copy_(p0s)
+                A_, w_coeff, d1, rho1 = _fisher_update(fb, fb.J, fb.K, fb.L, fb.tr)
+                _apply_refresh(fb, A_, w_coeff, d1, rho1)
         else:
             if p0 is None:
                 p0 = (Xm * Xm).sum((1, 2))
@@ -315,6 +326,24 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
                 else:
                     _statistics(fb, Xc, left, H)
                     fb.tr.copy_(p0)
+                    pending.append(fb)
+            return out
+    if native and fb.W.dtype == torch.float32:
+        from .. import ops
+        cu = ops._cu()
+        if cu.ngd_small_matrix_ok(fb.N, fb.D, fb.R):
+            if updating and not hasattr(fb, "J"):
+                _alloc_stats(fb)
+            p0s, out = cu.ngd_small_matrix(Xc, fb, left, updating)
+            if updating:
+                if not cu.ngd_kl_any(fb):             # L = J Wᵀ (= Hᵀ H exactly, since H = X Wᵀ)
+                    torch.bmm(fb.J, fb.W.transpose(1, 2), out=fb.L)
+                    torch.bmm(fb.J, fb.J.transpose(1, 2), out=fb.K)
+                fb.tr.copy_(p0s)
+                if pending is None:
+                    A_, w_coeff, d1, rho1 = _fisher_update(fb, fb.J, fb.K, fb.L, fb.tr)
+                    _apply_refresh(fb, A_, w_coeff, d1, rho1)
+                else:
                     pending.append(fb)
             return out
     H, Xhat = project()
@@ -364,12 +393,18 @@ def precondition_small_axis(fb: FactorBatch, d_p: torch.Tensor, pa: int, pending
     A = int(math.prod(phys[:pa]))
     B = int(math.prod(phys[pa + 1:]))
     X = d_p.contiguous()
+    if fb.t == 0:
+        # warm start (ngd_optimizer.py:356-376): 3 refreshes on the same gradient, on the same native kernels
+        _alloc_stats(fb)
+        for _ in range(3):
+            p0w, _ = cu.ngd_small_axis(X, fb.W, A, fb.D, B, fb.J)
+            cu.ngd_small_kl(fb.J, fb.W, fb.K, fb.L)
+            fb.tr.copy_(p0w)
+            A_, w_coeff, d1, rho1 = _fisher_update(fb, fb.J, fb.K, fb.L, fb.tr)
+            _apply_refresh(fb, A_, w_coeff, d1, rho1)
     updating = fb.updating()
     fb.t += 1
-    if updating and fb.N <= fb.D:      # cannot happen for a sensible tensor; keep the general path's semantics
-        fb.t -= 1
-        Xm = X.movedim(pa + 1, -1)
-        return precondition(fb, Xm.reshape(n, fb.N, fb.D), False, pending).reshape(Xm.shape).movedim(-1, pa + 1)
+    # (N <= D: the reference takes L = Hᵀ H there, ngd_optimizer.py:215-217 — the same matrix as J Wᵀ, since H = X Wᵀ)
     if updating and not hasattr(fb, "J"):
         _alloc_stats(fb)
     p0, out = cu.ngd_small_axis(X, fb.W, A, fb.D, B, fb.J if updating else None)
@@ -610,7 +645,7 @@ class NGD(Optimizer):
             if fb is None:
                 fb = sg.factors[axis] = FactorBatch(n, N, D, group["alpha"], group["rank"], group["update_period"],
                                                     group["eta"], d_p.dtype, d_p.device)
-            if fb.t > 0 and _small_axis_native(fb, d_p):
+            if _small_axis_native(fb, d_p):
                 # short axis (conv kernel axes, class axes): one bandwidth-bound pass over the tensor where it lies
                 d_p = precondition_small_axis(fb, d_p, pa, pending)
             elif pa == nd - 1:
