@@ -421,11 +421,13 @@ FDT_API int fdt_ngd_stats_j_ex(const float* H, const float* X, float* J, int n, 
     TfParams p{};
     p.batches = n;
     // M = R, N = D, K = N;  A[m = r, k = i] = H[i][r]: stored [K][rows];  B[n = d, k = i] = X[i][d] ([K][rows]) or X'[d][i] (K-major)
-    p.M = R; p.N = D; p.K = N; p.BN = pick_bn(D); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = x_trans ? 0 : 1;
+    // N extent = the padded Dw (a multiple of 4: the epilogue adds 4 columns at a time); X's tensor map keeps the true D, so the
+    // padding columns receive zeros
+    p.M = R; p.N = Dw; p.K = N; p.BN = pick_bn(Dw); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = x_trans ? 0 : 1;
     p.out = J; p.cin = nullptr; p.ldc = Dw; p.batch_stride_c = (int64_t)R * Dw; p.sums = nullptr;
     if (!encode_operand(&tA, H, 1, R, N, n, BM)) return -4;
     if (!encode_operand(&tB, X, p.b_mn, D, N, n, p.BN)) return -4;
-    const int tiles = ((D + p.BN - 1) / p.BN) * n;
+    const int tiles = ((Dw + p.BN - 1) / p.BN) * n;
     int splits = (148 + tiles - 1) / tiles;
     return launch(tA, tB, p, splits, st);
 }

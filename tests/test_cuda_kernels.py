@@ -507,9 +507,9 @@ def test_ngd_gpu_trajectory_matches_reference_and_uses_no_library_gemm():
     from fdt.optim.ngd import NGD
     from fdt.parallel.flat import FlatParameters
     ref = load("ngd_optimizer")
-    # conv (tc + short axes), stem-like [64,3,3,3] (shared-memory kernel: rows of 27), Linear, an "embedding" whose row
-    # count is not a multiple of 4 (padded pitch, split-K projection), a 10-class output layer (short axis)
-    shapes = [(64, 32, 3, 3), (64, 32, 3, 3), (64, 3, 3, 3), (128, 64), (1002, 64), (10, 256)]
+    # conv (tc + short axes), a stem-like [48,5,3,3] (shared-memory kernel: rows of 45 floats), Linear, an "embedding" whose row
+    # count is not a multiple of 4 (padded pitch, split-K projection), a tensor with only short axes (10, 7, 3, 3)
+    shapes = [(64, 32, 3, 3), (64, 32, 3, 3), (48, 5, 3, 3), (128, 64), (1002, 128), (2050, 96), (10, 7, 3, 3)]
     g = torch.Generator().manual_seed(0)
     p_ref = [torch.nn.Parameter((torch.randn(*s, generator=g) * 0.1).cuda()) for s in shapes]
     p_new = [torch.nn.Parameter(p.detach().clone()) for p in p_ref]
@@ -531,4 +531,5 @@ def test_ngd_gpu_trajectory_matches_reference_and_uses_no_library_gemm():
     torch.cuda.synchronize()
     for s, a, b in zip(shapes, p_ref, p_new):
         rel = ((a - b).norm() / a.norm()).item()
+        print(s, f"rel {rel:.2e}")
         assert rel < 1e-3, (s, rel)
