@@ -46,6 +46,11 @@ def _common_flags(p: argparse.ArgumentParser):
     p.add_argument("--steps_per_epoch", default=0, type=int, help="cap steps per epoch (0 = full epoch)")
     p.add_argument("--eval_steps", default=0, type=int, help="cap eval batches (0 = full test set)")
     p.add_argument("--cuda_graph", action="store_true", help="capture the train step in CUDA graphs")
+    p.add_argument("--dtype", default="bf16", choices=["bf16", "fp16"],
+                   help="bf16 (default): no loss scaling needed.  fp16: the reference's AMP flow (resnet50_test.py:533-548) — "
+                        "dynamic loss scaling through backward, unscale, found-inf skip, scale update, all on the device; "
+                        "the sm_100a kernels keep bf16 storage (fp32 exponent range), so this exercises the GradScaler "
+                        "logic rather than half-precision storage")
     p.add_argument("--lr_scale", default=None, type=float, help="LR multiplier under --distributed (reference: 4)")
     p.add_argument("--log_every", default=50, type=int)
     p.add_argument("--seed", default=123456, type=int)
@@ -76,6 +81,14 @@ def _wrap(model, args, device, default_mode):
     if args.distributed and mode == "fsdp":
         return FullyShardedEngine(model, comm, allocator=allocator), comm
     return DataParallelEngine(model, comm, allocator=allocator), comm
+
+
+def _make_scaler(args, device):
+    """``--dtype fp16`` → the device-side GradScaler equivalent; bf16 needs none."""
+    if getattr(args, "dtype", "bf16") != "fp16":
+        return None
+    from .engine.amp import DynamicLossScaler
+    return DynamicLossScaler(device)
 
 
 def _progress(tag, epoch, step, nsteps, metrics: DeviceMetrics):
@@ -223,7 +236,8 @@ def run_resnet(args, tuning=False):
     if args.resume:
         ckpt.load_optimizer_sidecar("resnet", optimizer, scheduler, args.ckpt_dir, rank,
                                     bool(getattr(engine, "optimizer_state_sharded", False)))
-    trainer = Trainer(engine, optimizer, ResNetStep(args.alpha, meta), clip_norm=10.0, use_cuda_graph=args.cuda_graph)
+    trainer = Trainer(engine, optimizer, ResNetStep(args.alpha, meta), clip_norm=10.0, use_cuda_graph=args.cuda_graph,
+                      scaler=_make_scaler(args, device))
 
     n_epochs = args.epoch
     training_acc, testing_acc = np.zeros(n_epochs), []
@@ -366,7 +380,8 @@ def run_transformer(args, tuning=False):
     if args.resume:
         ckpt.load_optimizer_sidecar("transformer", optimizer, scheduler, args.ckpt_dir, rank,
                                     bool(getattr(engine, "optimizer_state_sharded", False)))
-    trainer = Trainer(engine, optimizer, TransformerStep(), clip_norm=10.0, use_cuda_graph=args.cuda_graph)
+    trainer = Trainer(engine, optimizer, TransformerStep(), clip_norm=10.0, use_cuda_graph=args.cuda_graph,
+                      scaler=_make_scaler(args, device))
 
     training_accuracy, testing_accuracy = [], []
     training_time_epoch = np.zeros(max(epochs_total - start_epoch, 1))

@@ -181,3 +181,53 @@ def test_transformer_variable_length_epoch_is_native():
     assert _lib.FALLBACKS.count == before
     assert _lib.LAUNCHES.by_name.get("fdt_attn_fwd", 0) - n_fused0 == 3 * 6
     assert torch.isfinite(eng.flat.grad_flat).all()
+
+
+def test_cli_fp16_loss_scaling_with_madgrad_graph(tmp_path):
+    """--dtype fp16 (device-side GradScaler flow) + the non-NGD default optimizer (flat, graph-capturable MADGRAD)."""
+    out = _run_cli("resnet50_test.py", "--epoch", "1", "--bs", "64", "--model", "resnet18", "--dtype", "fp16", "--steps_per_epoch", "16",
+                   "--eval_steps", "1", "--cuda_graph", "--ckpt_dir", str(tmp_path))
+    assert "test acc" in out
+
+
+@pytest.mark.parametrize("opt_name", ["madgrad", "mirror", "ngd"])
+def test_graph_replay_follows_lr_and_momentum_schedules(opt_name):
+    """A captured CUDA graph must not freeze lr / momentum / step count: the graph-replayed trajectory with an LR (and,
+    for NGD, momentum) schedule equals the eager one (same data, deterministic model without atomics-heavy layers)."""
+    import torch
+    from fdt.engine.trainer import Trainer
+    from fdt.optim import MADGRAD, NGD, MirrorMADGRAD
+    from fdt.parallel.ddp import DataParallelEngine
+    dev = torch.device("cuda")
+
+    def run(use_graph):
+        torch.manual_seed(0)
+        model = torch.nn.Sequential(torch.nn.Linear(32, 64, bias=False), torch.nn.Tanh(), torch.nn.Linear(64, 16, bias=False)).to(dev)
+        eng = DataParallelEngine(model)
+        params = eng.optimizer_params()
+        opt = {"madgrad": lambda: MADGRAD(params, lr=1e-2, momentum=0.9, weight_decay=1e-5),
+               "mirror": lambda: MirrorMADGRAD(params, lr=1e-2, momentum=0.9),
+               "ngd": lambda: NGD(params, lr=1e-2, momentum=0.9, weight_decay=1e-4)}[opt_name]()
+
+        def fwd(e, batch):
+            x, y = batch
+            out = e(x)
+            return torch.nn.functional.mse_loss(out, y), out.detach().sum()
+
+        tr = Trainer(eng, opt, fwd, clip_norm=10.0, use_cuda_graph=use_graph, graph_warmup=3)
+        g = torch.Generator(device=dev).manual_seed(1)
+        X = torch.randn(24, 64, 32, device=dev, generator=g)
+        Y = torch.randn(24, 64, 16, device=dev, generator=g)
+        for i in range(24):
+            for grp in opt.param_groups:                       # a schedule stepping every iteration
+                grp["lr"] = 1e-2 * (0.9 ** i)
+                if opt_name == "ngd":
+                    grp["momentum"] = 0.9 - 0.01 * i
+            tr.step((X[i], Y[i]))
+        torch.cuda.synchronize()
+        assert (not use_graph) or tr._graphs, "no graph was captured"
+        return eng.flat.param_flat.clone()
+
+    a, b = run(False), run(True)
+    rel = ((a - b).norm() / a.norm()).item()
+    assert rel < 1e-4, rel
