@@ -341,6 +341,76 @@ all_gather_range_kernel(const CommCtx c, const int64_t* __restrict__ sub, __nv_b
     block_barrier(c, (nb + blockIdx.x) * c.world);
 }
 
+// Broadcast of ONE owner's large range [lo, hi) to every rank in two phases, so that the owner's NVLink egress is one copy of
+// the range instead of world-1 copies (a 62 MB token embedding owned by one rank would otherwise take 7 x 62 MB out of a single
+// GPU): the range is cut into `world` slices; phase 1: rank r pulls slice r from the owner; flag barrier; phase 2: rank r pulls
+// slice s from rank s, for every s.  Block b handles portion b of every slice, so the per-block barrier (block b of every rank)
+// covers exactly the data block b reads in phase 2.  The bf16 shadow of everything that lands (and of the owner's own copy)
+// is written in the same pass.
+__device__ __forceinline__ void copy_cast_span(const float* __restrict__ src, float* __restrict__ dst, __nv_bfloat16* __restrict__ shadow,
+                                               int64_t s0, int64_t s1, bool store_f32) {
+    constexpr int U = 4;
+    for (int64_t i = s0 + threadIdx.x * 4; i < s1; i += (int64_t)kBlock * 4 * U) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t e = i + (int64_t)u * kBlock * 4;
+            if (e < s1) v[u] = ld_cg(src + e);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t e = i + (int64_t)u * kBlock * 4;
+            if (e < s1) {
+                if (store_f32) st_cg(dst + e, v[u]);
+                if (shadow) {
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(v[u].x, v[u].y), h1 = __floats2bfloat162_rn(v[u].z, v[u].w);
+                    *reinterpret_cast<uint2*>(shadow + e) = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBlock)
+bcast_two_phase_kernel(const CommCtx c, int owner, int64_t lo, int64_t hi, __nv_bfloat16* __restrict__ shadow) {
+    const int nb = gridDim.x;
+    block_barrier(c, blockIdx.x * c.world);                           // the owner's range is final
+    float* mine = c.buf[c.rank];
+    const int64_t len = hi - lo;
+    const int64_t slice = ((len / 4 + c.world - 1) / c.world) * 4;    // elements per slice (multiple of 4)
+    const int64_t per = ((slice / 4 + nb - 1) / nb) * 4;              // elements of a slice handled by one block
+    auto span = [&](int s, int64_t& a, int64_t& b) {
+        const int64_t sl0 = lo + min(len, slice * s), sl1 = lo + min(len, slice * s + slice);
+        a = min(sl1, sl0 + per * blockIdx.x);
+        b = min(sl1, a + per);
+    };
+    int64_t a, b;
+    if (c.rank != owner) {
+        span(c.rank, a, b);
+        copy_cast_span(c.buf[owner], mine, shadow, a, b, true);       // phase 1: my slice, from the owner
+    }
+    block_barrier(c, (nb + blockIdx.x) * c.world);                    // slice s (portion b) is valid on rank s
+    for (int k = 1; k <= c.world; ++k) {
+        const int s = (c.rank + k) % c.world;                         // rotated: spread the load over the peers
+        if (s == c.rank && c.rank != owner) continue;                 // my own slice: copied (and cast) in phase 1
+        span(s, a, b);
+        const bool local = (c.rank == owner);                         // the owner already holds everything: cast only
+        const int src_rank = local ? owner : s;
+        copy_cast_span(c.buf[src_rank], mine, shadow, a, b, !local);
+    }
+    block_barrier(c, (2 * nb + blockIdx.x) * c.world);                // nobody still reads my copy when I go on to overwrite it
+}
+
+// [lo, hi): absolute element offsets (multiples of 4) of a range owned by rank `owner`.  blocks <= 85 (3 barriers per block).
+FDT_API int fdt_comm_bcast_range(const void* ctx, int owner, int64_t lo, int64_t hi, void* shadow_bf16, int blocks, cudaStream_t st) {
+    CommCtx c = *static_cast<const CommCtx*>(ctx);
+    if (c.world < 2 || c.world > kMaxWorld || owner < 0 || owner >= c.world || (lo % 4) || (hi % 4) || hi < lo) return -1;
+    if (blocks < 1 || blocks > 85) return -1;
+    bcast_two_phase_kernel<<<blocks, kBlock, 0, st>>>(c, owner, lo, hi, (__nv_bfloat16*)shadow_bf16);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
 // sub: DEVICE pointer to 2*world int64 {lo_r, hi_r} (multiples of 4, absolute element offsets; hi_r == lo_r allowed).
 FDT_API int fdt_comm_all_gather_range(const void* ctx, const int64_t* sub, void* shadow_bf16, int blocks, cudaStream_t st) {
     CommCtx c = *static_cast<const CommCtx*>(ctx);

@@ -121,9 +121,19 @@ class DataParallelEngine(nn.Module):
         cap_rs = int(os.environ.get("FDT_COMM_BLOCKS", "64"))
         self._rs_blocks = [_blocks_for(max(hi - lo for lo, hi in flat.bucket_ranges[k]), min(cap_rs, 64)) for k in range(nb)]
         # forward stage s <-> gradient bucket nb-1-s: the same sub-range of every rank's region
-        self._ag_tables, self._ag_blocks = [], []
+        # A range far larger than its peers' (one rank owns the 62 MB token embedding) is taken out of the pull all-gather —
+        # world-1 ranks pulling it at once would be limited by that one owner's egress — and broadcast in two phases.
+        self._ag_tables, self._ag_blocks, self._ag_bcast = [], [], []
         for s in range(nb):
-            rng = flat.bucket_ranges[nb - 1 - s]
+            rng = list(flat.bucket_ranges[nb - 1 - s])
+            mean = sum(hi - lo for lo, hi in rng) / comm.world
+            big = []
+            if os.environ.get("FDT_BCAST_2PHASE", "1") == "1":
+                for r, (lo, hi) in enumerate(rng):
+                    if hi - lo > max(1 << 20, 2 * mean):
+                        big.append((r, lo, hi, _blocks_for(hi - lo, 85)))
+                        rng[r] = (lo, lo)
+            self._ag_bcast.append(big)
             self._ag_tables.append(torch.tensor([v for lo_hi in rng for v in lo_hi], dtype=torch.int64, device=dev))
             self._ag_blocks.append(_blocks_for(max(hi - lo for lo, hi in rng), 128))
         if flat.shadow_flat is None:
@@ -176,6 +186,8 @@ class DataParallelEngine(nn.Module):
             n = len(self._ag_tables)
             for s in range(n):
                 symm.all_gather_range_(flat.param_flat, self._ag_tables[s], flat.shadow_flat, self._ag_blocks[s], channel=1)
+                for owner, lo, hi, blocks in self._ag_bcast[s]:
+                    symm.bcast_range_(flat.param_flat, owner, lo, hi, flat.shadow_flat, blocks, channel=1)
                 if s == n - 1:
                     flat.refresh_dgrad_shadow()          # backward's transposed operands need the whole shadow
                 e = torch.cuda.Event()

@@ -148,6 +148,13 @@ class SymmetricHeap:
         the bf16 shadow of the same elements.  ``sub_dev``: int64 device tensor, identical on all ranks."""
         _lib.call("fdt_comm_all_gather_range", ctypes.byref(self.channel_ctx(flat, channel)), sub_dev, shadow, int(blocks))
 
+    def bcast_range_(self, flat: torch.Tensor, owner: int, lo: int, hi: int, shadow: Optional[torch.Tensor], blocks: int,
+                     channel: int = 1):
+        """Two-phase broadcast of ``flat[lo:hi]`` from ``owner`` to every rank (scatter slices, then all-gather them), with the
+        bf16 shadow of the same elements; for ranges so large that world-1 direct pulls would saturate the owner's links."""
+        _lib.call("fdt_comm_bcast_range", ctypes.byref(self.channel_ctx(flat, channel)), int(owner), _lib.i64(lo), _lib.i64(hi),
+                  shadow, int(blocks))
+
     def multicast_addr(self, t: torch.Tensor) -> int:
         return int(self._ctx(t).mc or 0)
 

@@ -253,6 +253,8 @@ int fdt_comm_all_gather_cast(const void* ctx, int64_t region, void* shadow_bf16,
  * fdt_comm_reduce_scatter_range calls until fdt_comm_take_scalar. */
 int fdt_comm_reduce_scatter_range(const void* ctx, int64_t lo, int64_t hi, int blocks, int use_multicast, cudaStream_t st);
 int fdt_comm_all_gather_range(const void* ctx, const int64_t* sub, void* shadow_bf16, int blocks, cudaStream_t st);
+/* broadcast of one owner's large range in two phases (scatter slices, then all-gather them): owner egress = 1x the range */
+int fdt_comm_bcast_range(const void* ctx, int owner, int64_t lo, int64_t hi, void* shadow_bf16, int blocks, cudaStream_t st);
 int fdt_comm_barrier(const void* ctx, cudaStream_t st);
 int fdt_comm_take_scalar(float* slot, float* out, cudaStream_t st);
 int fdt_comm_mc_red_add(float* dst_mc, const float* src, int64_t n, float alpha, cudaStream_t st);

@@ -144,6 +144,23 @@ def check_ranges(heap, dev, rank, world):
     torch.cuda.current_stream().wait_stream(side)
     ok &= check("all_gather_range", buf, truth, 0, 0)
     ok &= bool(torch.equal(shadow, truth.bfloat16()))
+    # two-phase broadcast of one owner's range (odd length in vectors, not a multiple of world or of the block count)
+    owner = world - 1
+    lo, hi = 4 * 13, 4 * 13 + 4 * 100003
+    nb = heap.alloc_f32(hi + 64)
+    truth2 = torch.randn(hi + 64, device=dev, generator=torch.Generator(device=dev).manual_seed(123))
+    nb.fill_(-7.0)
+    if rank == owner:
+        nb[lo:hi] = truth2[lo:hi]
+    shadow2 = torch.zeros(hi + 64, dtype=torch.bfloat16, device=dev)
+    torch.cuda.synchronize()
+    dist.barrier()
+    with torch.cuda.stream(side):
+        heap.bcast_range_(nb, owner, lo, hi, shadow2, blocks=7, channel=1)
+    torch.cuda.current_stream().wait_stream(side)
+    ok &= check("bcast_range", nb[lo:hi], truth2[lo:hi], 0, 0)
+    ok &= bool(torch.equal(shadow2[lo:hi], truth2[lo:hi].bfloat16()))
+    ok &= bool((nb[:lo] == -7.0).all()) and bool((nb[hi:] == -7.0).all())
     if rank == 0:
         print(f"range collectives: {'ok' if ok else 'MISMATCH'}", flush=True)
     return ok
