@@ -45,6 +45,19 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
     return out
 
 
+def gemm2_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act: str = "none",
+             addend: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    """The 2-CTA kernel (csrc/gemm2_sm100.cu): clusters of two CTAs, ``tcgen05.mma.cta_group::2`` on 256 x 256 tiles.
+    bf16 out; N % 256 == 0, K % 64 == 0."""
+    M, K = a.shape
+    N = b.shape[0]
+    if K % 64 or N % 256 or M < 1 or not (a.is_contiguous() and b.is_contiguous()):
+        return None
+    out = torch.empty(M, N, dtype=BF16, device=a.device)
+    call("fdt_gemm2_nt", a, b, out, bias, addend, M, N, K, ACT[act])
+    return out
+
+
 def _conv_ok(x, w16, stride, padding) -> bool:
     """Shapes the implicit-GEMM kernel covers: stride 1 or 2, "same"-style padding (pad = k // 2), channel counts that are
     multiples of 64 and an OUTPUT width that is a power of two <= 128 (a 128-pixel tile = whole rows / whole images)."""

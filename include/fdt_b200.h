@@ -146,6 +146,10 @@ int fdt_gemm_nt(const void* A, const void* B, void* out_bf16, float* out_f32, co
 /* y[Nb,H,W,Cout] = conv(x[Nb,H,W,Cin], w[Cout,k,k,Cin]), stride 1, pad = k/2, NHWC bf16 (implicit GEMM: shifted 4-D TMA boxes). */
 int fdt_conv_fwd(const void* x, const void* w, void* y, float* sums, int Nb, int H, int W, int Cin, int Cout,
                  int ksize, int pad, cudaStream_t st);
+/* 2-CTA form (csrc/gemm2_sm100.cu): thread-block clusters of two CTAs, tcgen05.mma.cta_group::2 on 256 x 256 tiles, each CTA
+ * staging half of A and half of B; N % 256 == 0, K % 64 == 0.  out bf16 = act(A B^T + bias) [+ addend]. */
+int fdt_gemm2_nt(const void* A, const void* B, void* out_bf16, const float* bias, const void* addend, int M, int N, int K,
+                 int act, cudaStream_t st);
 /* generalised forms: `addend` (optional bf16 tensor indexed like the output, may alias it) is added in the epilogue — the
  * other branch's gradient at a residual fork; fdt_conv_ex also takes stride 2 (TMA element strides, no im2col);
  * fdt_conv_dgrad_s2 is the data gradient of a stride-2 convolution as four parity-class implicit GEMMs (no col2im):

@@ -341,3 +341,24 @@ def test_attention_dropout_long_sequence_consistent():
     assert torch.isfinite(vv.grad.float()).all()
     assert torch.allclose(vv.grad.float(), col.unsqueeze(-1).expand_as(vv.grad), rtol=2e-2, atol=2e-2)
     assert abs(col.sum().item() / (B * H * L) - 1.0) < 0.05
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 256, 128), (1000, 512, 512), (8192, 1536, 512), (333, 256, 192), (4096, 1024, 1024)])
+@pytest.mark.parametrize("act,bias,addend", [("none", False, False), ("gelu", True, False), ("none", False, True)])
+def test_gemm2_two_cta(M, N, K, act, bias, addend):
+    """2-CTA kernel (thread-block clusters, tcgen05.mma.cta_group::2, 256 x 256 tiles) against fp32 matmul."""
+    from fdt.ops import gemm_sm100 as g
+    torch.manual_seed(21)
+    a = (torch.randn(M, K, device="cuda") / math.sqrt(K)).bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bi = torch.randn(N, device="cuda") if bias else None
+    ad = torch.randn(M, N, device="cuda").bfloat16() if addend else None
+    out = g.gemm2_nt(a, b, bi, act, ad)
+    assert out is not None and out.dtype == torch.bfloat16
+    ref = a.float() @ b.float().t()
+    if bias:
+        ref = ref + bi
+    ref = {"none": lambda t: t, "gelu": F.gelu}[act](ref)
+    if addend:
+        ref = ref + ad.float()
+    assert _rel(out, ref) < 6e-3, _rel(out, ref)

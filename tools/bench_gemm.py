@@ -36,8 +36,24 @@ def graph_time(fns, reps=10):
     return ts[len(ts) // 2] * 1e3 / len(fns)
 
 
+def gemm_table():
+    print("gemm: us 1-CTA kernel | us 2-CTA kernel (cta_group::2) | us cublas | TFLOP/s 1-CTA | TFLOP/s 2-CTA | TFLOP/s cublas")
+    for (M, N, K) in [(8192, 512, 512), (8192, 1536, 512), (8192, 1024, 512), (8192, 512, 1024), (131072, 256, 64),
+                      (4096, 4096, 4096), (8192, 8192, 8192)]:
+        nb = 2 if M * N > 5e7 else 6
+        As = [torch.randn(M, K, device="cuda").bfloat16() for _ in range(nb)]
+        b = torch.randn(N, K, device="cuda").bfloat16()
+        tn = graph_time([(lambda a=a: g.gemm_nt(a, b)) for a in As])
+        t2 = graph_time([(lambda a=a: g.gemm2_nt(a, b)) for a in As])
+        tl = graph_time([(lambda a=a: F.linear(a, b)) for a in As])
+        fl = 2 * M * N * K / 1e6
+        print(f"M{M} N{N} K{K}: {tn:8.1f} | {t2:8.1f} | {tl:8.1f} | {fl / tn:7.1f} | {fl / t2:7.1f} | {fl / tl:7.1f}")
+
+
 def main():
     torch.backends.cudnn.benchmark = True
+    if "--gemm-only" in sys.argv:
+        return gemm_table()
     B = 128
     print("conv fwd (N=128): us native | us cudnn | TFLOP/s native | GB/s native (min traffic)")
     for (C, O, HW, k) in [(64, 64, 32, 3), (64, 64, 32, 1), (64, 256, 32, 1), (256, 64, 32, 1), (128, 128, 16, 3), (128, 512, 16, 1),
@@ -51,14 +67,7 @@ def main():
         tl = graph_time([(lambda x=x: F.conv2d(x, w, padding=k // 2)) for x in xs])
         fl = 2 * B * HW * HW * C * O * k * k
         print(f"C{C:4d} O{O:4d} {HW:2d}x{HW:<2d} k{k}: {tn:8.1f} | {tl:8.1f} | {fl / tn / 1e6:7.1f} | {by / tn / 1e3:7.0f}")
-    print("gemm: us native | us cublas | TFLOP/s native")
-    for (M, N, K) in [(8192, 512, 512), (8192, 1536, 512), (8192, 1024, 512), (8192, 512, 1024), (8192, 8192, 8192)]:
-        nb = 2 if M * N > 5e7 else 6
-        As = [torch.randn(M, K, device="cuda").bfloat16() for _ in range(nb)]
-        b = torch.randn(N, K, device="cuda").bfloat16()
-        tn = graph_time([(lambda a=a: g.gemm_nt(a, b)) for a in As])
-        tl = graph_time([(lambda a=a: F.linear(a, b)) for a in As])
-        print(f"M{M} N{N} K{K}: {tn:8.1f} | {tl:8.1f} | {2 * M * N * K / tn / 1e6:7.1f}")
+    gemm_table()
     print("channel kernels: [P,C] bf16: us reduce2(stats) GB/s | us affine_act GB/s")
     for (P, C) in [(131072, 64), (131072, 256), (32768, 512), (8192, 1024), (2048, 2048)]:
         nb = max(2, min(8, int(200e6 // (P * C * 2)) + 1))
