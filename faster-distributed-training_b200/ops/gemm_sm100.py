@@ -20,6 +20,7 @@ from ._lib import call, i64
 BF16 = torch.bfloat16
 ACT = {"none": 0, "relu": 1, "celu": 2, "gelu": 3, "tanh": 4}
 _DISABLED = os.environ.get("FDT_GEMM", "auto") == "library"
+_GEMM2 = os.environ.get("FDT_GEMM2", "1") == "1"      # route large GEMMs to the 2-CTA kernel (csrc/gemm2_sm100.cu)
 
 
 def available() -> bool:
@@ -39,6 +40,10 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
     if K % 64 or N % 64 or M < 1 or not (a.is_contiguous() and b.is_contiguous()):
         return None
     out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+    if _GEMM2 and sums is None and out_dtype == BF16 and N % 256 == 0 and M >= 1024:
+        # large plain GEMMs (the transformer's Linear layers): 2-CTA clusters, tcgen05.mma.cta_group::2 on 256 x 256 tiles
+        call("fdt_gemm2_nt", a, b, out, bias, addend, M, N, K, ACT[act])
+        return out
     o16 = out if out_dtype == BF16 else None
     o32 = out if out_dtype == torch.float32 else None
     call("fdt_gemm_nt_ex", a, b, o16, o32, bias, sums, addend, M, N, K, ACT[act])

@@ -11,7 +11,8 @@ cap() {  # name target regex skip
 }
 cap conv3x3 conv3x3 gemm_nt 2
 cap conv1x1 conv1x1 gemm_nt 2
-cap gemm gemm gemm_nt 1
+cap gemm gemm1 gemm_nt_kernel 1
+cap gemm2 gemm2 gemm2_nt 1
 cap wgrad wgrad wgrad_kernel 2
 cap attn_fwd attn attn_fwd 1
 cap attn_bwd attn attn_bwd 1
@@ -24,3 +25,21 @@ cap ngd_tc_deflate ngd_tc tf32_gemm 4
 cap ngd_tc_stats ngd_tc tf32_gemm 5
 cap lin_prep lin_prep linear_bwd_prep 2
 cap wprep wprep dgrad_weights 2
+cap conv_s2_fwd conv_s2 gemm_nt_kernel 2
+cap conv_s2_dgrad conv_s2 gemm_nt_kernel 5
+cap attn512_fwd attn512 attn_fwd 1
+cap attn512_bwd attn512 attn_bwd 1
+cap ln_fwd rowwise ln_fwd 1
+cap ln_bwd rowwise ln_bwd 1
+cap embed_fwd rowwise embed_fwd 1
+cap embed_bwd rowwise embed_bwd 1
+cap mixup_ce rowwise mixup_ce 1
+cap head_mix rowwise head_mix_fwd 1
+cap sgd_momentum optim sgd_momentum_dev 1
+cap clip_wd optim clip_wd 1
+cap madgrad optim madgrad_dev 1
+cap input_aug_mixup input_head input_aug_mixup_kernel 1
+cap input_aug_mixup_bwd input_head input_aug_mixup_bwd 1
+cap pool_fc_fwd input_head pool_fc_fwd 1
+cap pool_fc_bwd input_head pool_fc_bwd 1
+cap ngd_small_matrix ngd_small ngd_small_matrix 1
