@@ -16,12 +16,16 @@ def main():
     ap.add_argument("--bs", type=int, default=None)
     ap.add_argument("--kinds", default="plain,update")
     ap.add_argument("--dump", default=None)
+    ap.add_argument("--mode", default="ddp", choices=["ddp", "fsdp"])
     args = ap.parse_args()
     import bench
-    dev = torch.device("cuda", 0)
+    rank, local, world = bench.dist_env()          # under torchrun: one rank per GPU, rank 0 reports
+    torch.cuda.set_device(local)
+    bench.init_dist(world)
+    dev = torch.device("cuda", local)
     bs = args.bs or (128 if args.model == "resnet50" else 64)
-    tr, _ = bench.build_fdt(args.model, bs, dev, 1, True, "ddp")
-    loader = bench.make_host_batches(args.model, bs, 4, 128, 0)
+    tr, _ = bench.build_fdt(args.model, bs, dev, world, True, args.mode)
+    loader = bench.make_host_batches(args.model, bs, 4, 128, rank)
     batches = [tuple(t.to(dev) for t in b) for b in loader]
     for i in range(24):
         tr.step(batches[i % 4])
@@ -41,6 +45,8 @@ def main():
             torch.cuda.synchronize()
         evs = [e for e in prof.profiler.kineto_results.events() if e.device_type() == torch.autograd.DeviceType.CUDA]
         evs = sorted(evs, key=lambda e: e.start_ns())
+        if rank != 0:
+            continue
         if not evs:
             print("no device events")
             continue
@@ -68,6 +74,13 @@ def main():
         print("  first wgrad at", first(lambda n: "wgrad" in n), " last wgrad end", last(lambda n: "wgrad" in n))
         print("  first ngd kernel at", first(lambda n: "ngd" in n), " last", last(lambda n: "ngd" in n))
         print("  sgd_momentum at", first(lambda n: "sgd_momentum" in n))
+        if world > 1:
+            # collectives of the sharded step: reduce-scatter buckets (should start inside backward, i.e. before the last
+            # wgrad ends) and the staged all-gather / broadcast (should overlap the forward pass)
+            for e in evs:
+                n = e.name()
+                if "reduce_kernel" in n or "all_gather" in n or "bcast_two_phase" in n or "take_scalar" in n:
+                    print(f"  comm  {(e.start_ns() - t0) / 1e6:8.3f} ms  +{e.duration_ns() / 1e3:7.1f} us  stream {e.device_resource_id():<4d} {n[:70]}")
         # gaps on the union timeline (no kernel running anywhere)
         cur = t0
         idle = 0
@@ -84,3 +97,5 @@ def main():
 
 if __name__ == "__main__":
     main()
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()
