@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "faster-distributed-training_b200", "build")
 INTEREST = re.compile(r"^(UTCHMMA|UTCQMMA|UTCIMMA|UTCOMMA|UTC[A-Z]*MMA|UTMALDG|UTMASTG|UTMAPF|UTMACCTL|LDTM|STTM|UTCBAR|UTCATOMSWS|SYNCS|REDG|RED|ATOMG|ATOMS|"
                       r"LDG\.E\.128|STG\.E\.128|LDS\.128|STS\.128|MEMBAR|REDUX|ACQBULK|PREEXIT|MULTIMEM|LDGMC|HMMA|FFMA)")
-KEEP_FULL = {"gemm_sm100", "wgrad_sm100", "attention_sm100", "comm", "ngd_gemm_sm100"}
+KEEP_FULL = None      # full gzipped listing for every source file
 
 
 def main():
@@ -22,7 +22,7 @@ def main():
     for obj in sorted(f for f in os.listdir(OBJ) if f.endswith(".o")):
         name = obj[:-2]
         txt = subprocess.run(["cuobjdump", "-sass", os.path.join(OBJ, obj)], capture_output=True, text=True).stdout
-        if name in KEEP_FULL:
+        if KEEP_FULL is None or name in KEEP_FULL:
             with gzip.open(os.path.join(ROOT, "profiles", f"sass_{name}.txt.gz"), "wt") as f:
                 f.write(txt)
         out.append(f"\n## {name}.cu\n")
