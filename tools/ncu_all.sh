@@ -3,11 +3,19 @@
 # command has exited 0 without ncu, as the profiling recipe requires.
 set -u
 mkdir -p gpurun_out
+KEEP="gemm2 gemm conv3x3 conv_s2_dgrad attn512_fwd attn512_bwd wgrad ngd_tc_project"   # full reports kept (gpurun_out is capped at 64 MiB)
 cap() {  # name target regex skip
-  python tools/ncu_target.py "$2" > gpurun_out/plain_$1.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k "regex:$3" -s "$4" -c 1 -o gpurun_out/prof_$1 \
+  if [ ! -f gpurun_out/plain_ok_$2 ]; then
+    python tools/ncu_target.py "$2" > gpurun_out/plain_$2.log 2>&1 && touch gpurun_out/plain_ok_$2
+  fi
+  [ -f gpurun_out/plain_ok_$2 ] || { echo "plain run of $2 failed: not profiled"; return; }
+  ncu --set full --clock-control none --import-source on -k "regex:$3" -s "$4" -c 1 -f -o gpurun_out/prof_$1 \
       python tools/ncu_target.py "$2" > gpurun_out/ncu_$1.log 2>&1
   tail -1 gpurun_out/ncu_$1.log
+  # the raw metric page as CSV (what tools/ncu_summary.py reads); drop the report itself unless it is on the keep list
+  ncu -i gpurun_out/prof_$1.ncu-rep --page raw --csv > gpurun_out/ncuraw_$1.csv 2>/dev/null
+  case " $KEEP " in *" $1 "*) ;; *) rm -f gpurun_out/prof_$1.ncu-rep ;; esac
+  rm -f gpurun_out/ncu_$1.log
 }
 cap conv3x3 conv3x3 gemm_nt 2
 cap conv1x1 conv1x1 gemm_nt 2

@@ -35,13 +35,18 @@ def to_unit(val, unit, want):
 
 
 rows = []
-for rep in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", "prof_*.ncu-rep"))):
-    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+reps = sorted(glob.glob(os.path.join(ROOT, "gpurun_out", "ncuraw_*.csv"))) or sorted(glob.glob(os.path.join(ROOT, "gpurun_out", "prof_*.ncu-rep")))
+for rep in reps:
+    if rep.endswith(".csv"):          # exported on the GPU box by tools/ncu_all.sh (the reports themselves are too large to bring back)
+        out = open(rep).read()
+    else:
+        out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     r = list(csv.reader(io.StringIO(out)))
     if len(r) < 3:
         continue
     hdr, units, vals = r[0], r[1], r[2]
-    d = {"capture": os.path.basename(rep)[5:-8], "kernel": vals[hdr.index("Kernel Name")][:70] if "Kernel Name" in hdr else "?"}
+    base = os.path.basename(rep)
+    d = {"capture": base[7:-4] if base.endswith(".csv") else base[5:-8], "kernel": vals[hdr.index("Kernel Name")][:70] if "Kernel Name" in hdr else "?"}
     for h, u, v in zip(hdr, units, vals):
         if h in KEYS and v:
             try:
