@@ -533,3 +533,29 @@ def test_ngd_gpu_trajectory_matches_reference_and_uses_no_library_gemm():
         rel = ((a - b).norm() / a.norm()).item()
         print(s, f"rel {rel:.2e}")
         assert rel < 1e-3, (s, rel)
+
+
+def test_batch_stat_normalisation_form_is_the_references():
+    """The FusedConvBN form — UNBIASED variance, eps added to the standard deviation (resnet.py:85-100) — checked where it
+    matters: 32 values per channel (biased vs unbiased differ by 1.6 %) and a conv output whose std is comparable to eps
+    (eps inside vs outside the sqrt differ by tens of per cent).  Runs under strict mode: native kernels only."""
+    from fdt.ops import _lib
+    ops = _ops()
+    torch.manual_seed(11)
+    N, C, hw = 2, 64, 4
+    x = torch.randn(N, C, hw, hw, device=DEV)
+    w = torch.randn(C, C, 1, 1, device=DEV) / math.sqrt(C) * 2e-3          # conv output std ~ 2e-3, eps = 1e-3
+    xr, wr = x.bfloat16().float(), w.bfloat16().float()
+    y = torch.nn.functional.conv2d(xr, wr)
+    mean = y.mean((0, 2, 3), keepdim=True)
+    want = (y - mean) / (y.var((0, 2, 3), unbiased=True, keepdim=True).sqrt() + 1e-3)
+    biased = (y - mean) / (y.var((0, 2, 3), unbiased=False, keepdim=True).sqrt() + 1e-3)
+    inside = (y - mean) / (y.var((0, 2, 3), unbiased=True, keepdim=True) + 1e-3).sqrt()
+    _lib.set_strict(True)
+    try:
+        out = ops.conv_bnstat_act(x.bfloat16().to(memory_format=torch.channels_last), w.clone(), 1, 0, 1e-3, "none", None)
+    finally:
+        _lib.set_strict(False)
+    rel = lambda a, b: ((a.float() - b).norm() / b.norm()).item()
+    assert rel(out, want) < 6e-3, rel(out, want)
+    assert rel(out, want) < 0.5 * rel(out, biased) and rel(out, want) < 0.1 * rel(out, inside)

@@ -16,8 +16,8 @@ def test_resnet_forward_matches_oracle():
         ref = m(x)
         out = m.cuda()(x.cuda())
     assert out.dtype == torch.float32
-    err = (out.cpu() - ref).abs().max().item()
-    assert err < 0.15 * max(ref.abs().max().item(), 1.0), err
+    rel = ((out.cpu() - ref).norm() / ref.norm()).item()          # bf16 end to end through 20 conv+BN units vs the fp32 oracle
+    assert rel < 3e-2, rel
 
 
 def test_transformer_forward_matches_oracle():
@@ -31,8 +31,8 @@ def test_transformer_forward_matches_oracle():
     with torch.no_grad():
         ref = m(tok, typ, None, mask)
         out = m.cuda()(tok.cuda(), typ.cuda(), None, mask.cuda())
-    err = (out.float().cpu() - ref).abs().max().item()
-    assert err < 0.1 * max(ref.abs().max().item(), 1.0), err
+    rel = ((out.float().cpu() - ref).norm() / ref.norm()).item()
+    assert rel < 3e-2, rel
 
 
 @pytest.mark.parametrize("graph", [False, True])
