@@ -152,8 +152,7 @@ class ResNetStep:
         targets = targets.long()
         if self.meta is None and images.dtype == torch.uint8 and ops.use_native(images):
             # one kernel: crop + flip + normalise of both partners, λ-blend, bf16 NHWC out
-            lam = mx.sample_beta(self.alpha, images.device)
-            index = mx.randperm(images.size(0), images.device)
+            lam, index = mx.sample_mixup(self.alpha, images.size(0), images.device)
             x = ops._cu().input_aug_mixup(images, True, index, lam, cifar_data.MEAN, cifar_data.STD)
             ya, yb = targets, targets[index]
             logits = engine(x)

@@ -194,3 +194,65 @@ FDT_API int fdt_pool_fc_bwd(const float* dlogits, const float* W, const float* p
     FDT_CHECK_LAUNCH();
     return 0;
 }
+
+// ---- device-side mixup draws ---------------------------------------------------------------------------------------
+// lam ~ Beta(alpha, alpha) and a uniform random permutation of 0..B-1 in ONE tiny launch (the reference samples Beta on the
+// host with `.item()` and calls torch.randperm — resnet50_test.py:359-362; the torch equivalents on the device are ~18
+// small kernels: two Gamma draws, a sort-based randperm, index arithmetic).  One thread does the work: it is O(B).
+namespace {
+__device__ float philox_uniform(const Philox& rng, uint64_t off, uint32_t& ctr) {       // (0, 1]
+    const uint4 r = rng((uint64_t)ctr++, off);
+    return (float)((r.x >> 8) + 1u) * (1.0f / 16777216.0f);
+}
+__device__ float philox_normal(const Philox& rng, uint64_t off, uint32_t& ctr) {
+    const float u1 = philox_uniform(rng, off, ctr), u2 = philox_uniform(rng, off, ctr);
+    return sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);
+}
+// Marsaglia & Tsang (2000); shape < 1 through Gamma(a) = Gamma(a + 1) * U^(1/a)
+__device__ float philox_gamma(const Philox& rng, uint64_t off, uint32_t& ctr, float a) {
+    float boost = 1.f;
+    if (a < 1.f) { boost = powf(philox_uniform(rng, off, ctr), 1.f / a); a += 1.f; }
+    const float d = a - 1.f / 3.f, c = rsqrtf(9.f * d);
+    for (int it = 0; it < 64; ++it) {
+        const float x = philox_normal(rng, off, ctr);
+        float v = 1.f + c * x;
+        if (v <= 0.f) continue;
+        v = v * v * v;
+        const float u = philox_uniform(rng, off, ctr);
+        if (logf(u) < 0.5f * x * x + d - d * v + d * logf(v)) return boost * d * v;
+    }
+    return boost * d;
+}
+__global__ void mixup_sample_kernel(const int64_t* __restrict__ seed_off, float alpha, int B, float* __restrict__ lam,
+                                    int64_t* __restrict__ perm) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Philox rng((uint64_t)seed_off[0]);
+    const uint64_t off = (uint64_t)seed_off[1];
+    uint32_t ctr = 0x40000000u;                          // a counter range of its own (the augmentation draws use b < 2^30)
+    if (lam) {
+        float l = alpha;
+        if (alpha > 0.f) {
+            const float g0 = philox_gamma(rng, off, ctr, alpha), g1 = philox_gamma(rng, off, ctr, alpha);
+            l = g0 / fmaxf(g0 + g1, 1e-20f);
+        }
+        lam[0] = l;
+    }
+    if (perm) {
+        for (int i = 0; i < B; ++i) perm[i] = i;
+        for (int i = B - 1; i > 0; --i) {                // Fisher-Yates
+            const uint4 r = rng((uint64_t)ctr++, off);
+            const int j = (int)(((uint64_t)r.x * (uint64_t)(i + 1)) >> 32);
+            const int64_t t = perm[i]; perm[i] = perm[j]; perm[j] = t;
+        }
+    }
+}
+}  // namespace
+
+// lam [1] ~ Beta(alpha, alpha) (alpha <= 0: lam = alpha, as the reference) and perm [B] = a uniform random permutation,
+// both optional (NULL); seed_off: device (seed, offset) pair.
+FDT_API int fdt_mixup_sample(const int64_t* seed_off, float alpha, int B, float* lam, int64_t* perm, cudaStream_t st) {
+    if (!seed_off || B < 0) return -1;
+    mixup_sample_kernel<<<1, 32, 0, st>>>(seed_off, alpha, B, lam, perm);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}

@@ -22,8 +22,22 @@ import torch.nn as nn
 from .. import ops
 
 
+def _native_draws(device, generator) -> bool:
+    """One-kernel device-side draws (csrc/input_head.cu::fdt_mixup_sample) when no torch generator pins the stream."""
+    return generator is None and torch.device(device).type == "cuda" and not ops._FORCE_TORCH
+
+
+def sample_mixup(alpha: float, n: int, device, generator: Optional[torch.Generator] = None):
+    """(λ ~ Beta(α, α), random permutation of n) — on CUDA one tiny kernel for both, otherwise the torch draws."""
+    if _native_draws(device, generator):
+        return ops._cu().mixup_sample(alpha, n, torch.device(device))
+    return sample_beta(alpha, device, generator=generator), randperm(n, device, generator)
+
+
 def sample_beta(alpha: float, device, shape=(), generator: Optional[torch.Generator] = None) -> torch.Tensor:
     """Draw Beta(α, α) on ``device`` without a host sync (two Gamma draws)."""
+    if shape == () and _native_draws(device, generator):
+        return ops._cu().mixup_sample(alpha, None, torch.device(device))[0]
     if alpha <= 0:
         return torch.full(shape, float(alpha), device=device)
     a = torch.full((2,) + tuple(shape), float(alpha), device=device)
@@ -32,6 +46,8 @@ def sample_beta(alpha: float, device, shape=(), generator: Optional[torch.Genera
 
 
 def randperm(n: int, device, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    if _native_draws(device, generator) and n > 0:
+        return ops._cu().mixup_sample(None, n, torch.device(device))[1]
     return torch.randperm(n, device=device, generator=generator)
 
 
@@ -50,8 +66,7 @@ def mixup_data(x, y, alpha=0.99, intra_only=False, generator=None):
 
     ``intra_only`` leaves same-class pairs unmixed (resnet50_test.py:364-371; vectorised here
     instead of a per-sample Python loop)."""
-    lam = sample_beta(alpha, x.device, generator=generator)
-    index = randperm(x.size(0), x.device, generator)
+    lam, index = sample_mixup(alpha, x.size(0), x.device, generator)
     y_a, y_b = y, y[index]
     if intra_only:
         per = torch.where(y_a == y_b, torch.ones_like(lam), lam).expand(x.size(0))

@@ -68,8 +68,11 @@ class Act(nn.Module):
 
 
 def _conv_bn(conv: nn.Conv2d, bn: nn.BatchNorm2d, x, act="none", residual=None, passthrough=False):
+    # num_batches_tracked of every BatchNorm is advanced by ONE multi-tensor add per forward pass (ResNet.forward) when the
+    # model runs on the native path; the per-unit increment stays for the CPU oracle and for blocks used on their own
+    nbt = None if getattr(bn, "_fdt_nbt_batched", False) else bn.num_batches_tracked
     return ops.conv_bnaffine_act(
-        x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked,
+        x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, nbt,
         conv.stride[0], conv.padding[0], bn.eps, bn.momentum, bn.training, act, residual,
         getattr(bn, "_fdt_arena", None), passthrough)
 
@@ -212,6 +215,15 @@ class ResNet(nn.Module):
                     if hasattr(m, "_fdt_arena_off"):
                         m._fdt_arena = (self._bn_arena, m._fdt_arena_off)
             self._bn_arena.begin(self._bn_total, x.device)     # also in eval: the FusedConvBN units always use batch statistics
+            bns = [m for m in self.modules() if isinstance(m, nn.BatchNorm2d)]
+            for m in bns:
+                m._fdt_nbt_batched = True
+            if self.training and bns:
+                torch._foreach_add_([m.num_batches_tracked for m in bns], 1)
+        else:
+            for m in self.modules():
+                if isinstance(m, nn.BatchNorm2d):
+                    m._fdt_nbt_batched = False
         # Stage boundaries for the parallel engines: forward "stage s" = the s-th entry of STAGES (its parameters may still
         # be arriving — all-gather overlapped with the previous stage's compute); gradient "bucket k" = the stage whose
         # gradients are final once backward crosses the boundary in front of it (reduce-scatter overlapped with the rest

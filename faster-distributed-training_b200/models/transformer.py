@@ -248,7 +248,6 @@ class Transformer(nn.Module):
         x = self.encode(tokens, token_types, key_mask)
         if not self.training:
             return self.classifier(x)
-        lam = mx.sample_beta(self.alpha, x.device, generator=generator)
-        perm = mx.randperm(x.size(0), x.device, generator)
+        lam, perm = mx.sample_mixup(self.alpha, x.size(0), x.device, generator)
         mixed = ops.head_mix(x, perm, lam, self.p_post, True)      # dropout(0.1) + lam*x + (1-lam)*x[perm], one kernel
         return self.classifier(mixed), perm, lam

@@ -117,6 +117,15 @@ def madgrad_(p, g, v, s, x0, lamb, ck, decay, eps, mirror):
 _seed_state = {}
 
 
+def reset_seed(device=None):
+    """Restart the framework's Philox stream (dropout masks, augmentation, mixup draws) from ``torch.initial_seed()`` with
+    counter 0 — call after ``torch.manual_seed`` to make two runs in one process draw the same sequence."""
+    if device is None:
+        _seed_state.clear()
+    else:
+        _seed_state.pop(torch.device(device), None)
+
+
 def _next_seed_off(device) -> torch.Tensor:
     """Device-resident (seed, counter) pair for Philox dropout masks; advances without a host sync
     (and inside CUDA-graph replays)."""
@@ -127,6 +136,16 @@ def _next_seed_off(device) -> torch.Tensor:
     cur = st.clone()
     st[1] += 1
     return cur
+
+
+def mixup_sample(alpha: Optional[float], B: Optional[int], device):
+    """(lam, perm): lam ~ Beta(alpha, alpha) as a 0-d fp32 tensor and a random permutation of 0..B-1 (int64), drawn on the
+    device by ONE tiny kernel from the framework's Philox stream; pass ``alpha=None`` / ``B=None`` to skip either."""
+    so = _next_seed_off(device)
+    lam = torch.empty((), dtype=torch.float32, device=device) if alpha is not None else None
+    perm = torch.empty(int(B), dtype=torch.int64, device=device) if B else None
+    call("fdt_mixup_sample", so, float(alpha if alpha is not None else 0.0), int(B or 0), lam, perm)
+    return lam, perm
 
 
 # ----------------------------------------------------------------------------- conv back ends
@@ -321,6 +340,7 @@ class _ConvBNAct(torch.autograd.Function):
             call("fdt_bn_act_fwd", y, res, out, bnctx, scratch, gamma, beta, cfg.get("running_mean"), cfg.get("running_var"),
                  i64(P), C, float(eps), float(cfg.get("momentum") or 0.0), form, act, launches=4 if form != 2 else 2)
         ctx.save_for_backward(x, weight, w16, y, out, bnctx)
+        ctx.gamma, ctx.beta = gamma, beta
         ctx.cfg = (stride, padding, act, form, residual is not None, gamma is not None)
         if cfg.get("passthrough"):
             return out, x.view_as(x)            # alias of the input: its consumer's gradient comes back through this node
@@ -346,9 +366,14 @@ class _ConvBNAct(torch.autograd.Function):
             g = gout
             call(red, gout, y, None, None, sums, i64(P), C, 0, launches=nl)
         dgamma = dbeta = None
+        ret_gamma = ret_beta = None
         if affine:
-            dgamma = torch.empty(C, dtype=torch.float32, device=dev)
-            dbeta = torch.empty(C, dtype=torch.float32, device=dev)
+            # written (not accumulated) by the kernel: straight into the parameters' slots of the flat gradient buffer when
+            # there are any (a BatchNorm's gamma / beta are used by exactly one unit), else into fresh tensors
+            dgamma, dbeta = _flat_grad_slot(ctx.gamma), _flat_grad_slot(ctx.beta)
+            if dgamma is None or dbeta is None:
+                dgamma = ret_gamma = torch.empty(C, dtype=torch.float32, device=dev)
+                dbeta = ret_beta = torch.empty(C, dtype=torch.float32, device=dev)
         dy = torch.empty_like(y)
         call("fdt_bn_bwd_apply", g, y, dy, sums, bnctx, dgamma, dbeta, i64(P), C, form)
         addend = None
@@ -356,7 +381,7 @@ class _ConvBNAct(torch.autograd.Function):
             addend = _nhwc(gpass)
         dx, dw = _conv_bwd(dy, x, w16, stride, padding, ctx.needs_input_grad[0], ctx.needs_input_grad[1], weight.shape, weight,
                            getattr(ctx, "im2col_A", None), addend)
-        return dx, dw, dgamma, dbeta, (g if has_res else None), None
+        return dx, dw, ret_gamma, ret_beta, (g if has_res else None), None
 
 
 def conv_bnstat_act(x, weight, stride, padding, eps, act, residual, arena=None, passthrough=False):
@@ -385,6 +410,7 @@ class _PoolFC(torch.autograd.Function):
         call("fdt_pool_fc_fwd", x, w, None if bias is None else bias.detach().float().contiguous(), pooled, logits,
              N, H * W, C, K)
         ctx.save_for_backward(w, pooled)
+        ctx.weight, ctx.bias = weight, bias
         ctx.geom = (N, C, H, W, K, bias is not None)
         return logits
 
@@ -395,10 +421,14 @@ class _PoolFC(torch.autograd.Function):
         g = g.float().contiguous()
         dx = torch.empty((N, C, H, W), dtype=BF16, device=g.device, memory_format=torch.channels_last) \
             if ctx.needs_input_grad[0] else None
-        dW = torch.zeros(K, C, dtype=torch.float32, device=g.device)
-        db = torch.zeros(K, dtype=torch.float32, device=g.device) if has_bias else None
+        # the kernel accumulates: straight into the flat gradient slots when the parameters have them
+        wslot, bslot = _flat_grad_slot(ctx.weight), (_flat_grad_slot(ctx.bias) if has_bias else None)
+        dW = wslot if wslot is not None else torch.zeros(K, C, dtype=torch.float32, device=g.device)
+        db = None
+        if has_bias:
+            db = bslot if bslot is not None else torch.zeros(K, dtype=torch.float32, device=g.device)
         call("fdt_pool_fc_bwd", g, w, pooled, dx, dW, db, N, H * W, C, K)
-        return dx, dW, db
+        return dx, (None if wslot is not None else dW), (None if (bslot is not None or not has_bias) else db)
 
 
 def pool_fc(x, weight, bias):

@@ -204,6 +204,9 @@ int fdt_input_aug_mixup_ex(const void* x_u8, const int64_t* perm, const float* l
 int fdt_input_aug_mixup_bwd(const void* x_u8, const int64_t* perm, const float* lamsrc, int lam_mode, const int64_t* seed_off,
                             const void* g_bf16, float* dlam, int B, int H, int W, int pad, int train, const float* mean3,
                             const float* std3, cudaStream_t st);
+/* lam [1] ~ Beta(alpha, alpha) and perm [B] = uniform random permutation in one launch (either may be NULL);
+ * ref: mixup_data's host-side Beta + torch.randperm (resnet50_test.py:355-362) */
+int fdt_mixup_sample(const int64_t* seed_off, float alpha, int B, float* lam, int64_t* perm, cudaStream_t st);
 int fdt_pool_fc_fwd(const void* x, const float* W, const float* bias, float* pooled, float* logits, int N, int HW,
                     int C, int K, cudaStream_t st);
 int fdt_pool_fc_bwd(const float* dlogits, const float* W, const float* pooled, void* dx, float* dW, float* db,

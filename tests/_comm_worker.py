@@ -204,6 +204,8 @@ def main():
 
     def run(engine_cls, use_symm, steps=4, **kw):
         torch.manual_seed(0)
+        from fdt.ops import cuda_ops
+        cuda_ops.reset_seed()               # same Philox stream (augmentation, mixup draws) in every run
         comm = Communicator()
         alloc = None
         if use_symm:

@@ -559,3 +559,25 @@ def test_batch_stat_normalisation_form_is_the_references():
     rel = lambda a, b: ((a.float() - b).norm() / b.norm()).item()
     assert rel(out, want) < 6e-3, rel(out, want)
     assert rel(out, want) < 0.5 * rel(out, biased) and rel(out, want) < 0.1 * rel(out, inside)
+
+
+def test_mixup_sample_kernel_draws():
+    """Device-side Beta(alpha, alpha) + random permutation (one launch): permutations are valid and differ between calls,
+    lambda has the Beta(0.99, 0.99) mean / variance (1/2, 1/(4(2a+1)) = 0.0839), alpha <= 0 passes through."""
+    from fdt.ops import cuda_ops as cu
+    dev = torch.device("cuda")
+    lams, perms = [], []
+    for _ in range(400):
+        lam, perm = cu.mixup_sample(0.99, 128, dev)
+        lams.append(lam)
+        perms.append(perm)
+    P = torch.stack(perms)
+    assert torch.equal(P.sort(dim=1).values, torch.arange(128, device=dev).expand(400, 128))
+    assert len({tuple(p.tolist()) for p in perms[:50]}) == 50
+    pos0 = (P == 0).float().argmax(1).float()             # where element 0 lands: uniform on 0..127
+    assert abs(pos0.mean().item() - 63.5) < 8.0
+    L = torch.stack(lams)
+    assert (L > 0).all() and (L < 1).all()
+    assert abs(L.mean().item() - 0.5) < 0.06 and abs(L.var().item() - 0.0839) < 0.025
+    lam0, _ = cu.mixup_sample(0.0, 4, dev)
+    assert float(lam0) == 0.0
