@@ -90,7 +90,8 @@ __global__ void madgrad_kernel(float* __restrict__ p, const float* __restrict__ 
 // from device memory, so a captured CUDA graph follows LR and momentum schedules without re-capture.
 // hyper = {lr, momentum, dampening}
 __global__ void sgd_momentum_dev_kernel(float* __restrict__ p, const float* __restrict__ d, float* __restrict__ buf,
-                                        int64_t n, const float* __restrict__ hyper, int nesterov, int first) {
+                                        int64_t n, const float* __restrict__ hyper, int nesterov, int first,
+                                        __nv_bfloat16* __restrict__ shadow) {
     const float lr = hyper[0], momentum = hyper[1], dampening = hyper[2];
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
     for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
@@ -110,6 +111,10 @@ __global__ void sgd_momentum_dev_kernel(float* __restrict__ p, const float* __re
             }
             pv.x -= lr * st.x; pv.y -= lr * st.y; pv.z -= lr * st.z; pv.w -= lr * st.w;
             *reinterpret_cast<float4*>(p + i) = pv;
+            if (shadow) {          // the bf16 operand copy of the updated parameters, in the same pass
+                *reinterpret_cast<__nv_bfloat162*>(shadow + i) = __floats2bfloat162_rn(pv.x, pv.y);
+                *reinterpret_cast<__nv_bfloat162*>(shadow + i + 2) = __floats2bfloat162_rn(pv.z, pv.w);
+            }
         } else {
             for (int64_t j = i; j < n; ++j) {
                 const float dj = d[j];
@@ -120,6 +125,7 @@ __global__ void sgd_momentum_dev_kernel(float* __restrict__ p, const float* __re
                     st = nesterov ? dj + momentum * b : b;
                 }
                 p[j] -= lr * st;
+                if (shadow) shadow[j] = __float2bfloat16(p[j]);
             }
         }
     }
@@ -220,9 +226,9 @@ FDT_API int fdt_madgrad(float* p, const float* g, float* v, float* s, float* x0,
 }
 
 FDT_API int fdt_sgd_momentum_dev(float* p, const float* d, float* buf, int64_t n, const float* hyper, int nesterov, int first,
-                                 cudaStream_t st) {
+                                 void* shadow_bf16, cudaStream_t st) {
     if (!hyper) return -1;
-    sgd_momentum_dev_kernel<<<grid_for(n, 4), 256, 0, st>>>(p, d, buf, n, hyper, nesterov, first);
+    sgd_momentum_dev_kernel<<<grid_for(n, 4), 256, 0, st>>>(p, d, buf, n, hyper, nesterov, first, (__nv_bfloat16*)shadow_bf16);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -22,14 +22,13 @@ static_assert(sizeof(WPrepDesc) == 32, "descriptor layout is mirrored in python"
 
 constexpr int kTile = 64;
 
-__global__ void __launch_bounds__(256)
-dgrad_weights_kernel(const WPrepDesc* __restrict__ descs) {
-    const WPrepDesc d = descs[blockIdx.y];
+// tiles first, first + step, ... of weight d (a tile = 64 x 64 elements of one tap, transposed through shared memory)
+__device__ __forceinline__ void dgrad_weights_body(const WPrepDesc& d, int first, int step) {
     __shared__ bf16 tile[kTile][kTile + 2];
     const int to = (d.O + kTile - 1) / kTile, ti = (d.I + kTile - 1) / kTile;
     const int total = d.T * to * ti;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;     // 32 x 8
-    for (int id = blockIdx.x; id < total; id += gridDim.x) {
+    for (int id = first; id < total; id += step) {
         const int t = id / (to * ti), rem = id - t * to * ti;
         const int o0 = (rem / ti) * kTile, i0 = (rem % ti) * kTile;
         // load: rows = o, 2 consecutive i per thread
@@ -65,12 +64,38 @@ dgrad_weights_kernel(const WPrepDesc* __restrict__ descs) {
     }
 }
 
+__global__ void __launch_bounds__(256)
+dgrad_weights_kernel(const WPrepDesc* __restrict__ descs) {
+    dgrad_weights_body(descs[blockIdx.y], blockIdx.x, gridDim.x);
+}
+
+// Balanced form: one tile per block over the concatenated tile lists of all weights (a fixed number of blocks per weight
+// leaves the 512x512x3x3 filters with 12 tiles per block and the 64x64 ones with idle blocks).
+__global__ void __launch_bounds__(256)
+dgrad_weights_flat_kernel(const WPrepDesc* __restrict__ descs, int count) {
+    int id = blockIdx.x;
+    for (int k = 0; k < count; ++k) {
+        const WPrepDesc d = descs[k];
+        const int n = d.T * ((d.O + kTile - 1) / kTile) * ((d.I + kTile - 1) / kTile);
+        if (id < n) { dgrad_weights_body(d, id, 1 << 30); return; }
+        id -= n;
+    }
+}
+
 }  // namespace
 
 // descs: `count` 32-byte descriptors {src, dst, O, T, I, mode} in device memory.
 FDT_API int fdt_dgrad_weights(const void* descs, int count, cudaStream_t st) {
     if (count <= 0) return 0;
     dgrad_weights_kernel<<<dim3(48, count), 256, 0, st>>>((const WPrepDesc*)descs);
+    FDT_CHECK_LAUNCH();
+    return 0;
+}
+
+// total_tiles = Σ over descriptors of T * ceil(O/64) * ceil(I/64) (computed by the caller, who built the table).
+FDT_API int fdt_dgrad_weights_flat(const void* descs, int count, int total_tiles, cudaStream_t st) {
+    if (count <= 0 || total_tiles <= 0) return 0;
+    dgrad_weights_flat_kernel<<<total_tiles, 256, 0, st>>>((const WPrepDesc*)descs, count);
     FDT_CHECK_LAUNCH();
     return 0;
 }

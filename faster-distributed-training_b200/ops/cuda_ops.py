@@ -96,9 +96,10 @@ def sgd_momentum_(p, d, buf, lr, momentum, dampening, nesterov, first):
          int(bool(nesterov)), int(bool(first)))
 
 
-def sgd_momentum_dev_(p, d, buf, hyper, nesterov, first):
-    """hyper: device fp32 {lr, momentum, dampening} (graph-replay safe)."""
-    call("fdt_sgd_momentum_dev", p, d, buf, i64(p.numel()), hyper, int(bool(nesterov)), int(bool(first)))
+def sgd_momentum_dev_(p, d, buf, hyper, nesterov, first, shadow=None):
+    """hyper: device fp32 {lr, momentum, dampening} (graph-replay safe); ``shadow``: optional bf16 buffer that receives the
+    updated parameters in the same pass."""
+    call("fdt_sgd_momentum_dev", p, d, buf, i64(p.numel()), hyper, int(bool(nesterov)), int(bool(first)), shadow)
 
 
 def clip_wd_(g, p, sq, max_norm, wd, skipped):

@@ -785,7 +785,14 @@ class NGD(Optimizer):
             from .. import ops
             if ops.use_native(pflat):
                 # lr, momentum and dampening are read from device memory: graph replays follow their schedules
-                ops._cu().sgd_momentum_dev_(pflat, gflat, buf, self._hyper(gi, group, pflat.device), nesterov, first)
+                shadow = None
+                span = self._lr_tensors.get(("span", gi))
+                if span is not None and not span[0].sharded and span[0].shadow_flat is not None and len(self.param_groups) == 1:
+                    # unsharded buffers: the bf16 operand shadow of the updated parameters comes out of this same pass
+                    flat, lo, hi = span
+                    shadow = flat.shadow_flat[lo:hi]
+                    flat.shadow_fresh = True
+                ops._cu().sgd_momentum_dev_(pflat, gflat, buf, self._hyper(gi, group, pflat.device), nesterov, first, shadow)
                 return
         lr = self._lr(gi, group, pflat.device)
         d_p = gflat

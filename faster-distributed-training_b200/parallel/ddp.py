@@ -293,6 +293,7 @@ class DataParallelEngine(nn.Module):
 
     def load_state_dict(self, *a, **kw):
         self._stale = True
+        self.flat.shadow_fresh = False          # parameters change behind the optimizer's back: re-cast the whole shadow
         return super().load_state_dict(*a, **kw)
 
     def zero_grad(self):

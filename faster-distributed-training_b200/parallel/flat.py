@@ -204,8 +204,11 @@ class FlatParameters:
             return
         if self.shadow_flat is None:
             self.shadow_flat = torch.empty(self.total, dtype=torch.bfloat16, device=self.device)
-        from ..ops import cuda_ops
-        cuda_ops.cast_bf16_(self.param_flat, self.shadow_flat)
+        if getattr(self, "shadow_fresh", False):
+            self.shadow_fresh = False          # the optimizer's update kernel already wrote the shadow of what it changed
+        else:
+            from ..ops import cuda_ops
+            cuda_ops.cast_bf16_(self.param_flat, self.shadow_flat)
         self.refresh_dgrad_shadow()
 
     # -- data-gradient operand layouts (transposed / tap-rotated weights), one launch per step
@@ -254,7 +257,8 @@ class FlatParameters:
         blob = b"".join(rows)
         dev = torch.empty(len(blob), dtype=torch.uint8, device=self.device)
         dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
-        self._dgrad_table = (dev, len(rows))
+        tiles = sum(T * ((O + 63) // 64) * ((I + 63) // 64) for _, O, T, I, _, _ in ents)
+        self._dgrad_table = (dev, len(rows), tiles)
 
     def refresh_dgrad_shadow(self):
         if self.device.type != "cuda" or self.shadow_flat is None:
@@ -263,7 +267,7 @@ class FlatParameters:
             self._build_dgrad_table()
         if self._dgrad_table is not None:
             from ..ops._lib import call
-            call("fdt_dgrad_weights", self._dgrad_table[0], self._dgrad_table[1])
+            call("fdt_dgrad_weights_flat", self._dgrad_table[0], self._dgrad_table[1], self._dgrad_table[2])
 
     def dgrad_shadow_of(self, p: torch.nn.Parameter, mode: int) -> Optional[torch.Tensor]:
         ent = getattr(self, "_dgrad_views", {}).get(p._fdt_flat[1])

@@ -130,6 +130,7 @@ int fdt_cast_bf16(const float* x, void* y_bf16, int64_t n, cudaStream_t st);
  *   add of ngd_optimizer.py:478-479 in one pass; a non-finite norm zeroes the step and bumps *skipped).
  * fdt_madgrad_dev: hyper = {lr + eps, k, momentum}; lamb = hyper[0]*sqrt(hyper[1]+1); tick != 0 advances k afterwards. */
 int fdt_sgd_momentum_dev(float* p, const float* d, float* buf, int64_t n, const float* hyper, int nesterov, int first,
+                         void* shadow_bf16 /* optional: bf16 copy of the updated parameters, written in the same pass */,
                          cudaStream_t st);
 int fdt_clip_wd(float* g, const float* p, int64_t n, const float* sq, float max_norm, float wd, float* skipped,
                 cudaStream_t st);
@@ -173,6 +174,8 @@ int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int
 /* per-step operand layouts of the data-gradient GEMMs (transposed / tap-rotated bf16 weights) for every layer in one launch.
  * descs: `count` 32-byte device records {const bf16* src; bf16* dst; int O, T, I, mode}.  csrc/weight_prep.cu */
 int fdt_dgrad_weights(const void* descs, int count, cudaStream_t st);
+/* same, one 64x64 tile per block over all weights (total_tiles = sum of T*ceil(O/64)*ceil(I/64)): balanced */
+int fdt_dgrad_weights_flat(const void* descs, int count, int total_tiles, cudaStream_t st);
 /* explicit im2col / col2im (strided convs, the 3-channel stem): A[N*Ho*Wo, Kp] <-> x[N,H,W,C] */
 int fdt_im2col(const void* x, void* A, int N, int H, int W, int C, int k, int stride, int pad, int Ho, int Wo, int Kp,
                cudaStream_t st);

@@ -144,7 +144,7 @@ elif what == "optim":
         sq.zero_()
         call("fdt_sqnorm", g_, i64(n), sq)
         call("fdt_clip_wd", g_, p_, i64(n), sq, 10.0, 1e-4, skipped)
-        call("fdt_sgd_momentum_dev", p_, g_, buf, i64(n), hyper, 0, 0)
+        call("fdt_sgd_momentum_dev", p_, g_, buf, i64(n), hyper, 0, 0, sh)
         call("fdt_madgrad_dev", p_, g_, v_, s_, x0, i64(n), hy2, 0.0, 1e-6, 0, 1)
         call("fdt_cast_bf16", p_, sh, i64(n))
 elif what == "input_head":
