@@ -158,7 +158,7 @@ def _heap(device, world, rank):
     return _HEAP["heap"]
 
 
-def build_fdt(model_name, bs, device, world, use_graph, mode):
+def build_fdt(model_name, bs, device, world, use_graph, mode, meta=False):
     from fdt.cli import ResNetStep, TransformerStep
     from fdt.engine.trainer import Trainer
     from fdt.models.resnet import resnet50
@@ -176,7 +176,11 @@ def build_fdt(model_name, bs, device, world, use_graph, mode):
     torch.manual_seed(123456)
     if model_name == "resnet50":
         model = resnet50(10).to(device)
-        step_obj = ResNetStep(0.99, None)
+        mm = None
+        if meta:        # --meta_learning: learnable per-sample mixing weights (resnet50_test.py:388-401, 525), fused kernels
+            from fdt.data.mixup import MetaMixup
+            mm = MetaMixup(bs, compat=False, device=device)
+        step_obj = ResNetStep(0.99, mm)
         lr, wd = 0.01 * world, 1e-4
     else:
         model = Transformer(4, 30522, alpha=0.99).to(device)
@@ -184,7 +188,10 @@ def build_fdt(model_name, bs, device, world, use_graph, mode):
         lr, wd = 1e-4 * world, 0.0
     Engine = FullyShardedEngine if (mode == "fsdp" and world > 1) else DataParallelEngine
     engine = Engine(model, comm, allocator=allocator)
-    opt = NGD(engine.optimizer_params(), lr=lr, momentum=0.9, weight_decay=wd)
+    params = list(engine.optimizer_params())
+    if model_name == "resnet50" and meta:
+        params.append(step_obj.meta.lam)
+    opt = NGD(params, lr=lr, momentum=0.9, weight_decay=wd)
     trainer = Trainer(engine, opt, step_obj, clip_norm=10.0, use_cuda_graph=use_graph)
     return trainer, comm
 
@@ -200,11 +207,11 @@ def make_host_batches(model_name, bs, n, seq_len, seed):
     return TensorBatchLoader(ds.tensors(), bs, shuffle=True, drop_last=True, pin=True, ring=max(n, 4), seed=seed)
 
 
-def measure_fdt(args, rank, local, world, model, mode, bs, steps, sample_clocks):
+def measure_fdt(args, rank, local, world, model, mode, bs, steps, sample_clocks, meta=False):
     """Device-timed steps + the end-to-end loop for one (model, parallel mode).  Returns a dict."""
     from fdt import ops
     device = torch.device("cuda", local)
-    trainer, comm = build_fdt(model, bs, device, world, args.cuda_graph, mode)
+    trainer, comm = build_fdt(model, bs, device, world, args.cuda_graph, mode, meta)
     loader = make_host_batches(model, bs, 8, args.seq_len, seed=rank)
     host_batches = [tuple(b) for b in iter(loader)]
     dev_batches = [tuple(t.to(device) for t in b) for b in host_batches]
@@ -269,13 +276,17 @@ def fdt_extras(args, rank, local, world):
     """The other series BASELINE.json names (transformer samples/s; FSDP), measured in the same process right after
     the headline so they land in the driver's record: same timing rules, fewer steps."""
     steps = max(3, min(args.steps, 10))
-    plan = [("transformer_ddp", "transformer", "ddp", 64)]
+    plan = [("transformer_ddp", "transformer", "ddp", 64, False)]
     if world > 1:
-        plan += [("transformer_fsdp", "transformer", "fsdp", 64), ("resnet50_fsdp", "resnet50", "fsdp", 128)]
+        plan += [("transformer_fsdp", "transformer", "fsdp", 64, False), ("resnet50_fsdp", "resnet50", "fsdp", 128, False),
+                 # BASELINE.json config 4: ResNet-50 FSDP FULL_SHARD, NGD + meta-mixup, 256 img/GPU
+                 ("resnet50_fsdp_meta_bs256", "resnet50", "fsdp", 256, True)]
+    else:
+        plan += [("resnet50_meta_mixup", "resnet50", "ddp", 128, True)]
     out = {}
-    for key, model, mode, bs in plan:
+    for key, model, mode, bs, meta in plan:
         try:
-            m = measure_fdt(args, rank, local, world, model, mode, bs, steps, False)
+            m = measure_fdt(args, rank, local, world, model, mode, bs, steps, False, meta)
             out[key] = _series(m, bs, world, "img/s" if model == "resnet50" else "samples/s")
             out[key]["parallelism"] = f"{mode}{world}"
         except Exception as e:                      # an auxiliary series must never take the headline down
