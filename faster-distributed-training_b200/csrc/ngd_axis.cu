@@ -171,7 +171,7 @@ FDT_API int fdt_ngd_small_kl(const float* J, const float* W, float* K, float* L,
 // One CTA per factor keeps X, W and H in shared memory and does the complete step of ngd_optimizer.py:138-218 for it:
 //   H = X Wᵀ, X̂ = X − H W, p0 = ΣX², p1 = ΣX̂², out = X̂·sqrt(p0 / (p1 + 1e-30)) (X if p1 is NaN), and optionally J = Hᵀ X.
 namespace {
-constexpr int kSmallMaxElems = 8192;      // each of N*D, R*D, N*R (floats): 3 x 32 KB of shared memory
+constexpr int kSmallMaxElems = 24576;     // N*D + R*D + N*R floats in total: 96 KB of shared memory
 
 __global__ void __launch_bounds__(256)
 ngd_small_matrix_kernel(const float* __restrict__ X, const float* __restrict__ W, int ldw, float* __restrict__ out,
@@ -243,15 +243,15 @@ ngd_small_matrix_kernel(const float* __restrict__ X, const float* __restrict__ W
 }  // namespace
 
 // X [n, N, D] (x_trans == 0) or [n, D, N] (x_trans != 0); W [n, R, ldw] (ldw >= D: padded pitch); out: same layout as X
-// (may NOT alias X); p0 [n] = ΣX² per factor; J [n, R, ldj] or NULL.  N*D, R*D, N*R <= 8192 each.
+// (may NOT alias X); p0 [n] = ΣX² per factor; J [n, R, ldj] or NULL.  N*D + R*D + N*R <= 24576.
 FDT_API int fdt_ngd_small_matrix(const float* X, const float* W, int ldw, float* out, float* p0, float* J, int ldj, int n,
                                  int N, int D, int R, int x_trans, cudaStream_t st) {
     if (n <= 0 || N < 1 || D < 1 || R < 1 || ldw < D || (J && ldj < D)) return -1;
-    if ((int64_t)N * D > kSmallMaxElems || (int64_t)R * D > kSmallMaxElems || (int64_t)N * R > kSmallMaxElems) return -1;
+    if ((int64_t)N * D + (int64_t)R * D + (int64_t)N * R > kSmallMaxElems) return -1;
     const size_t smem = sizeof(float) * ((size_t)N * D + (size_t)R * D + (size_t)N * R);
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(ngd_small_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * kSmallMaxElems * 4);
+        cudaError_t e = cudaFuncSetAttribute(ngd_small_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallMaxElems * 4);
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }

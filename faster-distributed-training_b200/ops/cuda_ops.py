@@ -868,7 +868,7 @@ def ngd_small_axis(X: torch.Tensor, W: torch.Tensor, A: int, D: int, B: int, J: 
 
 
 def ngd_small_matrix_ok(N: int, D: int, R: int) -> bool:
-    return N * D <= 8192 and R * D <= 8192 and N * R <= 8192
+    return N * D + R * D + N * R <= 24576
 
 
 def ngd_small_matrix(X: torch.Tensor, fb, left: bool, want_j: bool):

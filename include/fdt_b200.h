@@ -244,7 +244,7 @@ int fdt_ngd_stats_kl(const float* J, const float* W, float* K, float* L, int n, 
 int fdt_ngd_small_axis(const float* X, const float* W, float* Xhat, float* sums, float* J, int n, int64_t A, int D,
                        int64_t B, int R, cudaStream_t st);
 
-/* complete preconditioning step of SMALL factors (N*D, R*D, N*R <= 8192 each) held in shared memory, one CTA per factor:
+/* complete preconditioning step of SMALL factors (N*D + R*D + N*R <= 24576 floats) held in shared memory, one CTA per factor:
  * out = rescaled (X - X W^T W) in the layout of X, p0 [n] = sum X^2, J [n,R,ldj] = H^T X or NULL; W, J with row pitch ldw / ldj.
  * For gradient views whose rows are not 16-byte aligned (3-channel stem, [B,1,1,1] theta) — no cuBLAS for them either. */
 int fdt_ngd_small_matrix(const float* X, const float* W, int ldw, float* out, float* p0, float* J, int ldj, int n,
