@@ -109,6 +109,9 @@ class Trainer:
 
     def _eager_step(self, batch) -> Tuple[torch.Tensor, Any]:
         eng = self.engine
+        if self.device.type == "cuda":
+            from ..ops import cuda_ops
+            cuda_ops.begin_step_seeds(self.device)           # one add: fresh Philox counters for every random kernel of the step
         with _nvtx("fdt/gather+zero"):
             eng.zero_grad()
             eng.pre_forward()

@@ -116,6 +116,36 @@ def madgrad_(p, g, v, s, x0, lamb, ck, decay, eps, mirror):
 
 
 _seed_state = {}
+_SEED_ROWS = 1024
+
+
+class _SeedTable:
+    """Device-resident (seed, counter) pairs for the Philox streams of one device: a table of ``_SEED_ROWS`` rows with
+    consecutive counters.  Every random kernel of a step takes the next row (a view — no clone, no launch); the Trainer
+    advances the whole table by its length with ONE in-place add at the start of each step (also inside CUDA-graph
+    replays), so no host synchronisation and no per-call bookkeeping kernels.  A backward pass regenerates its masks from
+    the row its forward used; rows only change at step boundaries.  Without a Trainer the table is replaced (not mutated)
+    when it runs out, so rows still held by pending backward passes stay valid."""
+
+    def __init__(self, device):
+        seed = torch.initial_seed() & 0x7FFFFFFFFFFF
+        self.tab = torch.stack([torch.full((_SEED_ROWS,), seed, dtype=torch.int64), torch.arange(_SEED_ROWS, dtype=torch.int64)],
+                               dim=1).to(device)
+        self.idx = 0
+
+    def next(self) -> torch.Tensor:
+        if self.idx >= _SEED_ROWS:
+            nxt = self.tab.clone()
+            nxt[:, 1] += _SEED_ROWS
+            self.tab, self.idx = nxt, 0
+        row = self.tab[self.idx]
+        self.idx += 1
+        return row
+
+    def begin_step(self):
+        if self.idx:
+            self.tab[:, 1] += _SEED_ROWS
+            self.idx = 0
 
 
 def reset_seed(device=None):
@@ -127,16 +157,21 @@ def reset_seed(device=None):
         _seed_state.pop(torch.device(device), None)
 
 
+def begin_step_seeds(device):
+    """Advance the device's seed table (one launch) and hand out rows from its start again; called by the Trainer at the
+    start of every step."""
+    st = _seed_state.get(torch.device(device))
+    if st is not None:
+        st.begin_step()
+
+
 def _next_seed_off(device) -> torch.Tensor:
-    """Device-resident (seed, counter) pair for Philox dropout masks; advances without a host sync
-    (and inside CUDA-graph replays)."""
+    """Device-resident (seed, counter) pair for a Philox-driven kernel: the next row of the device's seed table."""
+    device = torch.device(device)
     st = _seed_state.get(device)
     if st is None:
-        st = torch.tensor([torch.initial_seed() & 0x7FFFFFFFFFFF, 0], dtype=torch.int64, device=device)
-        _seed_state[device] = st
-    cur = st.clone()
-    st[1] += 1
-    return cur
+        st = _seed_state[device] = _SeedTable(device)
+    return st.next()
 
 
 def mixup_sample(alpha: Optional[float], B: Optional[int], device):
