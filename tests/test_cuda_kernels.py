@@ -254,11 +254,12 @@ def test_input_aug_mixup_kernel():
     frac_pad = ((aug - pad_val).abs() < 2e-2).float().mean().item()
     assert 0.0 < frac_pad < 0.4
     # blend linearity: lam=0.3 equals 0.3*T(x) + 0.7*T(x[perm]) when the same augmentation draw is used
-    st = cu._seed_state[imgs.device].clone()
+    tab = cu._seed_state[imgs.device]               # rewind the seed table so the three calls take the same row
+    at = tab.idx
     a = cu.input_aug_mixup(imgs, True, perm, one, cifar.MEAN, cifar.STD).float()
-    cu._seed_state[imgs.device].copy_(st)
+    tab.idx = at
     b = cu.input_aug_mixup(imgs, True, perm, torch.zeros((), device=DEV), cifar.MEAN, cifar.STD).float()
-    cu._seed_state[imgs.device].copy_(st)
+    tab.idx = at
     c = cu.input_aug_mixup(imgs, True, perm, torch.full((), 0.3, device=DEV), cifar.MEAN, cifar.STD).float()
     _close(c, 0.3 * a + 0.7 * b, 2e-2, 3e-2, "blend")
 
