@@ -86,7 +86,9 @@ class MultiheadAttention(nn.Module):
         for l in list(self.heads) + [self.output]:
             l.weight._fdt_group_unit = 4
 
-    def forward(self, x, key_mask=None):
+    def forward(self, x, key_mask=None, residual=None, p_res=0.0):
+        """``residual`` given: returns ``residual + dropout(output_linear(attention), p_res)`` (the sub-layer's closing
+        ops fused with the output projection); otherwise the projection alone."""
         B, L, _ = x.shape
         o = ops.qkv_attention(x, [l.weight for l in self.heads], [l.bias for l in self.heads], self.h, key_mask,
                               self.p, self.training, self.mask_compat)
@@ -95,6 +97,8 @@ class MultiheadAttention(nn.Module):
                        for l in self.heads]
             o = ops.attention(q, k, v, key_mask, self.p, self.training, self.mask_compat)
             o = o.transpose(1, 2).reshape(B, L, self.h * self.d_k)
+        if residual is not None:
+            return ops.linear_dropout_add(o, self.output.weight, self.output.bias, residual, p_res, self.training)
         return ops.linear(o, self.output.weight, self.output.bias)
 
 
@@ -105,8 +109,10 @@ class PositionalWiseFFN(nn.Module):
         self.w_2 = nn.Linear(d_ff, d_model)
         self.p = dropout
 
-    def forward(self, x):
+    def forward(self, x, residual=None, p_res=0.0):
         h = ops.linear(x, self.w_1.weight, self.w_1.bias, act="gelu", dropout_p=self.p, training=self.training)
+        if residual is not None:
+            return ops.linear_dropout_add(h, self.w_2.weight, self.w_2.bias, residual, p_res, self.training)
         return ops.linear(h, self.w_2.weight, self.w_2.bias)
 
 
@@ -119,7 +125,7 @@ class sublayerConnectionAttention(nn.Module):
 
     def forward(self, x, key_mask=None):
         y, xp = self.layernorm(x, passthrough=True)     # the residual consumes the alias: gradients meet inside the LN backward
-        return ops.dropout_add(self.multiheads(y, key_mask), xp, self.p, self.training)
+        return self.multiheads(y, key_mask, residual=xp, p_res=self.p)
 
 
 class sublayerConnectionFFN(nn.Module):
@@ -131,7 +137,7 @@ class sublayerConnectionFFN(nn.Module):
 
     def forward(self, x):
         y, xp = self.layernorm(x, passthrough=True)
-        return ops.dropout_add(self.ffn(y), xp, self.p, self.training)
+        return self.ffn(y, residual=xp, p_res=self.p)
 
 
 class Pooler(nn.Module):

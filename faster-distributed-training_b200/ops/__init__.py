@@ -127,6 +127,16 @@ def mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat=False):
     return ref.mlp_head(x, W1, b1, W2, b2, bias_grad_mean_compat)
 
 
+def linear_dropout_add(x, weight, bias, residual, p, training):
+    """``residual + dropout(x Wᵀ + b, p)`` — the closing Linear of a sub-layer with its dropout and residual add."""
+    p = float(p) if training else 0.0
+    if use_native(x):
+        out = _cu().linear_dropout_add(x, weight, bias, residual, p)
+        if out is not None:
+            return out
+    return dropout_add(linear(x, weight, bias), residual, p, True)
+
+
 def cls_gather(x):
     """First-token rows of the [B, L, D] residual stream (the pooler's input, transformer.py:99-101)."""
     if use_native(x):

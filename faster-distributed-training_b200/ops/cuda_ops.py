@@ -664,6 +664,14 @@ def linear(x, weight, bias, act, drop_p=0.0):
     return F.dropout(out, drop_p, True) if drop_p > 0 else out
 
 
+def linear_dropout_add(x, weight, bias, residual, p):
+    """residual + dropout(linear(x)); None when the fused path does not apply."""
+    if not _native_gemm():
+        return None
+    from . import linear_sm100
+    return linear_sm100.linear_dropout_add(x, weight, bias, residual, p)
+
+
 def attention(q, k, v, key_mask, dropout_p, training, mask_compat):
     if _native_gemm():
         from . import gemm_sm100

@@ -173,6 +173,78 @@ def linear_fused(x, weights, biases) -> Optional[torch.Tensor]:
     return _LinearFused.apply(x, flat, w_off, b_off, len(weights), *weights, *[b for b in biases if b is not None])
 
 
+class _LinearDropoutAdd(torch.autograd.Function):
+    """out (fp32) = residual + dropout(x Wᵀ + b, p): the closing Linear of a pre-LN sub-layer together with its dropout and
+    residual add (transformer.py:254-259, 271-275).  Forward: GEMM with bias epilogue + one dropout-add pass.  Backward: ONE
+    pass turns the fp32 residual-stream gradient into the masked bf16 GEMM operand AND the bias gradient (the separate
+    dropout-backward and bias-reduction passes are gone), then the data- and weight-gradient GEMMs; the residual-stream
+    gradient itself is handed on untouched."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, p):
+        from .cuda_ops import _next_seed_off
+        from ._lib import call, i64
+        shp = x.shape
+        x16 = x.to(BF16).reshape(-1, shp[-1]).contiguous()
+        w16 = _w16(weight).contiguous()
+        b32 = None if bias is None else bias.detach().float().reshape(-1).contiguous()
+        z = g.gemm_nt(x16, w16, b32, "none")
+        res = residual.float().contiguous()
+        out = torch.empty_like(res)
+        so = _next_seed_off(z.device) if p > 0 else None
+        call("fdt_dropout_add", z, 1, res, out, i64(z.numel()), float(p), so)
+        ctx.save_for_backward(x16, w16, weight, bias, so)
+        ctx.p, ctx.shp, ctx.xdtype = float(p), shp, x.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        from .cuda_ops import _flat_grad_slot, _wdgrad
+        from ._lib import call, i64
+        from . import wgrad_sm100
+        x16, w16, weight, bias, so = ctx.saved_tensors
+        N, K = w16.shape
+        g32 = gout.float().contiguous()
+        g2 = g32.view(-1, N)
+        T = g2.shape[0]
+        need_db = bias is not None and ctx.needs_input_grad[2]
+        db_slot = _flat_grad_slot(bias) if need_db else None
+        db = None
+        if need_db and db_slot is None:
+            db = torch.zeros(N, dtype=torch.float32, device=g2.device)
+        gz = torch.empty(T, N, dtype=BF16, device=g2.device)
+        dbp = (db_slot if db_slot is not None else db) if need_db else None
+        if ctx.p > 0:
+            call("fdt_linear_bwd_prep_dropout", g2, 1, None, gz, dbp, i64(T), N, 0, ctx.p, so)
+        else:
+            call("fdt_linear_bwd_prep", g2, 1, None, gz, dbp, i64(T), N, 0)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            wt = _wdgrad(weight, 0)
+            if wt is not None and tuple(wt.shape) != (K, N):
+                wt = None
+            dx = g.gemm_nt(gz, wt if wt is not None else w16.t().contiguous(), None, "none").view(ctx.shp).to(ctx.xdtype)
+        if ctx.needs_input_grad[1]:
+            slot = _flat_grad_slot(weight)
+            dw = wgrad_sm100.linear_wgrad(gz, x16, slot) if slot is not None else wgrad_sm100.linear_wgrad(gz, x16)
+            if dw is True:
+                dw = None
+            elif dw is None:
+                from ._lib import note_fallback
+                note_fallback("linear_bwd", "cuBLAS weight-gradient GEMM")
+                dw = (gz.t() @ x16).float()
+        if db is not None:
+            db = db.view(bias.shape)
+        return dx, dw, db, (g32 if ctx.needs_input_grad[3] else None), None
+
+
+def linear_dropout_add(x, weight, bias, residual, p) -> Optional[torch.Tensor]:
+    K, N = x.shape[-1], weight.shape[0]
+    if K % 64 or N % 64 or not g.available() or tuple(residual.shape[:-1]) != tuple(x.shape[:-1]) or residual.shape[-1] != N:
+        return None
+    return _LinearDropoutAdd.apply(x, weight, bias, residual, float(p))
+
+
 def linear(x, weight, bias, act, drop_p: float = 0.0) -> Optional[torch.Tensor]:
     K = x.shape[-1]
     N = weight.shape[0]

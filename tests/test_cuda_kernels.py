@@ -582,3 +582,36 @@ def test_mixup_sample_kernel_draws():
     assert abs(L.mean().item() - 0.5) < 0.06 and abs(L.var().item() - 0.0839) < 0.025
     lam0, _ = cu.mixup_sample(0.0, 4, dev)
     assert float(lam0) == 0.0
+
+
+def test_linear_dropout_add_sublayer_tail():
+    """residual + dropout(x Wᵀ + b): forward and all four gradients vs fp32 (p = 0), and with p > 0 the backward mask equals
+    the forward mask (d out / d bias is the column count of kept elements / (1 - p))."""
+    from fdt import ops
+    torch.manual_seed(6)
+    T, K, N = 512, 1024, 512
+    x = (torch.randn(4, T // 4, K, device=DEV) / math.sqrt(K)).bfloat16().requires_grad_(True)
+    w = torch.randn(N, K, device=DEV, requires_grad=True)
+    b = torch.randn(N, device=DEV, requires_grad=True)
+    res = torch.randn(4, T // 4, N, device=DEV, requires_grad=True)
+    g = torch.randn(4, T // 4, N, device=DEV)
+    out = ops.linear_dropout_add(x, w, b, res, 0.0, True)
+    assert out.dtype == torch.float32
+    out.backward(g)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().bfloat16().float().requires_grad_(True)
+    br, rr = b.detach().clone().requires_grad_(True), res.detach().clone().requires_grad_(True)
+    ref = rr + torch.nn.functional.linear(xr, wr, br)
+    ref.backward(g)
+    rel = lambda a, c: ((a.float() - c.float()).norm() / c.float().norm()).item()
+    assert rel(out, ref) < 5e-3
+    assert rel(x.grad, xr.grad) < 1e-2 and rel(w.grad, wr.grad) < 1e-2 and rel(b.grad, br.grad) < 1e-2
+    assert torch.equal(res.grad, g)
+    # dropout: forward mask == backward mask
+    b2 = torch.zeros(N, device=DEV, requires_grad=True)
+    x0 = torch.zeros(4, T // 4, K, device=DEV).bfloat16()
+    ones = torch.ones(N, device=DEV)
+    o2 = ops.linear_dropout_add(x0, w.detach(), (b2 + ones), torch.zeros_like(res), 0.1, True)   # = mask / (1 - p)
+    o2.sum().backward()
+    assert torch.allclose(b2.grad, o2.sum((0, 1)), rtol=2e-2, atol=1.0)
+    assert abs(o2.mean().item() - 1.0) < 0.02
