@@ -191,7 +191,7 @@ class _LinearDropoutAdd(torch.autograd.Function):
         z = g.gemm_nt(x16, w16, b32, "none")
         res = residual.float().contiguous()
         out = torch.empty_like(res)
-        so = _next_seed_off(z.device) if p > 0 else None
+        so = _next_seed_off(z.device)          # the kernel reads the pair even for p == 0
         call("fdt_dropout_add", z, 1, res, out, i64(z.numel()), float(p), so)
         ctx.save_for_backward(x16, w16, weight, bias, so)
         ctx.p, ctx.shp, ctx.xdtype = float(p), shp, x.dtype
