@@ -157,3 +157,93 @@ def test_resume_with_other_optimizer_skips_sidecar(tmp_path):
     ck.save_checkpoint("resnet", m, 50.0, 1, 0, str(tmp_path), opt, None)
     assert ck.load_optimizer_sidecar("resnet", MADGRAD(m.parameters(), lr=1e-3), None, str(tmp_path)) is False
     assert ck.load_optimizer_sidecar("resnet", NGD(m.parameters(), lr=0.1, momentum=0.9), None, str(tmp_path)) is True
+
+
+def test_loader_small_ring_and_staged_batches():
+    """ring < 8 used to index past the allocated staging buffers (advisor finding): the ring is now as long as it says."""
+    import torch
+    from fdt.data.loader import TensorBatchLoader
+    x = torch.arange(64 * 3).reshape(64, 3).float()
+    y = torch.arange(64)
+    dl = TensorBatchLoader((x, y), 4, shuffle=False, drop_last=True, pin=False, ring=2)
+    assert dl.ring >= 8 and len(dl._stage) == dl.ring
+    seen = [b[1].clone() for b in dl]
+    assert len(seen) == 16 and torch.equal(torch.cat(seen), y)
+
+
+def test_optimizer_sidecar_is_per_rank_when_sharded(tmp_path):
+    """A sharded engine writes one optimizer sidecar per rank, and a rank never loads another rank's shard."""
+    import torch
+    from fdt.engine import checkpoint as ckpt
+    from fdt.optim import NGD
+
+    class Eng(torch.nn.Module):
+        optimizer_state_sharded = True
+
+        def __init__(self):
+            super().__init__()
+            self.l = torch.nn.Linear(8, 6, bias=False)
+
+    for rank in (0, 1):
+        eng = Eng()
+        opt = NGD(eng.parameters(), lr=0.1, momentum=0.9)
+        eng.l.weight.grad = torch.randn(6, 8)
+        opt.step()
+        ckpt.save_checkpoint("m", eng, 0.5, 1, rank, str(tmp_path), opt, None)
+    assert (tmp_path / "m_opt_rank0.pth").exists() and (tmp_path / "m_opt_rank1.pth").exists()
+    assert not (tmp_path / "m_opt.pth").exists()
+    eng = Eng()
+    opt = NGD(eng.parameters(), lr=0.1, momentum=0.9)
+    assert ckpt.load_optimizer_sidecar("m", opt, None, str(tmp_path), rank=1, sharded=True)
+    # a shard that belongs to another rank is refused
+    import shutil
+    shutil.copy(tmp_path / "m_opt_rank0.pth", tmp_path / "m_opt_rank3.pth")
+    opt3 = NGD(Eng().parameters(), lr=0.1, momentum=0.9)
+    assert not ckpt.load_optimizer_sidecar("m", opt3, None, str(tmp_path), rank=3, sharded=True)
+
+
+def test_ngd_load_state_dict_validates_before_mutating():
+    import torch
+    from fdt.optim import NGD
+    a = torch.nn.Linear(8, 6, bias=False)
+    oa = NGD(a.parameters(), lr=0.1, momentum=0.9)
+    a.weight.grad = torch.randn(6, 8)
+    oa.step()
+    sd = oa.state_dict()
+    b = torch.nn.Linear(10, 6, bias=False)           # different shape: the state must be rejected untouched
+    ob = NGD(b.parameters(), lr=0.3, momentum=0.5)
+    with pytest.raises(ValueError):
+        ob.load_state_dict(sd)
+    assert ob.param_groups[0]["lr"] == 0.3 and ob.param_groups[0]["momentum"] == 0.5
+    c = torch.nn.Linear(8, 6, bias=False)
+    oc = NGD(c.parameters(), lr=0.3, momentum=0.5)
+    oc.load_state_dict(sd)
+    assert oc.param_groups[0]["lr"] == 0.1
+
+
+def test_fallback_counter_and_strict_mode():
+    from fdt.ops import _lib
+    n0 = _lib.FALLBACKS.count
+    _lib.note_fallback("unit_test_op", "because")
+    assert _lib.FALLBACKS.count == n0 + 1 and _lib.FALLBACKS.by_name["unit_test_op: because"] >= 1
+    _lib.set_strict(True)
+    try:
+        with pytest.raises(_lib.NativeCoverageError):
+            _lib.note_fallback("unit_test_op", "strict")
+    finally:
+        _lib.set_strict(False)
+        _lib.FALLBACKS.count -= 1
+        _lib.FALLBACKS.by_name.pop("unit_test_op: because", None)
+
+
+def test_c_abi_signatures_cover_every_entry_point():
+    """Every FDT_API symbol of the sources has a declaration in include/fdt_b200.h (ctypes argtypes come from there)."""
+    import pathlib
+    import re
+    from fdt.ops import _lib
+    root = pathlib.Path(__file__).resolve().parent.parent
+    names = set()
+    for f in (root / "faster-distributed-training_b200" / "csrc").glob("*.cu"):
+        names |= set(re.findall(r"FDT_API int (fdt_\w+)", f.read_text()))
+    sigs = _lib.signatures()
+    assert names and not (names - set(sigs)), sorted(names - set(sigs))
