@@ -51,9 +51,12 @@ struct GemmParams {
     int omode, OH, OW, oph, opw;
 };
 
-// Column statistics (Σ, Σ² per output channel — the BatchNorm batch statistics of a conv output) are accumulated per
-// CTA in shared memory over all the tiles it owns and flushed with one global atomic per touched column at the end.
-constexpr int kSumCols = 2048;
+// Column statistics (Σ, Σ² per output channel — the BatchNorm batch statistics of a conv output): each warp reduces its
+// 32 rows with a shuffle butterfly, the four warps of an epilogue warpgroup meet in a scratch array, and one thread per
+// column adds the tile's total to the warpgroup's own accumulator in shared memory — plain loads and stores, no atomics
+// on shared memory (they are compare-and-swap loops for fp32).  The accumulators are flushed with one global atomic per
+// touched column when the CTA is done.
+constexpr int kSumCols = 1024;
 
 template <int BN, int kStages>
 struct SmemLayout {
@@ -63,9 +66,11 @@ struct SmemLayout {
     static constexpr int kCOff = kStages * kStageBytes;           // bf16 output staging: BN/64 atoms of 16 KB, per warpgroup
     static constexpr int kCBytes = 2 * (BN / 64) * 16384;
     static constexpr int kBarOff = kCOff + kCBytes;
-    static constexpr int kSumOff = kBarOff + (((2 * kStages + 4) * 8 + 16 + 15) & ~15);   // per-CTA column statistics
-    static constexpr int kTotal = kSumOff + 2 * kSumCols * 4 + 1024;                     // + alignment slack
+    static constexpr int kSumOff = kBarOff + (((2 * kStages + 4) * 8 + 16 + 15) & ~15);   // [2 warpgroups][Σ, Σ²][kSumCols]
+    static constexpr int kScrOff = kSumOff + 2 * 2 * kSumCols * 4;                       // [2 warpgroups][4 warps][Σ, Σ²][BN]
+    static constexpr int kTotal = kScrOff + 2 * 4 * 2 * BN * 4 + 1024;                   // + alignment slack
 };
+static_assert(SmemLayout<128, 4>::kTotal <= 232448 && SmemLayout<64, 7>::kTotal <= 232448, "shared memory budget");
 
 // Persistent: gridDim.x CTAs (<= #SMs) walk the tile list (m fastest, so neighbouring CTAs share the weight
 // tile in L2).  The accumulator is double-buffered in tensor memory (2 x BN columns): while the epilogue warps
@@ -81,9 +86,10 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
     n_tile = r / rows;
 }
 
-__device__ __forceinline__ bool tma_out_any(const GemmParams& p) { return p.out != nullptr && p.omode == 0; }
+// what the epilogue of an instantiation does besides the bf16 TMA store (EPI_ANY: decided at run time from GemmParams)
+enum : int { EPI_STORE = 0, EPI_ADDEND = 1, EPI_SUMS = 2, EPI_ANY = 7 };
 
-template <int BN, int kStages, bool kConv>
+template <int BN, int kStages, bool kConv, int kEpi>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
@@ -110,9 +116,10 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     if (warp == 1) tmem_alloc<2 * BN>(tmem_ptr);
     float* s_sums = reinterpret_cast<float*>(smem + L::kSumOff);
+    float* s_scr = reinterpret_cast<float*>(smem + L::kScrOff);
     const bool smem_sums = p.sums != nullptr && p.N <= kSumCols;
     if (smem_sums)
-        for (int i = threadIdx.x; i < 2 * p.N; i += kThreads) s_sums[i] = 0.f;
+        for (int i = threadIdx.x; i < 4 * kSumCols; i += kThreads) s_sums[i] = 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -176,59 +183,79 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
     } else {
-        // ---------------- epilogue: warpgroup wg (warps 2-5 / 6-9) drains accumulator buffer wg, i.e. every other tile
+        // ---------------- epilogue: warpgroup wg (warps 2-5 / 6-9) drains accumulator buffer wg, i.e. every other tile.
+        // What the epilogue does is fixed per instantiation (kEpi != EPI_ANY) for the shapes a ResNet step is made of, so
+        // the per-chunk code is straight-line: with two warps per scheduler there is nothing to hide a branch behind.
+        constexpr bool kAny = kEpi == EPI_ANY;
+        const bool has_bias = kAny && p.bias != nullptr;
+        const bool has_act = kAny && p.act != ACT_NONE;
+        const bool has_addend = kAny ? p.addend != nullptr : (kEpi & EPI_ADDEND) != 0;
+        const bool has_sums = kAny ? p.sums != nullptr : (kEpi & EPI_SUMS) != 0;
+        const bool has_f32 = kAny && p.out_f32 != nullptr;
+        const bool direct = kAny && p.out != nullptr && p.omode == 1;
+        const bool tma_out = kAny ? (p.out != nullptr && p.omode == 0) : true;
         const int q = warp & 3;
         const int wg = (warp - 2) >> 2;
         const int bar_id = 1 + wg;
-        const int leader = 64 + wg * 128;                         // first thread of the warpgroup issues the TMA stores
+        const int tw = threadIdx.x - (64 + wg * 128);              // thread index inside the warpgroup
+        const bool is_leader = tw == 0;                            // first thread of the warpgroup issues the TMA stores
         uint8_t* sC = smem + L::kCOff + wg * (L::kCBytes / 2);
+        constexpr int kAtoms = BN / 64;                            // 64-column (128-byte) slabs of the staging tile
+        const int N = p.N;
         uint32_t t = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
             if ((int)(t & 1) != wg) continue;
             int m_tile, n_tile;
             tile_coords(tile, tiles_m, tiles_n, m_tile, n_tile);
             const uint32_t acc = t & 1, use = t >> 1;
-            mbar_wait(&tmem_full_bar[acc], use & 1);
-            tc_fence_after();
             const uint32_t tm = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
-            const int row = m_tile * BM + q * 32 + lane;
+            const int r_in = q * 32 + lane;
+            const int row = m_tile * BM + r_in;
             const bool row_ok = row < p.M;
-            const bool tma_out = p.out && p.omode == 0;
             size_t orow = (size_t)row;                              // row of `out` / `addend` this thread's row maps to
-            if (kConv && p.omode == 1 && row_ok) {
+            if (kConv && direct && row_ok) {
                 const int hw = p.H * p.W;
                 const int n = row / hw, rem = row - n * hw;
                 const int i = rem / p.W, j = rem - i * p.W;
                 orow = ((size_t)n * p.OH + 2 * i + p.oph) * p.OW + 2 * j + p.opw;
             }
-            if (tma_out && t > 1) {
-                // this warpgroup's staging tile is still being read by its previous TMA store
-                if (threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            if ((tma_out || has_sums) && t > 1) {
+                // slab 0 of the staging tile may still be read by the store this warpgroup issued for its previous tile
+                // (the store of the last slab, issued after it, is allowed to stay in flight)
+                if (is_leader && tma_out) {
+                    if (kAtoms > 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                }
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             }
-#pragma unroll 1
+            mbar_wait(&tmem_full_bar[acc], use & 1);
+            tc_fence_after();
+            // two register buffers: the TMEM load of chunk c+1 is in flight while chunk c is converted and stored
+            uint32_t rbuf[2][32];
+            tmem_ld_32x32(tm, rbuf[0]);
+#pragma unroll
             for (int c = 0; c < BN / 32; ++c) {
-                uint32_t r[32];
-                tmem_ld_32x32(tm + c * 32, r);
                 tmem_ld_wait();
-                if (c == BN / 32 - 1) {                  // whole accumulator is in registers: hand it back to the MMA warp
+                if (c + 1 < BN / 32) tmem_ld_32x32(tm + (c + 1) * 32, rbuf[(c + 1) & 1]);
+                else {                                   // whole accumulator is in registers: hand it back to the MMA warp
                     tc_fence_before();
                     mbar_arrive(&tmem_empty_bar[acc]);
                 }
+                const uint32_t* r = rbuf[c & 1];
                 const int col0 = n_tile * BN + c * 32;
                 float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                if (p.bias) {
+                if (has_bias) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
                 }
-                if (p.act != ACT_NONE) {
+                if (has_act) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
                 }
-                if (p.addend && row_ok) {
-                    const __nv_bfloat16* ad = p.addend + orow * p.N + col0;
+                if (has_addend && row_ok) {
+                    const __nv_bfloat16* ad = p.addend + orow * N + col0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
                         float f[8];
@@ -237,7 +264,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         for (int u = 0; u < 8; ++u) v[j + u] += f[u];
                     }
                 }
-                if (p.sums) {
+                if (has_sums) {
                     // per-column Σ and Σ² over the 32 rows of this warp: butterfly transpose-reduce —
                     // after 5 exchange steps lane j holds the total of column j.
                     float s1[32], s2[32];
@@ -256,24 +283,19 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             s2[j] = (upper ? s2[j + off] : s2[j]) + recv2;
                         }
                     }
-                    if (smem_sums) {
-                        atomicAdd(s_sums + col0 + lane, s1[0]);
-                        atomicAdd(s_sums + p.N + col0 + lane, s2[0]);
-                    } else {
-                        atomicAdd(p.sums + col0 + lane, s1[0]);
-                        atomicAdd(p.sums + p.N + col0 + lane, s2[0]);
-                    }
+                    float* sc = s_scr + ((wg * 4 + q) * 2) * BN + c * 32 + lane;
+                    sc[0] = s1[0];
+                    sc[BN] = s2[0];
                 }
-                if (p.out && p.omode == 1) {
+                if (direct) {
                     if (row_ok) {
-                        __nv_bfloat16* o = p.out + orow * p.N + col0;
+                        __nv_bfloat16* o = p.out + orow * N + col0;
 #pragma unroll
                         for (int j = 0; j < 32; j += 8) st8(o + j, pack8(v + j));
                     }
-                } else if (p.out) {
+                } else if (tma_out) {
                     // bf16 tile → shared memory in the 128B-swizzled layout of the output tensor map
                     uint8_t* atom = sC + (c >> 1) * 16384;
-                    const int r_in = q * 32 + lane;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
                         const int col = (c & 1) * 32 + j;
@@ -281,31 +303,54 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         *reinterpret_cast<uint4*>(atom + off) = pack8(v + j).u;
                     }
                 }
-                if (row_ok && p.out_f32) {
-                    float* o = p.out_f32 + (size_t)row * p.N + col0;
+                if (has_f32 && row_ok) {
+                    float* o = p.out_f32 + (size_t)row * N + col0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 }
-            }
-            if (tma_out) {
-                fence_proxy_async();
-                asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");          // the 4 warps of this warpgroup
-                if (threadIdx.x == leader) {
-#pragma unroll
-                    for (int a = 0; a < BN / 64; ++a)
+                if (tma_out && (c & 1)) {
+                    // a 64-column slab is complete: store it now, so its drain overlaps the conversion of the next slab
+                    const int a = c >> 1;
+                    fence_proxy_async();
+                    if (a + 1 < kAtoms && t > 1 && is_leader)          // the next slab must be free before anyone writes it
+                        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");          // the 4 warps of this warpgroup
+                    if (is_leader) {
                         tma_store_2d(&tmC, sC + a * 16384, n_tile * BN + a * 64, m_tile * BM);
-                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                }
+            }
+            if (has_sums) {
+                // the four warps' column partials of this tile are in the scratch array (ordered by the slab barrier above)
+                if (!tma_out) asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+                if (tw < BN) {
+                    const float* sc = s_scr + wg * 8 * BN + tw;
+                    const float a = (sc[0] + sc[2 * BN]) + (sc[4 * BN] + sc[6 * BN]);
+                    const float b = (sc[BN] + sc[3 * BN]) + (sc[5 * BN] + sc[7 * BN]);
+                    const int col = n_tile * BN + tw;
+                    if (smem_sums) {
+                        float* ws = s_sums + wg * 2 * kSumCols;
+                        ws[col] += a;
+                        ws[kSumCols + col] += b;
+                    } else {
+                        atomicAdd(p.sums + col, a);
+                        atomicAdd(p.sums + N + col, b);
+                    }
                 }
             }
         }
-        if (smem_sums) {
-            asm volatile("bar.sync 3, 256;" ::: "memory");          // both epilogue warpgroups are done accumulating
-            for (int i = threadIdx.x - 64; i < 2 * p.N; i += 256) {
-                const float v = s_sums[i];
-                if (v != 0.f) atomicAdd(p.sums + i, v);
+        if (has_sums) {
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+            if (smem_sums) {
+                const float* ws = s_sums + wg * 2 * kSumCols;
+                for (int i = tw; i < N; i += 128) {
+                    const float a = ws[i], b = ws[kSumCols + i];
+                    if (a != 0.f || b != 0.f) { atomicAdd(p.sums + i, a); atomicAdd(p.sums + N + i, b); }
+                }
             }
         }
-        if (tma_out_any(p) && threadIdx.x == leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (tma_out && is_leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -361,14 +406,14 @@ bool encode_nhwc(CUtensorMap* m, const void* ptr, int Nb, int H, int W, int C, i
     return r == CUDA_SUCCESS;
 }
 
-template <int BN, bool kConv>
-int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t st) {
+template <int BN, bool kConv, int kEpi>
+int launch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t st) {
     CUtensorMap tmC;
     if (p.out) { if (!encode_2d(&tmC, p.out, p.N, p.M, 64, BM)) return -4; }
     else tmC = tmB;
     constexpr int kStages = (BN == 128) ? 4 : 7;      // one persistent CTA per SM: operand ring + 2 staging tiles
     using L = SmemLayout<BN, kStages>;
-    auto kern = gemm_nt_kernel<BN, kStages, kConv>;
+    auto kern = gemm_nt_kernel<BN, kStages, kConv, kEpi>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return (int)e;
     const int num_tiles = ((p.M + BM - 1) / BM) * (p.N / BN);
@@ -378,6 +423,17 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, 
     if (fdt::launch(kern, dim3(grid), dim3(kThreads), L::kTotal, st, tmA, tmB, tmC, p) != cudaSuccess) return (int)cudaGetLastError();
     FDT_CHECK_LAUNCH();
     return 0;
+}
+
+// The common epilogues (plain store, store + residual addend, store + column statistics) have their own instantiations.
+template <int BN, bool kConv>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t st) {
+    const bool simple = p.out && !p.out_f32 && !p.bias && p.act == ACT_NONE && p.omode == 0 && !(p.sums && p.addend);
+    static const bool force_any = [] { const char* e = getenv("FDT_GEMM_EPI_ANY"); return e && e[0] == '1'; }();
+    if (!simple || force_any) return launch_epi<BN, kConv, EPI_ANY>(tmA, tmB, p, st);
+    if (p.sums) return launch_epi<BN, kConv, EPI_SUMS>(tmA, tmB, p, st);
+    if (p.addend) return launch_epi<BN, kConv, EPI_ADDEND>(tmA, tmB, p, st);
+    return launch_epi<BN, kConv, EPI_STORE>(tmA, tmB, p, st);
 }
 
 // 128-wide N tiles unless that leaves more than half of the SMs without a tile (deep, narrow problems such as the

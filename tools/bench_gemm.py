@@ -56,7 +56,7 @@ def main():
     if "--gemm-only" in sys.argv:
         return gemm_table()
     B = 128
-    print("conv fwd (N=128): us native | us cudnn | TFLOP/s native | GB/s native (min traffic)")
+    print("conv fwd (N=128): us native | us native + BN statistics epilogue | us cudnn | TFLOP/s native | GB/s native (min traffic)")
     for (C, O, HW, k) in [(64, 64, 32, 3), (64, 64, 32, 1), (64, 256, 32, 1), (256, 64, 32, 1), (128, 128, 16, 3), (128, 512, 16, 1),
                           (512, 128, 16, 1), (256, 256, 8, 3), (256, 1024, 8, 1), (1024, 256, 8, 1), (512, 512, 4, 3),
                           (512, 2048, 4, 1), (2048, 512, 4, 1)]:
@@ -65,9 +65,11 @@ def main():
         xs = [torch.randn(B, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last) for _ in range(nb)]
         w = (torch.randn(O, C, k, k, device="cuda") / math.sqrt(C * k * k)).bfloat16().contiguous(memory_format=torch.channels_last)
         tn = graph_time([(lambda x=x: g.conv_fwd(x, w, 1, k // 2)) for x in xs])
+        sums = torch.zeros(2 * O, device="cuda")
+        ts = graph_time([(lambda x=x: g.conv_fwd(x, w, 1, k // 2, sums)) for x in xs])
         tl = graph_time([(lambda x=x: F.conv2d(x, w, padding=k // 2)) for x in xs])
         fl = 2 * B * HW * HW * C * O * k * k
-        print(f"C{C:4d} O{O:4d} {HW:2d}x{HW:<2d} k{k}: {tn:8.1f} | {tl:8.1f} | {fl / tn / 1e6:7.1f} | {by / tn / 1e3:7.0f}")
+        print(f"C{C:4d} O{O:4d} {HW:2d}x{HW:<2d} k{k}: {tn:8.1f} | {ts:8.1f} | {tl:8.1f} | {fl / tn / 1e6:7.1f} | {by / tn / 1e3:7.0f}")
     gemm_table()
     print("channel kernels: [P,C] bf16: us reduce2(stats) GB/s | us affine_act GB/s")
     for (P, C) in [(131072, 64), (131072, 256), (32768, 512), (8192, 1024), (2048, 2048)]:
