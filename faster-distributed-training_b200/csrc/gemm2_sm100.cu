@@ -100,6 +100,10 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
     n_tile = r / rows;
 }
 
+// what the epilogue of an instantiation does besides the bf16 TMA store (EPI_ANY: decided at run time from G2Params)
+enum : int { EPI_STORE = 0, EPI_ADDEND = 1, EPI_BIAS = 2, EPI_ANY = 7 };
+
+template <int kEpi>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm2_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmC, const G2Params p) {
@@ -180,13 +184,20 @@ gemm2_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
         }
     } else {
+        // What the epilogue does besides the bf16 store is fixed per instantiation (kEpi != EPI_ANY), so the per-chunk
+        // code is straight-line: with two epilogue warps per scheduler there is nothing to hide a branch behind.
+        constexpr bool kAny = kEpi == EPI_ANY;
+        const bool has_bias = kAny ? p.bias != nullptr : (kEpi & EPI_BIAS) != 0;
+        const bool has_act = kAny && p.act != ACT_NONE;
+        const bool has_addend = kAny ? p.addend != nullptr : (kEpi & EPI_ADDEND) != 0;
         const int q = warp & 3;
         const int wg = (warp - 2) >> 2;
         const int bar_id = 1 + wg;
-        const int store_thread = 64 + wg * 128;
-        uint8_t* sC = smem + kCOff + wg * (kCBytes / 2);
+        const bool is_store_thread = threadIdx.x == 64 + wg * 128;
+        uint8_t* sC = smem + kCOff + wg * (kCBytes / 2);            // two 64-column slabs, used alternately
         const uint32_t empty_remote0 = mapa(smem_u32(&tmem_empty_bar[0]), 0);
         const uint32_t empty_remote1 = mapa(smem_u32(&tmem_empty_bar[1]), 0);
+        const int N = p.N;
         uint32_t t = 0, stores = 0;
         for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++t) {
             if ((int)(t & 1) != wg) continue;
@@ -197,69 +208,80 @@ gemm2_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             tc_fence_after();
             const uint32_t tm = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
             const int row0 = m_tile * 2 * BM + (int)rank * BM;
-            const int row = row0 + q * 32 + lane;
+            const int r_in = q * 32 + lane;
+            const int row = row0 + r_in;
             const bool row_ok = row < p.M;
-#pragma unroll 1
-            for (int half = 0; half < 2; ++half) {
-                if (stores > 0) {       // the staging tile is still being read by this warpgroup's previous TMA store
-                    if (threadIdx.x == store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                    asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-                }
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(tm + half * 128 + c * 32, r);
-                    tmem_ld_wait();
-                    if (half == 1 && c == 3) {            // whole accumulator half is in registers: hand it back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) {
-                            if (leader) mbar_arrive(&tmem_empty_bar[acc]);
-                            else mbar_arrive_remote(acc ? empty_remote1 : empty_remote0);
-                        }
-                    }
-                    const int col0 = n_tile * BN + half * 128 + c * 32;
-                    float v[32];
+            // two register buffers: the TMEM load of chunk c+1 is in flight while chunk c is converted and stored
+            uint32_t rbuf[2][32];
+            tmem_ld_32x32(tm, rbuf[0]);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (p.bias) {
+            for (int c = 0; c < BN / 32; ++c) {
+                tmem_ld_wait();
+                if (c + 1 < BN / 32) tmem_ld_32x32(tm + (c + 1) * 32, rbuf[(c + 1) & 1]);
+                else {                                    // whole accumulator half is in registers: hand it back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (leader) mbar_arrive(&tmem_empty_bar[acc]);
+                        else mbar_arrive_remote(acc ? empty_remote1 : empty_remote0);
+                    }
+                }
+                const uint32_t* r = rbuf[c & 1];
+                const int col0 = n_tile * BN + c * 32;
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                if (has_bias) {
+                    if (kAny) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
-                    }
-                    if (p.act != ACT_NONE) {
+                    } else {                                 // 16-byte aligned bias (checked by the launcher)
+                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
-                    }
-                    if (p.addend && row_ok) {
-                        const __nv_bfloat16* ad = p.addend + (size_t)row * p.N + col0;
-#pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            float f[8];
-                            unpack8(ld8(ad + j), f);
-#pragma unroll
-                            for (int u = 0; u < 8; ++u) v[j + u] += f[u];
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 b = __ldg(b4 + j);
+                            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
                         }
                     }
-                    uint8_t* atom = sC + (c >> 1) * 16384;
-                    const int r_in = q * 32 + lane;
+                }
+                if (has_act) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
+                }
+                if (has_addend && row_ok) {
+                    const __nv_bfloat16* ad = p.addend + (size_t)row * N + col0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
-                        const int col = (c & 1) * 32 + j;
-                        const uint32_t off = (uint32_t)(r_in * 128 + ((((col >> 3) ^ (r_in & 7)) << 4)));
-                        *reinterpret_cast<uint4*>(atom + off) = pack8(v + j).u;
+                        float f[8];
+                        unpack8(ld8(ad + j), f);
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) v[j + u] += f[u];
                     }
                 }
-                fence_proxy_async();
-                asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-                if (threadIdx.x == store_thread) {
-                    tma_store_2d(&tmC, sC, n_tile * BN + half * 128, row0);
-                    tma_store_2d(&tmC, sC + 16384, n_tile * BN + half * 128 + 64, row0);
-                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                const int slab = c >> 1;                               // 64-column slab of the tile (0..3)
+                uint8_t* atom = sC + ((stores + slab) & 1) * 16384;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    const int col = (c & 1) * 32 + j;
+                    const uint32_t off = (uint32_t)(r_in * 128 + ((((col >> 3) ^ (r_in & 7)) << 4)));
+                    *reinterpret_cast<uint4*>(atom + off) = pack8(v + j).u;
                 }
-                ++stores;
+                if (c & 1) {
+                    // the slab is complete: store it now so that its drain overlaps the conversion of the next one.  Before
+                    // the barrier the store thread makes sure the PREVIOUS slab's store has been read out of shared
+                    // memory — that is the buffer the next slab is written to.
+                    fence_proxy_async();
+                    if (is_store_thread && stores + slab > 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+                    if (is_store_thread) {
+                        tma_store_2d(&tmC, atom, n_tile * BN + slab * 64, row0);
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                }
             }
+            stores += BN / 64;
         }
-        if (threadIdx.x == store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (is_store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -308,12 +330,6 @@ FDT_API int fdt_gemm2_nt(const void* A, const void* B, void* out_bf16, const flo
     G2Params p{};
     p.M = M; p.N = N; p.num_kb = K / BK; p.out = (__nv_bfloat16*)out_bf16; p.bias = bias;
     p.addend = (const __nv_bfloat16*)addend; p.act = act;
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(gemm2_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
     static int num_sms = 0;
     if (!num_sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
     const int num_tiles = ((M + 2 * BM - 1) / (2 * BM)) * (N / BN);
@@ -325,7 +341,16 @@ FDT_API int fdt_gemm2_nt(const void* A, const void* B, void* out_bf16, const flo
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_nt_kernel, tmA, tmB, tmC, p);
+    // the common epilogues (plain store, + bias, + residual addend) have their own straight-line instantiations
+    void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, G2Params) = gemm2_nt_kernel<EPI_ANY>;
+    if (act == ACT_NONE && !(bias && addend)) {
+        if (bias) { if ((reinterpret_cast<uintptr_t>(bias) & 15) == 0) kern = gemm2_nt_kernel<EPI_BIAS>; }
+        else if (addend) kern = gemm2_nt_kernel<EPI_ADDEND>;
+        else kern = gemm2_nt_kernel<EPI_STORE>;
+    }
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
     if (e != cudaSuccess) return (int)e;
     FDT_CHECK_LAUNCH();
     return 0;
