@@ -37,7 +37,6 @@ struct TfParams {
     int BN;                     // N tile (multiple of 16, <= 128)
     int a_mn, b_mn;             // operand storage: 0 = K contiguous ([rows][K]), 1 = M/N contiguous ([K][rows])
     int epi;
-    int c_trans;                // EPI_SUB/STORE: C/out element (m, n) lives at [n * ldc + m] instead of [m * ldc + n]
     int terms;                  // 3: fp32-accurate split products; 1: plain tf32
     float* out; const float* cin;
     int64_t ldc, batch_stride_c;
@@ -106,7 +105,7 @@ __device__ __forceinline__ void convert_tile(uint8_t* hi, uint8_t* lo, const uin
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TfParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -205,54 +204,32 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
                 const int n0 = n_tile * p.BN + c * 32;
                 if (!m_ok) continue;
-                if (p.c_trans) {
-                    // element (m, n) at [n * ldc + m]: lanes (consecutive m) hit consecutive addresses
-                    float x[32];
-                    if (p.epi == EPI_SUB) {
+                const size_t row = (size_t)m * p.ldc;
+                float4 x[8];
+                if (p.epi == EPI_SUB) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const int n = n0 + j;
-                            x[j] = (n < p.N && c * 32 + j < p.BN) ? __ldg(cin + (size_t)n * p.ldc + m) : 0.f;
-                        }
+                    for (int j = 0; j < 8; ++j) {
+                        const int n = n0 + 4 * j;
+                        x[j] = (n + 3 < p.N && c * 32 + 4 * j + 3 < p.BN) ? __ldg(reinterpret_cast<const float4*>(cin + row + n))
+                                                                          : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
+                }
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int n = n0 + j;
-                        if (n < p.N && c * 32 + j < p.BN) {
-                            const size_t idx = (size_t)n * p.ldc + m;
-                            float v = __uint_as_float(r[j]);
-                            if (p.epi == EPI_SUB) { sq_in += x[j] * x[j]; v = x[j] - v; sq_out += v * v; }
-                            if (p.epi == EPI_RED) atomicAdd(out + idx, v); else out[idx] = v;
+                for (int j = 0; j < 32; j += 4) {
+                    const int n = n0 + j;
+                    if (n + 3 < p.N && c * 32 + j + 3 < p.BN) {
+                        float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                               __uint_as_float(r[j + 3]));
+                        if (p.epi == EPI_SUB) {
+                            const float4 xx = x[j >> 2];
+                            sq_in += xx.x * xx.x + xx.y * xx.y + xx.z * xx.z + xx.w * xx.w;
+                            v = make_float4(xx.x - v.x, xx.y - v.y, xx.z - v.z, xx.w - v.w);
+                            sq_out += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
                         }
-                    }
-                } else {
-                    const size_t row = (size_t)m * p.ldc;
-                    float4 x[8];
-                    if (p.epi == EPI_SUB) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int n = n0 + 4 * j;
-                            x[j] = (n + 3 < p.N && c * 32 + 4 * j + 3 < p.BN) ? __ldg(reinterpret_cast<const float4*>(cin + row + n))
-                                                                              : make_float4(0.f, 0.f, 0.f, 0.f);
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        const int n = n0 + j;
-                        if (n + 3 < p.N && c * 32 + j + 3 < p.BN) {
-                            float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                                   __uint_as_float(r[j + 3]));
-                            if (p.epi == EPI_SUB) {
-                                const float4 xx = x[j >> 2];
-                                sq_in += xx.x * xx.x + xx.y * xx.y + xx.z * xx.z + xx.w * xx.w;
-                                v = make_float4(xx.x - v.x, xx.y - v.y, xx.z - v.z, xx.w - v.w);
-                                sq_out += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-                            }
-                            if (p.epi == EPI_RED)
-                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(out + row + n), "f"(v.x), "f"(v.y),
-                                             "f"(v.z), "f"(v.w) : "memory");
-                            else *reinterpret_cast<float4*>(out + row + n) = v;
-                        }
+                        if (p.epi == EPI_RED)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(out + row + n), "f"(v.x), "f"(v.y),
+                                         "f"(v.z), "f"(v.w) : "memory");
+                        else *reinterpret_cast<float4*>(out + row + n) = v;
                     }
                 }
             }
@@ -330,7 +307,10 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, TfParams p, int splits, c
     p.b_raw_off = off; if (p.b_mn) off += bt;
     p.stage_bytes = (off + 1023) & ~1023;
     p.num_kb = (p.K + BKE - 1) / BKE;
-    int stages = (220 * 1024) / p.stage_bytes;
+    // The four converter / epilogue warps of a CTA are latency-bound (one warp per scheduler), so two CTAs share an SM:
+    // the operand ring is sized to half of the shared memory (a ring that cannot fit twice gets a single stage at most).
+    int stages = (110 * 1024) / p.stage_bytes;
+    if (stages < 1) stages = (220 * 1024) / p.stage_bytes >= 1 ? 1 : 0;
     if (stages > 4) stages = 4;
     if (stages > p.num_kb) stages = p.num_kb < 1 ? 1 : p.num_kb;
     if (stages < 1) return -7;
@@ -372,7 +352,7 @@ FDT_API int fdt_ngd_project_ex(const float* X, const float* W, float* H, float* 
     TfParams p{};
     p.batches = n;
     // ---- H[N, R] = X Wᵀ :  M = N, N = R, K = D;  A = X (K-major, or [D][N] when transposed), B = W [R][D] K-major
-    p.M = N; p.N = R; p.K = Dw; p.BN = pick_bn(R); p.epi = EPI_STORE; p.c_trans = 0; p.a_mn = x_trans ? 1 : 0; p.b_mn = 0;
+    p.M = N; p.N = R; p.K = Dw; p.BN = pick_bn(R); p.epi = EPI_STORE; p.a_mn = x_trans ? 1 : 0; p.b_mn = 0;
     p.out = H; p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)N * R; p.sums = nullptr;
     if (!encode_operand(&tA, X, p.a_mn, N, D, n, BM)) return -4;
     if (!encode_operand(&tB, W, 0, R, Dw, n, p.BN)) return -4;
@@ -394,13 +374,21 @@ FDT_API int fdt_ngd_project_ex(const float* X, const float* W, float* H, float* 
     }
     int rc = launch(tA, tB, p, splits, st);
     if (rc) return rc;
-    // ---- Xhat = X − H W :  M = N, N = D, K = R;  A = H [N][R] K-major, B[n = d, k = r] = W[r][d]: stored [K][rows]
-    p.M = N; p.N = D; p.K = R; p.BN = pick_bn(D); p.epi = EPI_SUB; p.a_mn = 0; p.b_mn = 1;
-    p.out = Xhat; p.cin = X; p.sums = sums;
-    if (x_trans) { p.c_trans = 1; p.ldc = N; } else { p.c_trans = 0; p.ldc = D; }
+    p.epi = EPI_SUB; p.out = Xhat; p.cin = X; p.sums = sums; p.K = R;
     p.batch_stride_c = (int64_t)N * D;
-    if (!encode_operand(&tA, H, 0, N, R, n, BM)) return -4;
-    if (!encode_operand(&tB, W, 1, Dw, R, n, p.BN)) return -4;
+    if (!x_trans) {
+        // ---- Xhat = X − H W :  M = N, N = D, K = R;  A = H [N][R] K-major, B[n = d, k = r] = W[r][d]: stored [K][rows]
+        p.M = N; p.N = D; p.BN = pick_bn(D); p.a_mn = 0; p.b_mn = 1; p.ldc = D;
+        if (!encode_operand(&tA, H, 0, N, R, n, BM)) return -4;
+        if (!encode_operand(&tB, W, 1, Dw, R, n, p.BN)) return -4;
+    } else {
+        // ---- the gradient lies transposed ([D][N]): compute Xhatᵀ = Xᵀ − Wᵀ Hᵀ instead, so that the output tile is row-major
+        // where it is stored and the epilogue moves 16 bytes per access:  M = D, N = N, K = R;  A[m = d, k = r] = W[r][d]
+        // (stored [K][rows]), B = H [N][R] K-major.  Rows D .. Dw-1 of A are the zero padding and are never stored.
+        p.M = D; p.N = N; p.BN = pick_bn(N); p.a_mn = 1; p.b_mn = 0; p.ldc = N;
+        if (!encode_operand(&tA, W, 1, Dw, R, n, BM)) return -4;
+        if (!encode_operand(&tB, H, 0, N, R, n, p.BN)) return -4;
+    }
     return launch(tA, tB, p, 1, st);
 }
 
@@ -423,7 +411,7 @@ FDT_API int fdt_ngd_stats_j_ex(const float* H, const float* X, float* J, int n, 
     // M = R, N = D, K = N;  A[m = r, k = i] = H[i][r]: stored [K][rows];  B[n = d, k = i] = X[i][d] ([K][rows]) or X'[d][i] (K-major)
     // N extent = the padded Dw (a multiple of 4: the epilogue adds 4 columns at a time); X's tensor map keeps the true D, so the
     // padding columns receive zeros
-    p.M = R; p.N = Dw; p.K = N; p.BN = pick_bn(Dw); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = x_trans ? 0 : 1;
+    p.M = R; p.N = Dw; p.K = N; p.BN = pick_bn(Dw); p.epi = EPI_RED; p.a_mn = 1; p.b_mn = x_trans ? 0 : 1;
     p.out = J; p.cin = nullptr; p.ldc = Dw; p.batch_stride_c = (int64_t)R * Dw; p.sums = nullptr;
     if (!encode_operand(&tA, H, 1, R, N, n, BM)) return -4;
     if (!encode_operand(&tB, X, p.b_mn, D, N, n, p.BN)) return -4;
@@ -444,7 +432,7 @@ FDT_API int fdt_ngd_stats_hh(const float* H, float* L, int n, int N, int R, cuda
     CUtensorMap tA, tB;
     TfParams p{};
     p.batches = n;
-    p.M = R; p.N = R; p.K = N; p.BN = pick_bn(R); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 1; p.b_mn = 1;
+    p.M = R; p.N = R; p.K = N; p.BN = pick_bn(R); p.epi = EPI_RED; p.a_mn = 1; p.b_mn = 1;
     p.out = L; p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)R * R; p.sums = nullptr;
     if (!encode_operand(&tA, H, 1, R, N, n, BM)) return -4;
     if (!encode_operand(&tB, H, 1, R, N, n, p.BN)) return -4;
@@ -462,7 +450,7 @@ FDT_API int fdt_ngd_stats_kl(const float* J, const float* W, float* K, float* L,
     CUtensorMap tA, tB;
     TfParams p{};
     p.batches = n;
-    p.M = R; p.N = R; p.K = D; p.BN = pick_bn(R); p.epi = EPI_RED; p.c_trans = 0; p.a_mn = 0; p.b_mn = 0;
+    p.M = R; p.N = R; p.K = D; p.BN = pick_bn(R); p.epi = EPI_RED; p.a_mn = 0; p.b_mn = 0;
     p.cin = nullptr; p.ldc = R; p.batch_stride_c = (int64_t)R * R; p.sums = nullptr;
     if (!encode_operand(&tA, J, 0, R, D, n, BM)) return -4;
     if (!encode_operand(&tB, J, 0, R, D, n, p.BN)) return -4;
