@@ -289,19 +289,30 @@ ngd_sumsq2_kernel(const float* __restrict__ X, const float* __restrict__ Xh, flo
         atomicAdd(sums + n + f, tb);
     }
 }
-// out_f = isnan(p1) ? X_f : X̂_f · sqrt(p0 / (p1 + 1e-30))
+// out_f = isnan(p1) ? X_f : X̂_f · sqrt(p0 / (p1 + 1e-30)),  p0 = p_in[f], p1 = p_out[f].  The choice is uniform per factor,
+// so only one of the two inputs is read; 16 bytes per access when the factor length allows it.
+template <bool kVec>
 __global__ void __launch_bounds__(256)
-ngd_rescale_kernel(const float* __restrict__ X, const float* Xh, const float* __restrict__ sums,
-                   float* out, int n, int64_t M) {          // out may alias Xh (in-place rescale): no __restrict__ on the pair
+ngd_rescale_kernel(const float* __restrict__ X, const float* Xh, const float* __restrict__ p_in, const float* __restrict__ p_out,
+                   float* out, int64_t M) {                 // out may alias Xh (in-place rescale): no __restrict__ on the pair
     const int f = blockIdx.y;
-    const float p0 = sums[f], p1 = sums[n + f];
+    const float p0 = p_in[f], p1 = p_out[f];
     const bool bad = isnan(p1);
-    const float sc = sqrtf(p0 / (p1 + 1.0e-30f));
-    const float* x = X + (int64_t)f * M;
-    const float* xh = Xh + (int64_t)f * M;
+    const float sc = bad ? 1.f : sqrtf(p0 / (p1 + 1.0e-30f));
+    const float* src = (bad ? X : Xh) + (int64_t)f * M;
     float* o = out + (int64_t)f * M;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (int64_t)gridDim.x * blockDim.x)
-        o[i] = bad ? x[i] : xh[i] * sc;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (kVec) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* o4 = reinterpret_cast<float4*>(o);
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < (M >> 2); i += stride) {
+            float4 v = s4[i];
+            v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+            o4[i] = v;
+        }
+    } else {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += stride) o[i] = src[i] * sc;
+    }
 }
 
 struct NgdCommitDesc {          // one per factor; mirrored in fdt/ops/cuda_ops.py
@@ -438,14 +449,26 @@ FDT_API int fdt_ngd_sumsq2(const float* X, const float* Xh, float* sums, int n, 
     return 0;
 }
 
-FDT_API int fdt_ngd_rescale(const float* X, const float* Xh, const float* sums, float* out, int n, int64_t M, cudaStream_t st) {
-    int chunks = (int)((M + 256 * 4 - 1) / (256 * 4));
+// p_in / p_out: [n] each — Σ of squares of the reference input and of Xh.  With a chain of factors applied to one tensor
+// they come from different links: the norm the reference restores after every axis (ngd_optimizer.py:168) is the norm of the
+// chain's first input, so one rescale at the end with (first Σin, last Σout) equals the per-axis rescales.
+FDT_API int fdt_ngd_rescale2(const float* X, const float* Xh, const float* p_in, const float* p_out, float* out, int n, int64_t M,
+                             cudaStream_t st) {
+    if (n <= 0 || M <= 0) return n < 0 || M < 0 ? -1 : 0;
+    const bool vec = M % 4 == 0 && ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(Xh) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    const int64_t work = vec ? M / 4 : M;
+    int chunks = (int)((work + 256 * 4 - 1) / (256 * 4));
     if (chunks < 1) chunks = 1;
     const int cap = (148 * 8 + n - 1) / n;
     if (chunks > cap) chunks = cap;
-    ngd_rescale_kernel<<<dim3(chunks, n), 256, 0, st>>>(X, Xh, sums, out, n, M);
+    if (vec) ngd_rescale_kernel<true><<<dim3(chunks, n), 256, 0, st>>>(X, Xh, p_in, p_out, out, M);
+    else ngd_rescale_kernel<false><<<dim3(chunks, n), 256, 0, st>>>(X, Xh, p_in, p_out, out, M);
     FDT_CHECK_LAUNCH();
     return 0;
+}
+// sums: [2n] = Σ X_f² then Σ X̂_f²
+FDT_API int fdt_ngd_rescale(const float* X, const float* Xh, const float* sums, float* out, int n, int64_t M, cudaStream_t st) {
+    return fdt_ngd_rescale2(X, Xh, sums, sums + n, out, n, M, st);
 }
 
 // flags: `count` ints of caller-provided scratch.  max_elems = largest R*D among the factors (sizes the grid).

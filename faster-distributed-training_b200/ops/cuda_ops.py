@@ -898,15 +898,47 @@ def ngd_small_axis_ok(D: int, R: int) -> bool:
     return 2 <= D <= 12 and R == (D + 1) // 2
 
 
-def ngd_small_axis(X: torch.Tensor, W: torch.Tensor, A: int, D: int, B: int, J: Optional[torch.Tensor]):
+class NormChain:
+    """The factors of one tensor are applied axis after axis, and the reference restores the Frobenius norm after each of
+    them (ngd_optimizer.py:168) — so every link's output has the norm of the chain's FIRST input, and since every link is
+    linear in its input the intermediate rescales cancel: out = X̂_last · sqrt(Σ X_first² / Σ X̂_last²).  On steps without a
+    Fisher refresh (whose statistics need the properly scaled input) the links therefore skip their rescale pass (a read
+    and a write of the whole tensor each) and :meth:`finish` applies one at the end.  A non-finite link makes the final
+    Σ non-finite and the chain returns its first input (the reference falls back per axis, ngd_optimizer.py:157-159)."""
+
+    def __init__(self, x0: torch.Tensor):
+        self.x0 = x0
+        self.p_in = None
+        self.p_out = None
+
+    def link(self, sums: torch.Tensor, n: int):
+        if self.p_in is None:
+            self.p_in = sums[:n]
+        self.p_out = sums[n:2 * n]
+
+    def finish(self, xhat: torch.Tensor) -> torch.Tensor:
+        if self.p_in is None:
+            return xhat
+        xh = xhat if xhat.is_contiguous() else xhat.contiguous()
+        x0 = self.x0 if self.x0.is_contiguous() else self.x0.contiguous()
+        n = xh.shape[0]
+        call("fdt_ngd_rescale2", x0, xh, self.p_in, self.p_out, xh, n, i64(xh[0].numel()))
+        return xh
+
+
+def ngd_small_axis(X: torch.Tensor, W: torch.Tensor, A: int, D: int, B: int, J: Optional[torch.Tensor], chain=None):
     """Precondition a short axis of the physical gradient view ``X`` = [n, A, D, B] (csrc/ngd_axis.cu): projection,
     deflation, norm restoration and (when ``J`` is given) the Fisher statistics J = Σ h xᵀ, without materialising
-    H or a transposed copy.  Returns (p0 [n], out [same shape as X])."""
+    H or a transposed copy.  Returns (p0 [n], out [same shape as X]); with a :class:`NormChain` the rescale is left to
+    the end of the chain."""
     n = X.shape[0]
     Xhat = torch.empty_like(X)
     sums = torch.empty(2 * n, dtype=torch.float32, device=X.device)
     call("fdt_ngd_small_axis", X, W, Xhat, sums, J, n, i64(A), int(D), i64(B), int(W.shape[1]), launches=1)
-    call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(A * D * B))
+    if chain is not None:
+        chain.link(sums, n)
+    else:
+        call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(A * D * B))
     return sums[:n], Xhat
 
 
@@ -1008,10 +1040,12 @@ def ngd_tf32_ok(n, N, D, R, left) -> bool:
     return NGD_TC and R % 4 == 0 and 16 <= R <= 128 and ((N % 4 == 0) if left else (D % 4 == 0))
 
 
-def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool, sums: Optional[torch.Tensor] = None, D: Optional[int] = None):
+def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool, sums: Optional[torch.Tensor] = None, D: Optional[int] = None,
+                chain=None):
     """H = X Wᵀ and X̂ = X − H W for a factor batch on the tensor cores, then the norm-restoring rescale.  ``X`` is
     [n, N, D] (left=False) or the transposed gradient [n, D, N] (left=True), used where it lies.
-    Returns (H [n, N, R], out (same layout as X), p0 [n])."""
+    Returns (H [n, N, R], out (same layout as X), p0 [n]).  With a :class:`NormChain` the rescale is left to the end of
+    the chain and ``out`` is the unscaled X̂."""
     n, R, Dw = W.shape              # W: padded storage [n, R, Dw] (Dw = D rounded up to 4, zero padding columns)
     D = Dw if D is None else D
     N = X[0].numel() // D
@@ -1020,7 +1054,10 @@ def ngd_project(X: torch.Tensor, W: torch.Tensor, left: bool, sums: Optional[tor
     if sums is None:
         sums = torch.zeros(2 * n, dtype=torch.float32, device=X.device)
     call("fdt_ngd_project_ex", X, W, H, Xhat, sums, n, N, D, Dw, R, int(bool(left)), launches=2)
-    call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(N * D))
+    if chain is not None:
+        chain.link(sums, n)
+    else:
+        call("fdt_ngd_rescale", X, Xhat, sums, Xhat, n, i64(N * D))
     return H, Xhat, sums[:n]
 
 

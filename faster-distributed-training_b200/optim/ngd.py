@@ -28,6 +28,7 @@ Fixed (Q18): Nesterov uses ``d_p + momentum * buf``.
 from __future__ import annotations
 
 import math
+import os
 from collections import OrderedDict
 from typing import Dict, List, Optional, Tuple
 
@@ -255,7 +256,8 @@ def flush_refreshes(pending: List[FactorBatch]):
     pending.clear()
 
 
-def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optional[List[FactorBatch]] = None) -> torch.Tensor:
+def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optional[List[FactorBatch]] = None,
+                 chain=None) -> torch.Tensor:
     """Apply (and, on refresh steps, update) the inverse-Fisher factor.
 
     ``Xm`` is ``[n, N, D]`` (``left=False``) or its transpose ``[n, D, N]`` (``left=True``, used
@@ -319,7 +321,8 @@ def precondition(fb: FactorBatch, Xm: torch.Tensor, left: bool, pending: Optiona
         cu = ops._cu()
         if tc:
             fb._h_rows = True
-            H, out, p0 = cu.ngd_project(Xc, fb.Wp, left, getattr(fb, "_sums", None), fb.D)   # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale
+            # tcgen05 3xTF32: H, X̂ (+Σx², Σx̂²), rescale (left to the end of the tensor's chain of axes when there is no refresh)
+            H, out, p0 = cu.ngd_project(Xc, fb.Wp, left, getattr(fb, "_sums", None), fb.D, None if updating else chain)
             if updating:
                 if pending is None:
                     _refresh(fb, Xc, left, H, p0)
@@ -381,7 +384,8 @@ def _small_axis_native(fb: FactorBatch, d_p: torch.Tensor) -> bool:
     return ops.use_native(d_p) and ops._cu().ngd_small_axis_ok(fb.D, fb.R)
 
 
-def precondition_small_axis(fb: FactorBatch, d_p: torch.Tensor, pa: int, pending: Optional[List[FactorBatch]]) -> torch.Tensor:
+def precondition_small_axis(fb: FactorBatch, d_p: torch.Tensor, pa: int, pending: Optional[List[FactorBatch]],
+                            chain=None) -> torch.Tensor:
     """:func:`precondition` for a short axis (D <= 12) of the stacked physical tensor ``d_p`` = [n, *phys]: the axis
     at physical position ``pa`` is preconditioned in place of the ``[n, N, D]`` matrix view, so no transposed copy
     is made and H is never materialised (csrc/ngd_axis.cu).  Same math as ngd_optimizer.py:138-168,195-218; the
@@ -407,7 +411,7 @@ def precondition_small_axis(fb: FactorBatch, d_p: torch.Tensor, pa: int, pending
     # (N <= D: the reference takes L = Hᵀ H there, ngd_optimizer.py:215-217 — the same matrix as J Wᵀ, since H = X Wᵀ)
     if updating and not hasattr(fb, "J"):
         _alloc_stats(fb)
-    p0, out = cu.ngd_small_axis(X, fb.W, A, fb.D, B, fb.J if updating else None)
+    p0, out = cu.ngd_small_axis(X, fb.W, A, fb.D, B, fb.J if updating else None, None if updating else chain)
     if updating:
         cu.ngd_small_kl(fb.J, fb.W, fb.K, fb.L)      # K = J Jᵀ, L = J Wᵀ in one small launch
         fb.tr.copy_(p0)
@@ -635,6 +639,7 @@ class NGD(Optimizer):
         n = d_p.shape[0]
         nd = len(sg.shape)
         phys_shape = tuple(d_p.shape[1:])
+        chain = self._norm_chain(sg, d_p)
         for axis in range(nd):
             D = sg.shape[axis]
             if D == 1:
@@ -647,16 +652,45 @@ class NGD(Optimizer):
                                                     group["eta"], d_p.dtype, d_p.device)
             if _small_axis_native(fb, d_p):
                 # short axis (conv kernel axes, class axes): one bandwidth-bound pass over the tensor where it lies
-                d_p = precondition_small_axis(fb, d_p, pa, pending)
+                d_p = precondition_small_axis(fb, d_p, pa, pending, chain)
             elif pa == nd - 1:
-                d_p = precondition(fb, d_p.reshape(n, N, D), False, pending).reshape(n, *phys_shape)
+                d_p = precondition(fb, d_p.reshape(n, N, D), False, pending, chain).reshape(n, *phys_shape)
             elif pa == 0:
-                d_p = precondition(fb, d_p.reshape(n, D, N), True, pending).reshape(n, *phys_shape)
+                d_p = precondition(fb, d_p.reshape(n, D, N), True, pending, chain).reshape(n, *phys_shape)
             else:
                 Xm = d_p.movedim(pa + 1, -1)
                 mid = Xm.shape
-                d_p = precondition(fb, Xm.reshape(n, N, D), False, pending).reshape(mid).movedim(-1, pa + 1)
+                d_p = precondition(fb, Xm.reshape(n, N, D), False, pending, chain).reshape(mid).movedim(-1, pa + 1)
+        if chain is not None:
+            d_p = chain.finish(d_p)
         return d_p
+
+    def _norm_chain(self, sg, d_p):
+        """A :class:`fdt.ops.cuda_ops.NormChain` when every axis of this tensor stack runs on a native kernel that can leave
+        its norm restoration to the end of the chain and no factor refreshes its Fisher estimate on this step."""
+        if not (d_p.is_cuda and d_p.dtype == torch.float32) or os.environ.get("FDT_NGD_NORM_CHAIN", "1") != "1":
+            return None
+        from .. import ops
+        if not ops.use_native(d_p):
+            return None
+        cu = ops._cu()
+        nd = len(sg.shape)
+        links = 0
+        for axis in range(nd):
+            D = sg.shape[axis]
+            if D == 1:
+                continue
+            fb = sg.factors.get(axis)
+            if fb is None or fb.t == 0 or fb.updating():
+                return None
+            pa = sg.axis_map[axis]
+            if cu.ngd_small_axis_ok(fb.D, fb.R):
+                links += 1
+            elif pa in (0, nd - 1) and cu.ngd_tf32_ok(fb.n, fb.N, fb.D, fb.R, pa == 0 and pa != nd - 1):
+                links += 1
+            else:
+                return None
+        return cu.NormChain(d_p) if links >= 2 else None
 
     def _side_streams(self, sgs: List[_ShapeGroup]):
         import os

@@ -219,6 +219,10 @@ int fdt_pool_fc_bwd(const float* dlogits, const float* W, const float* pooled, v
  * ref: ngd_optimizer.py:151-168,195-218,322-324 */
 int fdt_ngd_sumsq2(const float* X, const float* Xh, float* sums, int n, int64_t M, cudaStream_t st);
 int fdt_ngd_rescale(const float* X, const float* Xh, const float* sums, float* out, int n, int64_t M, cudaStream_t st);
+/* same with the two sums given separately ([n] each): the end of a chain of factors rescales once with the first link's input
+   norm and the last link's output norm */
+int fdt_ngd_rescale2(const float* X, const float* Xh, const float* p_in, const float* p_out, float* out, int n, int64_t M,
+                     cudaStream_t st);
 int fdt_ngd_commit_multi(const void* descs, int count, int* flags, int max_elems, cudaStream_t st);
 /* W1 = A (J + wc ∘ W) for every factor (80-byte descriptors: W1,d1,rho1,W,d,rho,A,J,wc pointers + int R, D), fused
  * with the finiteness check, then the guarded hand-over: 3 launches for the whole model */

@@ -536,6 +536,41 @@ def test_ngd_gpu_trajectory_matches_reference_and_uses_no_library_gemm():
         assert rel < 1e-3, (s, rel)
 
 
+def test_ngd_norm_chain_equals_per_axis_rescale(monkeypatch):
+    """On steps without a Fisher refresh the per-axis norm restorations are folded into ONE rescale at the end of a
+    tensor's chain of axes (fdt.ops.cuda_ops.NormChain): same parameters as rescaling after every axis
+    (ngd_optimizer.py:168), to fp32 rounding, over 16 steps (refresh and plain steps mixed)."""
+    from fdt.ops import _lib
+    from fdt.optim.ngd import NGD
+    from fdt.parallel.flat import FlatParameters
+    shapes = [(64, 32, 3, 3), (64, 32, 3, 3), (128, 64), (256, 128, 1, 1), (10, 7, 3, 3)]
+    g = torch.Generator().manual_seed(0)
+    init = [(torch.randn(*s, generator=g) * 0.1).cuda() for s in shapes]
+    outs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("FDT_NGD_NORM_CHAIN", mode)
+        ps = [torch.nn.Parameter(p.clone()) for p in init]
+        FlatParameters(ps, torch.device("cuda"))
+        opt = NGD(ps, lr=0.01, momentum=0.9, weight_decay=1e-4)
+        gg = torch.Generator(device="cuda").manual_seed(1)
+        before = _lib.LAUNCHES.by_name.get("fdt_ngd_rescale2", 0)
+        _lib.set_strict(True)
+        try:
+            for step in range(16):
+                for p in ps:
+                    p.grad.copy_(torch.randn(p.shape, device="cuda", generator=gg))
+                opt.step()
+        finally:
+            _lib.set_strict(False)
+        torch.cuda.synchronize()
+        used = _lib.LAUNCHES.by_name.get("fdt_ngd_rescale2", 0) - before
+        assert (used > 0) == (mode == "1"), (mode, used)
+        outs[mode] = [p.detach().clone() for p in ps]
+    for s, a, b in zip(shapes, outs["0"], outs["1"]):
+        rel = ((a - b).norm() / a.norm()).item()
+        assert rel < 2e-5, (s, rel)
+
+
 def test_batch_stat_normalisation_form_is_the_references():
     """The FusedConvBN form — UNBIASED variance, eps added to the standard deviation (resnet.py:85-100) — checked where it
     matters: 32 values per channel (biased vs unbiased differ by 1.6 %) and a conv output whose std is comparable to eps
