@@ -223,23 +223,53 @@ __device__ float philox_gamma(const Philox& rng, uint64_t off, uint32_t& ctr, fl
     }
     return boost * d;
 }
-__global__ void mixup_sample_kernel(const int64_t* __restrict__ seed_off, float alpha, int B, float* __restrict__ lam,
-                                    int64_t* __restrict__ perm) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+// One block.  Thread 0 draws lam (rejection sampling: a data-dependent number of Philox calls), then the B - 1 swap indices
+// of the Fisher-Yates shuffle — one Philox call each, the serial part of the old single-thread form — are generated by all
+// threads at their fixed counters, and thread 0 only walks the swaps in shared memory.  Same draws, same permutation.
+constexpr int kPermMax = 4096;
+__global__ void __launch_bounds__(256)
+mixup_sample_kernel(const int64_t* __restrict__ seed_off, float alpha, int B, float* __restrict__ lam,
+                    int64_t* __restrict__ perm) {
+    __shared__ int s_perm[kPermMax];
+    __shared__ int s_j[kPermMax];
+    __shared__ uint32_t s_ctr;
     Philox rng((uint64_t)seed_off[0]);
     const uint64_t off = (uint64_t)seed_off[1];
-    uint32_t ctr = 0x40000000u;                          // a counter range of its own (the augmentation draws use b < 2^30)
-    if (lam) {
-        float l = alpha;
-        if (alpha > 0.f) {
-            const float g0 = philox_gamma(rng, off, ctr, alpha), g1 = philox_gamma(rng, off, ctr, alpha);
-            l = g0 / fmaxf(g0 + g1, 1e-20f);
+    if (threadIdx.x == 0) {
+        uint32_t ctr = 0x40000000u;                      // a counter range of its own (the augmentation draws use b < 2^30)
+        if (lam) {
+            float l = alpha;
+            if (alpha > 0.f) {
+                const float g0 = philox_gamma(rng, off, ctr, alpha), g1 = philox_gamma(rng, off, ctr, alpha);
+                l = g0 / fmaxf(g0 + g1, 1e-20f);
+            }
+            lam[0] = l;
         }
-        lam[0] = l;
+        s_ctr = ctr;
     }
-    if (perm) {
+    if (!perm) return;
+    __syncthreads();
+    const uint32_t ctr0 = s_ctr;
+    if (B <= kPermMax) {
+        for (int i = threadIdx.x; i < B; i += blockDim.x) {
+            s_perm[i] = i;
+            if (i > 0) {                                 // the swap for position i is the (B - 1 - i)-th draw
+                const uint4 r = rng((uint64_t)(ctr0 + (uint32_t)(B - 1 - i)), off);
+                s_j[i] = (int)(((uint64_t)r.x * (uint64_t)(i + 1)) >> 32);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int i = B - 1; i > 0; --i) {            // Fisher-Yates
+                const int j = s_j[i];
+                const int t = s_perm[i]; s_perm[i] = s_perm[j]; s_perm[j] = t;
+            }
+        __syncthreads();
+        for (int i = threadIdx.x; i < B; i += blockDim.x) perm[i] = s_perm[i];
+    } else if (threadIdx.x == 0) {
+        uint32_t ctr = ctr0;
         for (int i = 0; i < B; ++i) perm[i] = i;
-        for (int i = B - 1; i > 0; --i) {                // Fisher-Yates
+        for (int i = B - 1; i > 0; --i) {
             const uint4 r = rng((uint64_t)ctr++, off);
             const int j = (int)(((uint64_t)r.x * (uint64_t)(i + 1)) >> 32);
             const int64_t t = perm[i]; perm[i] = perm[j]; perm[j] = t;
@@ -252,7 +282,7 @@ __global__ void mixup_sample_kernel(const int64_t* __restrict__ seed_off, float 
 // both optional (NULL); seed_off: device (seed, offset) pair.
 FDT_API int fdt_mixup_sample(const int64_t* seed_off, float alpha, int B, float* lam, int64_t* perm, cudaStream_t st) {
     if (!seed_off || B < 0) return -1;
-    mixup_sample_kernel<<<1, 32, 0, st>>>(seed_off, alpha, B, lam, perm);
+    mixup_sample_kernel<<<1, 256, 0, st>>>(seed_off, alpha, B, lam, perm);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -70,16 +70,13 @@ dgrad_weights_kernel(const WPrepDesc* __restrict__ descs) {
 }
 
 // Balanced form: one tile per block over the concatenated tile lists of all weights (a fixed number of blocks per weight
-// leaves the 512x512x3x3 filters with 12 tiles per block and the 64x64 ones with idle blocks).
+// leaves the 512x512x3x3 filters with 12 tiles per block and the 64x64 ones with idle blocks).  The (weight, tile) pair of
+// every block comes from a table the caller built with the descriptors — a search through the descriptor list would be a
+// chain of dependent loads as long as the list.
 __global__ void __launch_bounds__(256)
-dgrad_weights_flat_kernel(const WPrepDesc* __restrict__ descs, int count) {
-    int id = blockIdx.x;
-    for (int k = 0; k < count; ++k) {
-        const WPrepDesc d = descs[k];
-        const int n = d.T * ((d.O + kTile - 1) / kTile) * ((d.I + kTile - 1) / kTile);
-        if (id < n) { dgrad_weights_body(d, id, 1 << 30); return; }
-        id -= n;
-    }
+dgrad_weights_map_kernel(const WPrepDesc* __restrict__ descs, const int2* __restrict__ tile_map) {
+    const int2 m = tile_map[blockIdx.x];
+    dgrad_weights_body(descs[m.x], m.y, 1 << 30);
 }
 
 }  // namespace
@@ -92,10 +89,10 @@ FDT_API int fdt_dgrad_weights(const void* descs, int count, cudaStream_t st) {
     return 0;
 }
 
-// total_tiles = Σ over descriptors of T * ceil(O/64) * ceil(I/64) (computed by the caller, who built the table).
-FDT_API int fdt_dgrad_weights_flat(const void* descs, int count, int total_tiles, cudaStream_t st) {
-    if (count <= 0 || total_tiles <= 0) return 0;
-    dgrad_weights_flat_kernel<<<total_tiles, 256, 0, st>>>((const WPrepDesc*)descs, count);
+// tile_map: total_tiles x {descriptor index, tile index inside that weight} (int32 pairs, device memory)
+FDT_API int fdt_dgrad_weights_map(const void* descs, const void* tile_map, int total_tiles, cudaStream_t st) {
+    if (total_tiles <= 0) return 0;
+    dgrad_weights_map_kernel<<<total_tiles, 256, 0, st>>>((const WPrepDesc*)descs, (const int2*)tile_map);
     FDT_CHECK_LAUNCH();
     return 0;
 }

@@ -257,8 +257,13 @@ class FlatParameters:
         blob = b"".join(rows)
         dev = torch.empty(len(blob), dtype=torch.uint8, device=self.device)
         dev.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
-        tiles = sum(T * ((O + 63) // 64) * ((I + 63) // 64) for _, O, T, I, _, _ in ents)
-        self._dgrad_table = (dev, len(rows), tiles)
+        # one block per 64 x 64 tile: (descriptor, tile in that weight) for every block, so that no block searches the list
+        per = [T * ((O + 63) // 64) * ((I + 63) // 64) for _, O, T, I, _, _ in ents]
+        k = torch.repeat_interleave(torch.arange(len(per), dtype=torch.int32), torch.tensor(per))
+        starts = torch.cumsum(torch.tensor([0] + per[:-1]), 0).to(torch.int32)
+        local = torch.arange(sum(per), dtype=torch.int32) - starts[k.long()]
+        tile_map = torch.stack([k, local], 1).contiguous().to(self.device)
+        self._dgrad_table = (dev, tile_map, sum(per))
 
     def refresh_dgrad_shadow(self):
         if self.device.type != "cuda" or self.shadow_flat is None:
@@ -267,7 +272,7 @@ class FlatParameters:
             self._build_dgrad_table()
         if self._dgrad_table is not None:
             from ..ops._lib import call
-            call("fdt_dgrad_weights_flat", self._dgrad_table[0], self._dgrad_table[1], self._dgrad_table[2])
+            call("fdt_dgrad_weights_map", self._dgrad_table[0], self._dgrad_table[1], self._dgrad_table[2])
 
     def dgrad_shadow_of(self, p: torch.nn.Parameter, mode: int) -> Optional[torch.Tensor]:
         ent = getattr(self, "_dgrad_views", {}).get(p._fdt_flat[1])

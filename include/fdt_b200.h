@@ -175,7 +175,8 @@ int fdt_linear_wgrad(const void* dy, const void* x, float* dw, int M, int N, int
  * descs: `count` 32-byte device records {const bf16* src; bf16* dst; int O, T, I, mode}.  csrc/weight_prep.cu */
 int fdt_dgrad_weights(const void* descs, int count, cudaStream_t st);
 /* same, one 64x64 tile per block over all weights (total_tiles = sum of T*ceil(O/64)*ceil(I/64)): balanced */
-int fdt_dgrad_weights_flat(const void* descs, int count, int total_tiles, cudaStream_t st);
+/* one block per 64 x 64 tile, with a caller-built table of total_tiles x {descriptor index, tile index in that weight} */
+int fdt_dgrad_weights_map(const void* descs, const void* tile_map, int total_tiles, cudaStream_t st);
 /* explicit im2col / col2im (strided convs, the 3-channel stem): A[N*Ho*Wo, Kp] <-> x[N,H,W,C] */
 int fdt_im2col(const void* x, void* A, int N, int H, int W, int C, int k, int stride, int pad, int Ho, int Wo, int Kp,
                cudaStream_t st);

@@ -568,7 +568,9 @@ def test_ngd_norm_chain_equals_per_axis_rescale(monkeypatch):
         outs[mode] = [p.detach().clone() for p in ps]
     for s, a, b in zip(shapes, outs["0"], outs["1"]):
         rel = ((a - b).norm() / a.norm()).item()
-        assert rel < 2e-5, (s, rel)
+        # fp32 rounding (1e-7 per step) grows ~100x over 16 NGD steps (atomics make even two identical runs differ by ~1e-5);
+        # a chain that restored the wrong norm would be off by tens of per cent
+        assert rel < 5e-4, (s, rel)
 
 
 def test_batch_stat_normalisation_form_is_the_references():
