@@ -230,6 +230,79 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             mbar_wait(&tmem_full_bar[acc], use & 1);
             tc_fence_after();
+            if (kEpi == EPI_SUMS) {
+                // ---- store + BatchNorm statistics.  The accumulator is read in the MMA-fragment layout (16x256b): a thread
+                // holds 4 rows x 16 columns of a 64-column slab, adds its rows in registers and meets the 7 other threads
+                // that hold the same columns in 3 shuffle stages (14 exchanges per sum; the row-per-thread layout needs 31).
+                const int g = lane >> 2, tq = lane & 3;                 // row group / column pair inside a block of 8
+                bool ok[4];
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr) ok[rr] = m_tile * BM + q * 32 + g + 8 * rr < p.M;
+#pragma unroll
+                for (int a = 0; a < kAtoms; ++a) {
+                    uint32_t r0[32], r1[32];                            // rows g, g + 8 (r0) and g + 16, g + 24 (r1)
+                    tmem_ld_16x256b_x8(tm + a * 64, r0);
+                    tmem_ld_16x256b_x8(tm + a * 64 + (16u << 16), r1);
+                    tmem_ld_wait();
+                    if (a == kAtoms - 1) {               // whole accumulator is in registers: hand it back to the MMA warp
+                        tc_fence_before();
+                        mbar_arrive(&tmem_empty_bar[acc]);
+                    }
+                    float s1[16], s2[16];                               // index 2 i + e: column 8 i + 2 tq + e of the slab
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const float v0 = ok[0] ? __uint_as_float(r0[4 * i + e]) : 0.f;
+                            const float v1 = ok[1] ? __uint_as_float(r0[4 * i + 2 + e]) : 0.f;
+                            const float v2 = ok[2] ? __uint_as_float(r1[4 * i + e]) : 0.f;
+                            const float v3 = ok[3] ? __uint_as_float(r1[4 * i + 2 + e]) : 0.f;
+                            s1[2 * i + e] = (v0 + v1) + (v2 + v3);
+                            s2[2 * i + e] = fmaf(v0, v0, v1 * v1) + fmaf(v2, v2, v3 * v3);
+                        }
+                    // transpose-reduce over lane bits 4, 3, 2: afterwards s[0], s[1] are the totals of column block i = g
+#pragma unroll
+                    for (int off = 16, n = 8; off >= 4; off >>= 1, n >>= 1) {
+                        const bool upper = (lane & off) != 0;
+#pragma unroll
+                        for (int j = 0; j < n; ++j) {
+                            const float send1 = upper ? s1[j] : s1[j + n];
+                            const float send2 = upper ? s2[j] : s2[j + n];
+                            const float recv1 = __shfl_xor_sync(0xffffffffu, send1, off);
+                            const float recv2 = __shfl_xor_sync(0xffffffffu, send2, off);
+                            s1[j] = (upper ? s1[j + n] : s1[j]) + recv1;
+                            s2[j] = (upper ? s2[j + n] : s2[j]) + recv2;
+                        }
+                    }
+                    {   // columns 8 g + 2 tq + {0, 1} = 2 lane + {0, 1} of the slab
+                        float* sc = s_scr + ((wg * 4 + q) * 2) * BN + a * 64 + 2 * lane;
+                        *reinterpret_cast<float2*>(sc) = make_float2(s1[0], s1[1]);
+                        *reinterpret_cast<float2*>(sc + BN) = make_float2(s2[0], s2[1]);
+                    }
+                    // bf16 pairs → the 128B-swizzled staging slab (row & 7 == g for all four rows of this thread)
+                    uint8_t* atom = sC + a * 16384;
+#pragma unroll
+                    for (int rr = 0; rr < 4; ++rr) {
+                        const uint32_t* rs = (rr & 2) ? r1 : r0;
+                        const uint32_t rowoff = (uint32_t)(q * 32 + g + 8 * rr) * 128 + tq * 4;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(rs[4 * i + 2 * (rr & 1)]),
+                                                                           __uint_as_float(rs[4 * i + 2 * (rr & 1) + 1]));
+                            *reinterpret_cast<__nv_bfloat162*>(atom + rowoff + ((i ^ g) << 4)) = h;
+                        }
+                    }
+                    // the slab is complete: store it now, so its drain overlaps the conversion of the next slab
+                    fence_proxy_async();
+                    if (a + 1 < kAtoms && t > 1 && is_leader)          // the next slab must be free before anyone writes it
+                        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");          // the 4 warps of this warpgroup
+                    if (is_leader) {
+                        tma_store_2d(&tmC, sC + a * 16384, n_tile * BN + a * 64, m_tile * BM);
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                }
+            } else {
             // two register buffers: the TMEM load of chunk c+1 is in flight while chunk c is converted and stored
             uint32_t rbuf[2][32];
             tmem_ld_32x32(tm, rbuf[0]);
@@ -320,6 +393,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     }
                 }
+            }
             }
             if (has_sums) {
                 // the four warps' column partials of this tile are in the scratch array (ordered by the slab barrier above)

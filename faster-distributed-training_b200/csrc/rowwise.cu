@@ -265,41 +265,58 @@ linear_bwd_prep_kernel(const void* __restrict__ gout, const __nv_bfloat16* __res
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
     if (col < N) {
-        for (int64_t r = (int64_t)blockIdx.y * 8 + ty; r < T; r += (int64_t)gridDim.y * 8) {
-            const int64_t off = r * N + col;
-            float g[8];
-            if (kF32In) {
-                const float4 a = *reinterpret_cast<const float4*>(static_cast<const float*>(gout) + off);
-                const float4 b = *reinterpret_cast<const float4*>(static_cast<const float*>(gout) + off + 4);
-                g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
-            } else {
-                unpack8(ld8(static_cast<const __nv_bfloat16*>(gout) + off), g);
-            }
-            if (p > 0.f) {              // the forward applied dropout after the activation: same Philox stream
-                float m[8];
-                keep8(seed_off, off, p, m);
+        // four rows per trip: their loads are issued together (a thread otherwise has one 16-byte load in flight at a time,
+        // far too little to cover the memory latency with ~900 resident threads per SM)
+        constexpr int kU = 4;
+        const int64_t step = (int64_t)gridDim.y * 8;
+        for (int64_t r0 = (int64_t)blockIdx.y * 8 + ty; r0 < T; r0 += kU * step) {
+            float g[kU][8];
+            bf16x8 sv8[kU];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) g[j] *= m[j];
-            }
-            if (act != ACT_NONE) {
-                float sv[8];
-                unpack8(ld8(saved + off), sv);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    float d;
-                    if (act == ACT_GELU) {
-                        const float z = sv[j];
-                        d = 0.5f * (1.f + erff(z * 0.70710678118654752f)) + z * 0.39894228040143268f * __expf(-0.5f * z * z);
-                    } else {
-                        d = act_bwd_from_out(sv[j], act);
-                    }
-                    g[j] *= d;
+            for (int u = 0; u < kU; ++u) {
+                const int64_t r = r0 + u * step;
+                if (r >= T) break;
+                const int64_t off = r * N + col;
+                if (kF32In) {
+                    const float4 a = *reinterpret_cast<const float4*>(static_cast<const float*>(gout) + off);
+                    const float4 b = *reinterpret_cast<const float4*>(static_cast<const float*>(gout) + off + 4);
+                    g[u][0] = a.x; g[u][1] = a.y; g[u][2] = a.z; g[u][3] = a.w; g[u][4] = b.x; g[u][5] = b.y; g[u][6] = b.z; g[u][7] = b.w;
+                } else {
+                    unpack8(ld8(static_cast<const __nv_bfloat16*>(gout) + off), g[u]);
                 }
+                if (act != ACT_NONE) sv8[u] = ld8(saved + off);
             }
-            if (gz) st8(gz + off, pack8(g));
-            if (db) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[j] += gz ? __bfloat162float(__float2bfloat16(g[j])) : g[j];
+            for (int u = 0; u < kU; ++u) {
+                const int64_t r = r0 + u * step;
+                if (r >= T) break;
+                const int64_t off = r * N + col;
+                if (p > 0.f) {              // the forward applied dropout after the activation: same Philox stream
+                    float m[8];
+                    keep8(seed_off, off, p, m);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) g[u][j] *= m[j];
+                }
+                if (act != ACT_NONE) {
+                    float sv[8];
+                    unpack8(sv8[u], sv);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float d;
+                        if (act == ACT_GELU) {
+                            const float z = sv[j];
+                            d = 0.5f * (1.f + erff(z * 0.70710678118654752f)) + z * 0.39894228040143268f * __expf(-0.5f * z * z);
+                        } else {
+                            d = act_bwd_from_out(sv[j], act);
+                        }
+                        g[u][j] *= d;
+                    }
+                }
+                if (gz) st8(gz + off, pack8(g[u]));
+                if (db) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] += gz ? __bfloat162float(__float2bfloat16(g[u][j])) : g[u][j];
+                }
             }
         }
     }
