@@ -249,17 +249,29 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         mbar_arrive(&tmem_empty_bar[acc]);
                     }
                     float s1[16], s2[16];                               // index 2 i + e: column 8 i + 2 tq + e of the slab
+                    if (ok[3]) {                                        // all four rows exist (every tile but a ragged last one)
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
+                        for (int i = 0; i < 8; ++i)
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const float v0 = ok[0] ? __uint_as_float(r0[4 * i + e]) : 0.f;
-                            const float v1 = ok[1] ? __uint_as_float(r0[4 * i + 2 + e]) : 0.f;
-                            const float v2 = ok[2] ? __uint_as_float(r1[4 * i + e]) : 0.f;
-                            const float v3 = ok[3] ? __uint_as_float(r1[4 * i + 2 + e]) : 0.f;
-                            s1[2 * i + e] = (v0 + v1) + (v2 + v3);
-                            s2[2 * i + e] = fmaf(v0, v0, v1 * v1) + fmaf(v2, v2, v3 * v3);
-                        }
+                            for (int e = 0; e < 2; ++e) {
+                                const float v0 = __uint_as_float(r0[4 * i + e]), v1 = __uint_as_float(r0[4 * i + 2 + e]);
+                                const float v2 = __uint_as_float(r1[4 * i + e]), v3 = __uint_as_float(r1[4 * i + 2 + e]);
+                                s1[2 * i + e] = (v0 + v1) + (v2 + v3);
+                                s2[2 * i + e] = fmaf(v0, v0, v1 * v1) + fmaf(v2, v2, v3 * v3);
+                            }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const float v0 = ok[0] ? __uint_as_float(r0[4 * i + e]) : 0.f;
+                                const float v1 = ok[1] ? __uint_as_float(r0[4 * i + 2 + e]) : 0.f;
+                                const float v2 = ok[2] ? __uint_as_float(r1[4 * i + e]) : 0.f;
+                                const float v3 = ok[3] ? __uint_as_float(r1[4 * i + 2 + e]) : 0.f;
+                                s1[2 * i + e] = (v0 + v1) + (v2 + v3);
+                                s2[2 * i + e] = fmaf(v0, v0, v1 * v1) + fmaf(v2, v2, v3 * v3);
+                            }
+                    }
                     // transpose-reduce over lane bits 4, 3, 2: afterwards s[0], s[1] are the totals of column block i = g
 #pragma unroll
                     for (int off = 16, n = 8; off >= 4; off >>= 1, n >>= 1) {

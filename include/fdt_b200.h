@@ -48,6 +48,13 @@ int fdt_bn_act_fwd_fused(const void* y, const void* res, void* out, float* ctx, 
                          float momentum, int form, int act, cudaStream_t st);
 int fdt_bn_bwd_apply(const void* g, const void* y, void* dy, const float* sums, const float* ctx, float* dgamma,
                      float* dbeta, int64_t P, int C, int form, cudaStream_t st);
+/* Backward of a ReLU unit without a residual input, mask re-derived from y with the forward's coefficients (ctx, beta or
+   NULL) instead of read from the activated output: pass 1 accumulates (accumulate != 0) or writes sums[2C] = sum g*m,
+   sum g*m*y; pass 2 writes dy and dgamma / dbeta.  C / 8 must divide 256. */
+int fdt_chan_reduce2_masky(const void* g, const void* y, const float* ctx, const float* beta, float* sums, int accumulate,
+                           int64_t P, int C, cudaStream_t st);
+int fdt_bn_bwd_apply_masky(const void* g, const void* y, void* dy, const float* sums, const float* ctx, const float* beta,
+                           float* dgamma, float* dbeta, int64_t P, int C, int form, cudaStream_t st);
 int fdt_chan_reduce2_acc(const void* a, const void* b, const void* out_act, void* g_store, float* sums, int64_t P, int C,
                          int act, cudaStream_t st);
 /* same, when scratch[0 .. 2C) already holds Σy, Σy² per channel (written by the conv GEMM epilogue: `sums` of

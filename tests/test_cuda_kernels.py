@@ -60,6 +60,45 @@ def test_conv_bnstat_act_fwd_bwd(cin, cout, k, hw, act, res):
         _relnorm(rn.grad, rr.grad, 3e-2, "dres")
 
 
+@pytest.mark.parametrize("affine", [False, True])
+def test_bn_backward_mask_from_y_equals_mask_from_output(affine, monkeypatch):
+    """Backward of a ReLU unit without a residual input: the kernels that re-derive the mask from the conv output
+    (scale*y + shift > 0, the forward's expression) give the gradients of the ones that read it from the activated output."""
+    ops = _ops()
+    from fdt.ops import cuda_ops
+    torch.manual_seed(5)
+    N, cin, cout, hw = 8, 64, 128, 8
+    x = torch.randn(N, cin, hw, hw, device=DEV)
+    w = torch.randn(cout, cin, 3, 3, device=DEV) / math.sqrt(cin * 9)
+    gamma = torch.rand(cout, device=DEV) + 0.5
+    beta = torch.randn(cout, device=DEV) * 0.3
+    gout = torch.randn(N, cout, hw, hw, device=DEV).bfloat16().to(memory_format=torch.channels_last)
+    res = {}
+    for flag in (False, True):
+        monkeypatch.setattr(cuda_ops, "_BWD_MASKY", flag)
+        before = _lib_launches("fdt_bn_bwd_apply_masky")
+        xi = x.bfloat16().to(memory_format=torch.channels_last).requires_grad_(True)
+        wi = w.clone().requires_grad_(True)
+        if affine:
+            g, b = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+            rm, rv, nb = torch.zeros(cout, device=DEV), torch.ones(cout, device=DEV), torch.zeros((), dtype=torch.long, device=DEV)
+            o = ops.conv_bnaffine_act(xi, wi, g, b, rm, rv, nb, 1, 1, 1e-5, 0.1, True, "relu", None)
+        else:
+            o = ops.conv_bnstat_act(xi, wi, 1, 1, 1e-3, "relu", None)
+        o.backward(gout)
+        assert (_lib_launches("fdt_bn_bwd_apply_masky") > before) == flag
+        res[flag] = [xi.grad.float(), wi.grad.float()] + ([g.grad, b.grad] if affine else [])
+    for a, b_ in zip(res[False], res[True]):
+        assert torch.isfinite(b_).all()
+        rel = ((a - b_).norm() / a.norm().clamp_min(1e-12)).item()
+        assert rel < 1e-3, rel          # (the channel sums are atomic accumulations: the two runs are not bit-identical)
+
+
+def _lib_launches(name):
+    from fdt.ops import _lib
+    return _lib.LAUNCHES.by_name.get(name, 0)
+
+
 @pytest.mark.parametrize("training", [True, False])
 def test_conv_bnaffine_act(training):
     ops = _ops()
