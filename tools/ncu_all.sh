@@ -4,7 +4,9 @@
 set -u
 mkdir -p gpurun_out
 KEEP="gemm2 gemm conv3x3 conv_s2_dgrad attn512_fwd attn512_bwd wgrad ngd_tc_project"   # full reports kept (gpurun_out is capped at 64 MiB)
+# ONLY="name name ..." restricts the run to those captures
 cap() {  # name target regex skip
+  if [ -n "${ONLY:-}" ]; then case " $ONLY " in *" $1 "*) ;; *) return ;; esac; fi
   if [ ! -f gpurun_out/plain_ok_$2 ]; then
     python tools/ncu_target.py "$2" > gpurun_out/plain_$2.log 2>&1 && touch gpurun_out/plain_ok_$2
   fi
@@ -19,6 +21,7 @@ cap() {  # name target regex skip
 }
 cap conv3x3 conv3x3 gemm_nt 2
 cap conv1x1 conv1x1 gemm_nt 2
+cap conv1x1_stats conv1x1_stats gemm_nt 2
 cap gemm gemm1 gemm_nt_kernel 1
 cap gemm2 gemm2 gemm2_nt 1
 cap wgrad wgrad wgrad_kernel 2

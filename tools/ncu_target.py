@@ -13,12 +13,13 @@ from fdt.ops._lib import call, i64  # noqa: E402
 
 what = sys.argv[1] if len(sys.argv) > 1 else "conv1x1"
 B = 128
-if what in ("conv1x1", "conv3x3"):
-    C, O, HW, k = (64, 256, 32, 1) if what == "conv1x1" else (128, 128, 16, 3)
+if what in ("conv1x1", "conv1x1_stats", "conv3x3"):
+    C, O, HW, k = (128, 128, 16, 3) if what == "conv3x3" else (64, 256, 32, 1)
     x = torch.randn(B, C, HW, HW, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
     w = (torch.randn(O, C, k, k, device="cuda") / math.sqrt(C * k * k)).bfloat16().contiguous(memory_format=torch.channels_last)
+    sums = torch.zeros(2 * O, device="cuda") if what == "conv1x1_stats" else None     # BN statistics in the epilogue
     for _ in range(5):
-        y = g.conv_fwd(x, w, 1, k // 2)
+        y = g.conv_fwd(x, w, 1, k // 2, sums)
 elif what == "gemm":
     a = torch.randn(8192, 8192, device="cuda").bfloat16()
     b = torch.randn(8192, 8192, device="cuda").bfloat16()
