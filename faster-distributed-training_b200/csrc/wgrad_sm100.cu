@@ -341,11 +341,13 @@ FDT_API int fdt_conv_wgrad_ex(const void* dy, const void* x, float* dw, int Nb, 
     if (bh > OH) { if (bh % OH) return -1; bn = bh / OH; bh = OH; }
     else if (OH % bh) return -1;
     const int64_t P = (int64_t)Nb * OH * OW;
-    if (P % 64 || (bn > 1 && Nb % bn)) return -1;
+    // bn > 1 (maps smaller than 64 pixels): any batch size — a k-block is bn whole images, and the images / rows its two boxes
+    // reach beyond the batch are zero-filled by the TMA unit
+    if (bn == 1 && P % 64) return -1;
     CUtensorMap tmDY, tmX;
     if (!encode_pc(&tmDY, dy, Cout, P)) return -4;
     WgradParams p{};
-    p.Cout = Cout; p.Cin = Cin; p.taps = ksize * ksize; p.kw = ksize; p.pad = pad; p.num_kb = (int)(P / 64); p.dw = dw;
+    p.Cout = Cout; p.Cin = Cin; p.taps = ksize * ksize; p.kw = ksize; p.pad = pad; p.num_kb = (int)((P + 63) / 64); p.dw = dw;
     p.H = OH; p.W = OW; p.bh = bh; p.bn = bn; p.in_mul = stride; p.alpha = alpha; p.multicast = multicast;
     const bool wide = (Cin % 128 == 0);
     if (ksize == 1 && stride == 1) {

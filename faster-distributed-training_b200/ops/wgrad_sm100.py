@@ -30,11 +30,10 @@ def _conv_ok(x_shape, w_shape, stride, padding) -> bool:
         return False
     bh = 64 // W
     if bh > H:
-        if bh % H or N % (bh // H):
-            return False
-    elif H % bh:
-        return False
-    return (N * H * W) % 64 == 0
+        # several images per 64-pixel k-block (4x4 / 2x2 maps): any batch size — the images a box reaches beyond the batch
+        # are zero-filled by the TMA unit and contribute nothing
+        return bh % H == 0
+    return H % bh == 0 and (N * H * W) % 64 == 0
 
 
 def conv_wgrad(dy, x, w_shape, stride, padding, accumulate_into=None, alpha: float = 1.0, multicast: bool = False):

@@ -47,8 +47,11 @@ class SymmetricHeap:
         self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
         if self.world > MAX_WORLD:
             raise RuntimeError(f"symmetric heap supports up to {MAX_WORLD} ranks on one node")
-        try:
-            symm_mem.enable_symm_mem_for_group(self.group.group_name)
+        try:            # needed by older torch releases, a deprecated no-op in newer ones
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore", FutureWarning)
+                symm_mem.enable_symm_mem_for_group(self.group.group_name)
         except Exception:
             pass
         self.sig = symm_mem.empty(SIG_SLOTS * SIG_CHANNELS, dtype=torch.int32, device=self.device)

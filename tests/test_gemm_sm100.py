@@ -72,7 +72,9 @@ def test_conv_dgrad(N, C, O, HW, k):
 
 
 @pytest.mark.parametrize("N,C,O,HW,k", [(4, 64, 64, 32, 3), (8, 128, 128, 16, 3), (16, 256, 256, 8, 3), (16, 512, 512, 4, 3),
-                                          (4, 64, 256, 32, 1), (8, 256, 64, 16, 1), (8, 128, 192, 8, 3)])
+                                          (4, 64, 256, 32, 1), (8, 256, 64, 16, 1), (8, 128, 192, 8, 3),
+                                          # 4x4 maps with a batch that is not a multiple of the 4 images of a 64-pixel k-block
+                                          (10, 128, 64, 4, 3), (17, 64, 128, 4, 1)])
 def test_conv_wgrad(N, C, O, HW, k):
     from fdt.ops import wgrad_sm100 as wg
     torch.manual_seed(4)
