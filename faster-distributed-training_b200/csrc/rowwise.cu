@@ -304,8 +304,7 @@ linear_bwd_prep_kernel(const void* __restrict__ gout, const __nv_bfloat16* __res
                     for (int j = 0; j < 8; ++j) {
                         float d;
                         if (act == ACT_GELU) {
-                            const float z = sv[j];
-                            d = 0.5f * (1.f + erff(z * 0.70710678118654752f)) + z * 0.39894228040143268f * __expf(-0.5f * z * z);
+                            d = gelu_bwd_from_in(sv[j]);
                         } else {
                             d = act_bwd_from_out(sv[j], act);
                         }
