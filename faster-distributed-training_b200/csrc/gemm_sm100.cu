@@ -228,6 +228,14 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             }
+            // the residual addend does not depend on the accumulator: its 64 bytes per row and chunk are requested one chunk
+            // ahead (the first ones before the wait for the MMA), so the global-load latency is not paid inside every chunk
+            bf16x8 adn[2][4];
+            const __nv_bfloat16* ad_row = p.addend + orow * N + n_tile * BN;
+            if (has_addend && row_ok) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) adn[0][j] = ld8(ad_row + 8 * j);
+            }
             mbar_wait(&tmem_full_bar[acc], use & 1);
             tc_fence_after();
             if (kEpi == EPI_SUMS) {
@@ -326,6 +334,10 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     tc_fence_before();
                     mbar_arrive(&tmem_empty_bar[acc]);
                 }
+                if (has_addend && row_ok && c + 1 < BN / 32) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) adn[(c + 1) & 1][j] = ld8(ad_row + (c + 1) * 32 + 8 * j);
+                }
                 const uint32_t* r = rbuf[c & 1];
                 const int col0 = n_tile * BN + c * 32;
                 float v[32];
@@ -340,11 +352,10 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     for (int j = 0; j < 32; ++j) v[j] = act_fwd(v[j], p.act);
                 }
                 if (has_addend && row_ok) {
-                    const __nv_bfloat16* ad = p.addend + orow * N + col0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
                         float f[8];
-                        unpack8(ld8(ad + j), f);
+                        unpack8(adn[c & 1][j >> 3], f);
 #pragma unroll
                         for (int u = 0; u < 8; ++u) v[j + u] += f[u];
                     }
