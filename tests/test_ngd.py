@@ -161,3 +161,44 @@ def test_plain_sgd_mode_and_nesterov():
         o1.step()
         o2.step()
     assert torch.allclose(p, q)
+
+
+def test_one_norm_restoration_per_chain_equals_one_per_axis():
+    """The identity the CUDA path's NormChain rests on (fdt/ops/cuda_ops.py): on a step without a Fisher refresh every
+    axis's factor is a fixed linear map followed by a rescale to the norm of ITS input (ngd_optimizer.py:138-168), so over
+    a tensor's chain of axes the rescales telescope to out = X̂_last · sqrt(Σ X_first² / Σ X̂_last²)."""
+    torch.manual_seed(3)
+    n, shape = 2, (12, 10, 6)
+    fbs = [FactorBatch(n, (12 * 10 * 6) // D, D, 4.0, -1, 4, 0.1, torch.float64, "cpu") for D in shape]
+    warm = torch.randn(n, *shape, dtype=torch.float64)
+
+    def views(t, axis):                      # [n, N, D] view with the preconditioned axis last
+        return t.movedim(axis + 1, -1).reshape(n, -1, shape[axis])
+
+    def unview(m, axis):
+        moved = [n] + [s for i, s in enumerate(shape) if i != axis] + [shape[axis]]
+        return m.reshape(moved).movedim(-1, axis + 1)
+
+    for _ in range(13):                      # past the always-refresh start; the factors now hold some estimate
+        t = warm
+        for axis, fb in enumerate(fbs):
+            t = unview(precondition(fb, views(t, axis).contiguous(), left=False), axis)
+        warm = torch.randn_like(warm)
+    assert not any(fb.updating() for fb in fbs)          # step 13: no refresh
+    X0 = torch.randn(n, *shape, dtype=torch.float64)
+    # reference order: rescale after every axis (precondition() does that), factors untouched on this step
+    Ws = [fb.W.clone() for fb in fbs]
+    t = X0
+    for axis, fb in enumerate(fbs):
+        t = unview(precondition(fb, views(t, axis).contiguous(), left=False), axis)
+    for fb, W in zip(fbs, Ws):
+        assert torch.equal(fb.W, W)
+    # chain: deflate only, one rescale at the end
+    u = X0
+    for axis, W in enumerate(Ws):
+        Xm = views(u, axis)
+        H = torch.bmm(Xm, W.transpose(1, 2))
+        u = unview(Xm - torch.bmm(H, W), axis)
+    scale = (X0.flatten(1).pow(2).sum(1) / u.flatten(1).pow(2).sum(1)).sqrt()
+    chain = u * scale.view(n, 1, 1, 1)
+    assert torch.allclose(chain, t, rtol=1e-10, atol=1e-12)
